@@ -1,0 +1,140 @@
+/* xb200.h -- C ABI of libxb200, the B200-native layer-range forward + sampling engine.
+ *
+ * The reference (satoutahhaithem/xotorch_support_jetson) is 100% Python and has no FFI;
+ * its plugin boundary is the Python class `InferenceEngine`
+ * (xotorch/inference/inference_engine.py:11-51).  This header is the native layer that a
+ * drop-in `InferenceEngine` subclass binds with ctypes; each entry
+ * point cites the reference code whose work it replaces.  Paths are relative to the
+ * reference repository root.
+ *
+ * Conventions: every function returns 0 on success, non-zero on failure;
+ * xb_last_error() returns a thread-local message for the last failure on this thread.
+ * No C++ exception crosses this boundary.  All device work is enqueued on the
+ * caller-supplied CUDA stream (`stream` is a cudaStream_t passed as void*) and the calls
+ * do not synchronise unless the name ends in _sync.  One engine handle serves one
+ * (GPU, layer range); calls on a handle must come from one thread at a time (the
+ * reference serialises engine work on a 1-worker executor,
+ * xotorch/inference/torch/sharded_inference_engine.py:46).
+ * There is NO CPU fallback: without a CUDA device every compute entry point fails.
+ */
+#ifndef XB200_H
+#define XB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define XB_ABI_VERSION 1
+
+typedef struct xb_engine xb_engine;
+
+/* RoPE flavour (xotorch/inference/torch/models/general_mha.py:33-63) */
+enum {
+  XB_ROPE_INTERLEAVED = 0, /* Llama3ScaledRoPE / RotaryPositionalEmbeddings: pairs (2i,2i+1), fp32 math */
+  XB_ROPE_HALF_SPLIT = 1   /* Qwen2RotaryPositionalEmbeddings: pairs (i,i+hd/2), bf16 math            */
+};
+
+/* Static description of one shard of one model: the fields the reference derives in
+ * load_model_config (xotorch/inference/torch/models/llm_utils.py:30-77) plus the Shard key
+ * (xotorch/inference/shard.py:4-39: start_layer/end_layer inclusive). */
+typedef struct xb_model_desc {
+  int32_t n_layers, start_layer, end_layer;
+  int32_t dim, n_heads, n_kv_heads, head_dim, inter_dim, vocab;
+  float norm_eps;
+  int32_t rope_kind;         /* XB_ROPE_* */
+  int32_t rmsnorm_two_round; /* 1: torchtune 0.6 RMSNorm (normalise, round, scale, round); 0: single rounding */
+  int32_t qkv_bias;          /* Qwen: q/k/v projections carry a bias (general_mha.py:52) */
+  int32_t tied_head;         /* LM head shares the embedding matrix (general_mha.py:43-44,56-57) */
+  int32_t max_positions;     /* rows of the RoPE table uploaded with XB_W_ROPE_TABLE */
+  int32_t max_batch_tokens;  /* most token rows one xb_forward call may carry */
+  int32_t max_seqs;          /* most sequences one xb_forward call may carry */
+} xb_model_desc;
+
+/* Weight slots.  Row order is the reference's torchtune layout AFTER its HF->torchtune
+ * remap (llm_utils.py:181-258; Llama q/k rows permuted by _permute, llm_utils.py:126-134).
+ * All matrices are bf16, row-major [out_features, in_features]. */
+enum {
+  XB_W_Q = 0, XB_W_K, XB_W_V, XB_W_O, XB_W_GATE, XB_W_UP, XB_W_DOWN,
+  XB_W_SA_NORM, XB_W_MLP_NORM, XB_W_Q_BIAS, XB_W_K_BIAS, XB_W_V_BIAS, /* per layer */
+  XB_W_EMBED, XB_W_FINAL_NORM, XB_W_LM_HEAD,                          /* layer = -1 */
+  XB_W_ROPE_TABLE /* layer = -1: fp32 [max_positions, head_dim/2, 2] (cos, sin) */
+};
+
+/* One forward call over a ragged batch: sequence i contributes q_lens[i] consecutive
+ * token rows starting at absolute position positions[i] of KV slot slot_ids[i].
+ * Replaces the (tokens|hidden, mask, input_pos, curr_pos) plumbing of
+ * ShardedGeneralModel.generate (general_mha.py:178-254) and the per-request
+ * ShardInferenceState (llm_utils.py:473-511): causality and cache extent follow from the
+ * positions, no [L+1024, C] mask is built or shipped. */
+typedef struct xb_batch {
+  int32_t n_seqs;
+  const int32_t* slot_ids;  /* host [n_seqs] */
+  const int32_t* q_lens;    /* host [n_seqs] */
+  const int32_t* positions; /* host [n_seqs] */
+  const int32_t* tokens;    /* device int32 [sum q_lens]; first shard only, else NULL */
+  const void* hidden_in;    /* device bf16 [sum q_lens, dim]; non-first shard only, else NULL */
+} xb_batch;
+
+typedef struct xb_counters {
+  uint64_t launches;          /* kernels launched by this engine since creation */
+  uint64_t forwards;          /* xb_forward calls */
+  uint64_t weight_bytes;      /* bf16 bytes of this shard's matrices read by one decode step */
+  uint64_t kv_bytes_per_pos;  /* K+V bytes per cached position over this shard's layers */
+  uint64_t kv_pages_total, kv_pages_free;
+} xb_counters;
+
+const char* xb_last_error(void);
+int xb_abi_version(void);
+
+/* Replaces ShardedGeneralModel.__init__ / GeneralMHA (general_mha.py:23-176): allocates
+ * only what the layer range needs (embedding on a first shard; final norm + head on a
+ * last shard -- the reference allocates all three on every shard, general_mha.py:124-130). */
+int xb_engine_create(const xb_model_desc* desc, int device, xb_engine** out);
+int xb_engine_destroy(xb_engine* e);
+
+/* Replaces load_model_weights_torchtune + load_state_dict (llm_utils.py:136-284).
+ * `src` may be host or device memory; `layer` is the absolute layer index or -1. */
+int xb_load_weight(xb_engine* e, int layer, int kind, const void* src, size_t nbytes);
+
+/* Paged KV cache.  Replaces setup_caches / reset_caches / KVCache.update
+ * (llm_utils.py:320-365; sharded_inference_engine.py:71-82,139-147): pages of
+ * `page_tokens` positions are handed to a slot on demand as it grows and returned by
+ * xb_kv_release_slot; nothing is zero-filled. */
+int xb_kv_reserve(xb_engine* e, int n_slots, int max_tokens_per_slot, int page_tokens);
+int xb_kv_release_slot(xb_engine* e, int slot);
+int xb_kv_slot_len(xb_engine* e, int slot, int* len);
+
+/* Replaces ShardTransformerDecoder.forward (llm_utils.py:367-440) with the intended
+ * hand-off semantics (a non-last shard returns the OUTPUT of its last layer).
+ * out: device bf16 [T, dim] on a non-last shard; device fp32 [n_seqs, vocab] logits of the
+ * last position of each sequence on a last shard (bf16-rounded values, as the reference's
+ * `model_logits[:, -1].float()`, sharded_inference_engine.py:366).
+ * taps: NULL, or (end_layer-start_layer+1) device pointers, each bf16 [T, dim], that
+ * receive the residual stream after each layer (parity instrumentation). */
+int xb_forward(xb_engine* e, const xb_batch* batch, void* out, void* const* taps, void* stream);
+
+/* Replaces TorchDynamicShardInferenceEngine.sample + torchtune.generation.sample
+ * (sharded_inference_engine.py:208-228).  logits: device fp32 [n, vocab].
+ * temp <= 0 selects first-index argmax.  top_k <= 0 and top_p <= 0 (or >= 1) disable
+ * the respective filter.  q: NULL (counter-based noise from `seed`) or device fp32
+ * [n, vocab] Exp(1) noise (reference-exact replay of its torch.Generator stream).
+ * tokens_out: device int32 [n]. */
+int xb_sample(xb_engine* e, const float* logits, int n, float temp, int top_k, float top_p, const float* q,
+              uint64_t seed, int32_t* tokens_out, void* stream);
+
+int xb_get_counters(xb_engine* e, xb_counters* out);
+
+/* Kernel-level test hook: y[T,N] (fp32) = x[T,K] * w[N,K]^T on device buffers.
+ * use_tensor_cores = 1 runs the tcgen05 kernel the engine uses (force_splits > 0 pins the
+ * K split count; round_bf16 rounds like nn.Linear), 0 runs the CUDA-core checker kernel.
+ * scratch: device fp32, at least 16*T*N elements. */
+int xb_debug_linear(const void* x, const void* w, int T, int N, int K, float* y, float* scratch,
+                    int use_tensor_cores, int force_splits, int round_bf16, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* XB200_H */

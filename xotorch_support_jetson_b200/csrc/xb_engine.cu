@@ -1,0 +1,541 @@
+// libxb200: the C ABI declared in include/xb200.h.
+// Engine object = weights of one layer range + paged KV cache + workspaces + launch plans.
+#include "../../include/xb200.h"
+#include "xb_common.cuh"
+#include "xb_gemm.cuh"
+#include "xb_kernels.cuh"
+
+#include <stdarg.h>
+#include <map>
+#include <vector>
+
+thread_local std::string g_xb_err;
+
+int xb_fail(int code, const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_xb_err = buf;
+  return code;
+}
+
+struct LayerW {
+  bf16 *wqkv = nullptr, *bqkv = nullptr, *wo = nullptr, *wgu = nullptr, *wdown = nullptr;
+  bf16 *sa_norm = nullptr, *mlp_norm = nullptr;
+  bf16 *k_pool = nullptr, *v_pool = nullptr;
+};
+
+enum Site { SITE_QKV = 0, SITE_O, SITE_GU, SITE_DOWN, SITE_HEAD };
+
+struct xb_engine {
+  xb_model_desc d;
+  int device = 0;
+  int num_sms = 148;
+  int nl = 0;  // local layers
+  int NQ = 0, NKV = 0, NQKV = 0;
+  std::vector<LayerW> L;
+  bf16 *embed = nullptr, *final_norm = nullptr, *lm_head = nullptr;
+  float* rope = nullptr;
+  // kv paging
+  int n_slots = 0, max_pages = 0, page_tokens = 0, n_pages = 0;
+  std::vector<int> free_pages;
+  std::vector<std::vector<int>> slot_pages;
+  std::vector<int> slot_len;
+  std::vector<int> h_page_table;
+  int* d_page_table = nullptr;
+  // batch meta (device)
+  int *d_tok_seq = nullptr, *d_tok_pos = nullptr, *d_seq_slot = nullptr, *d_seq_last = nullptr;
+  std::vector<int> h_meta;
+  // workspaces
+  bf16 *h = nullptr, *hn = nullptr, *q = nullptr, *attn = nullptr, *act = nullptr, *last_rows = nullptr;
+  void* gemm_out = nullptr;
+  size_t gemm_out_bytes = 0;
+  float *o_part = nullptr, *ml_part = nullptr;
+  int max_attn_splits = 16;
+  std::map<long long, GemmPlan> plans;
+  xb_counters c{};
+};
+
+#define LAUNCH_COUNT(e) ((e)->c.launches++)
+
+static int dmalloc(void** p, size_t bytes) {
+  XB_CUDA(cudaMalloc(p, bytes ? bytes : 16));
+  return 0;
+}
+
+extern "C" const char* xb_last_error(void) { return g_xb_err.c_str(); }
+extern "C" int xb_abi_version(void) { return XB_ABI_VERSION; }
+
+extern "C" int xb_engine_create(const xb_model_desc* desc, int device, xb_engine** out) {
+  XB_CHECK(desc != nullptr && out != nullptr, "null argument");
+  int ndev = 0;
+  cudaError_t ce = cudaGetDeviceCount(&ndev);
+  XB_CHECK(ce == cudaSuccess && ndev > 0, "no CUDA device available (%s): libxb200 has no CPU fallback",
+           cudaGetErrorString(ce));
+  XB_CHECK(device >= 0 && device < ndev, "device %d out of range (%d devices)", device, ndev);
+  XB_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  XB_CUDA(cudaGetDeviceProperties(&prop, device));
+  XB_CHECK(prop.major == 10, "libxb200 is built for sm_100a only; device %d is sm_%d%d", device, prop.major, prop.minor);
+  const xb_model_desc& d = *desc;
+  XB_CHECK(d.start_layer >= 0 && d.end_layer >= d.start_layer && d.end_layer < d.n_layers, "bad layer range [%d,%d] of %d",
+           d.start_layer, d.end_layer, d.n_layers);
+  XB_CHECK(d.head_dim == 64 || d.head_dim == 128, "head_dim %d not supported (64 or 128)", d.head_dim);
+  XB_CHECK(d.n_heads % d.n_kv_heads == 0, "n_heads %d not a multiple of n_kv_heads %d", d.n_heads, d.n_kv_heads);
+  XB_CHECK(d.dim % 8 == 0 && d.inter_dim % 8 == 0, "dim/inter_dim must be multiples of 8");
+  XB_CHECK(d.max_batch_tokens > 0 && d.max_seqs > 0 && d.max_positions > 0, "max_batch_tokens/max_seqs/max_positions must be > 0");
+  xb_engine* e = new xb_engine();
+  e->d = d;
+  e->device = device;
+  e->num_sms = prop.multiProcessorCount;
+  e->nl = d.end_layer - d.start_layer + 1;
+  e->NQ = d.n_heads * d.head_dim;
+  e->NKV = d.n_kv_heads * d.head_dim;
+  e->NQKV = e->NQ + 2 * e->NKV;
+  e->L.resize(e->nl);
+  const size_t D = d.dim, I = d.inter_dim;
+  uint64_t wbytes = 0;
+  for (int l = 0; l < e->nl; ++l) {
+    LayerW& w = e->L[l];
+    XB_TRY(dmalloc((void**)&w.wqkv, (size_t)e->NQKV * D * 2));
+    XB_TRY(dmalloc((void**)&w.wo, D * e->NQ * 2));
+    XB_TRY(dmalloc((void**)&w.wgu, 2 * I * D * 2));
+    XB_TRY(dmalloc((void**)&w.wdown, D * I * 2));
+    XB_TRY(dmalloc((void**)&w.sa_norm, D * 2));
+    XB_TRY(dmalloc((void**)&w.mlp_norm, D * 2));
+    if (d.qkv_bias) {
+      XB_TRY(dmalloc((void**)&w.bqkv, (size_t)e->NQKV * 2));
+      XB_CUDA(cudaMemset(w.bqkv, 0, (size_t)e->NQKV * 2));
+    }
+    wbytes += ((size_t)e->NQKV * D + D * e->NQ + 3 * I * D) * 2;
+  }
+  const bool first = d.start_layer == 0, last = d.end_layer == d.n_layers - 1;
+  if (first || (last && d.tied_head)) XB_TRY(dmalloc((void**)&e->embed, (size_t)d.vocab * D * 2));
+  if (last) {
+    XB_TRY(dmalloc((void**)&e->final_norm, D * 2));
+    if (!d.tied_head) XB_TRY(dmalloc((void**)&e->lm_head, (size_t)d.vocab * D * 2));
+    wbytes += (size_t)d.vocab * D * 2;
+  }
+  XB_TRY(dmalloc((void**)&e->rope, (size_t)d.max_positions * (d.head_dim / 2) * 2 * sizeof(float)));
+  e->c.weight_bytes = wbytes;
+  e->c.kv_bytes_per_pos = (uint64_t)2 * e->nl * e->NKV * 2;
+  // workspaces
+  const size_t T = d.max_batch_tokens;
+  XB_TRY(dmalloc((void**)&e->h, T * D * 2));
+  XB_TRY(dmalloc((void**)&e->hn, T * D * 2));
+  XB_TRY(dmalloc((void**)&e->q, T * e->NQ * 2));
+  XB_TRY(dmalloc((void**)&e->attn, T * e->NQ * 2));
+  XB_TRY(dmalloc((void**)&e->act, T * I * 2));
+  XB_TRY(dmalloc((void**)&e->last_rows, (size_t)d.max_seqs * D * 2));
+  size_t maxN = e->NQKV;
+  if (2 * I > maxN) maxN = 2 * I;
+  if (D > maxN) maxN = D;
+  e->gemm_out_bytes = T * maxN * 2;
+  if (e->gemm_out_bytes < ((size_t)64 << 20)) e->gemm_out_bytes = (size_t)64 << 20;
+  XB_TRY(dmalloc(&e->gemm_out, e->gemm_out_bytes));
+  XB_TRY(dmalloc((void**)&e->o_part, T * d.n_heads * e->max_attn_splits * d.head_dim * sizeof(float)));
+  XB_TRY(dmalloc((void**)&e->ml_part, T * d.n_heads * e->max_attn_splits * 2 * sizeof(float)));
+  XB_TRY(dmalloc((void**)&e->d_tok_seq, T * 4));
+  XB_TRY(dmalloc((void**)&e->d_tok_pos, T * 4));
+  XB_TRY(dmalloc((void**)&e->d_seq_slot, (size_t)d.max_seqs * 4));
+  XB_TRY(dmalloc((void**)&e->d_seq_last, (size_t)d.max_seqs * 4));
+  *out = e;
+  return 0;
+}
+
+extern "C" int xb_engine_destroy(xb_engine* e) {
+  if (e == nullptr) return 0;
+  cudaSetDevice(e->device);
+  cudaDeviceSynchronize();
+  for (LayerW& w : e->L) {
+    cudaFree(w.wqkv); cudaFree(w.bqkv); cudaFree(w.wo); cudaFree(w.wgu); cudaFree(w.wdown);
+    cudaFree(w.sa_norm); cudaFree(w.mlp_norm); cudaFree(w.k_pool); cudaFree(w.v_pool);
+  }
+  cudaFree(e->embed); cudaFree(e->final_norm); cudaFree(e->lm_head); cudaFree(e->rope);
+  cudaFree(e->d_page_table); cudaFree(e->d_tok_seq); cudaFree(e->d_tok_pos); cudaFree(e->d_seq_slot);
+  cudaFree(e->d_seq_last); cudaFree(e->h); cudaFree(e->hn); cudaFree(e->q); cudaFree(e->attn); cudaFree(e->act);
+  cudaFree(e->last_rows); cudaFree(e->gemm_out); cudaFree(e->o_part); cudaFree(e->ml_part);
+  delete e;
+  return 0;
+}
+
+extern "C" int xb_load_weight(xb_engine* e, int layer, int kind, const void* src, size_t nbytes) {
+  XB_CHECK(e != nullptr && src != nullptr, "null argument");
+  XB_CUDA(cudaSetDevice(e->device));
+  const xb_model_desc& d = e->d;
+  const size_t D = d.dim, I = d.inter_dim;
+  void* dst = nullptr;
+  size_t want = 0;
+  if (layer >= 0) {
+    XB_CHECK(layer >= d.start_layer && layer <= d.end_layer, "layer %d outside this shard [%d,%d]", layer, d.start_layer,
+             d.end_layer);
+    LayerW& w = e->L[layer - d.start_layer];
+    switch (kind) {
+      case XB_W_Q: dst = w.wqkv; want = (size_t)e->NQ * D * 2; break;
+      case XB_W_K: dst = w.wqkv + (size_t)e->NQ * D; want = (size_t)e->NKV * D * 2; break;
+      case XB_W_V: dst = w.wqkv + (size_t)(e->NQ + e->NKV) * D; want = (size_t)e->NKV * D * 2; break;
+      case XB_W_O: dst = w.wo; want = D * e->NQ * 2; break;
+      case XB_W_GATE: dst = w.wgu; want = I * D * 2; break;
+      case XB_W_UP: dst = w.wgu + I * D; want = I * D * 2; break;
+      case XB_W_DOWN: dst = w.wdown; want = D * I * 2; break;
+      case XB_W_SA_NORM: dst = w.sa_norm; want = D * 2; break;
+      case XB_W_MLP_NORM: dst = w.mlp_norm; want = D * 2; break;
+      case XB_W_Q_BIAS: XB_CHECK(w.bqkv, "model has no qkv bias"); dst = w.bqkv; want = (size_t)e->NQ * 2; break;
+      case XB_W_K_BIAS: XB_CHECK(w.bqkv, "model has no qkv bias"); dst = w.bqkv + e->NQ; want = (size_t)e->NKV * 2; break;
+      case XB_W_V_BIAS: XB_CHECK(w.bqkv, "model has no qkv bias"); dst = w.bqkv + e->NQ + e->NKV; want = (size_t)e->NKV * 2; break;
+      default: return xb_fail(1, "weight kind %d is not a per-layer kind", kind);
+    }
+  } else {
+    switch (kind) {
+      case XB_W_EMBED: XB_CHECK(e->embed, "this shard holds no embedding"); dst = e->embed; want = (size_t)d.vocab * D * 2; break;
+      case XB_W_FINAL_NORM: XB_CHECK(e->final_norm, "this shard holds no final norm"); dst = e->final_norm; want = D * 2; break;
+      case XB_W_LM_HEAD: XB_CHECK(e->lm_head, "this shard holds no separate LM head"); dst = e->lm_head; want = (size_t)d.vocab * D * 2; break;
+      case XB_W_ROPE_TABLE: dst = e->rope; want = (size_t)d.max_positions * (d.head_dim / 2) * 2 * sizeof(float); break;
+      default: return xb_fail(1, "weight kind %d is not a global kind", kind);
+    }
+  }
+  XB_CHECK(nbytes == want, "weight kind %d layer %d: got %zu bytes, expected %zu", kind, layer, nbytes, want);
+  XB_CUDA(cudaMemcpy(dst, src, nbytes, cudaMemcpyDefault));
+  return 0;
+}
+
+// ----------------------------------------------------------------------------- paged KV
+extern "C" int xb_kv_reserve(xb_engine* e, int n_slots, int max_tokens_per_slot, int page_tokens) {
+  XB_CHECK(e != nullptr, "null engine");
+  XB_CHECK(n_slots > 0 && max_tokens_per_slot > 0 && page_tokens > 0, "bad kv_reserve arguments");
+  XB_CUDA(cudaSetDevice(e->device));
+  XB_CUDA(cudaDeviceSynchronize());
+  for (LayerW& w : e->L) {
+    cudaFree(w.k_pool); cudaFree(w.v_pool);
+    w.k_pool = w.v_pool = nullptr;
+  }
+  cudaFree(e->d_page_table);
+  e->d_page_table = nullptr;
+  e->n_slots = n_slots;
+  e->page_tokens = page_tokens;
+  e->max_pages = (max_tokens_per_slot + page_tokens - 1) / page_tokens;
+  e->n_pages = n_slots * e->max_pages;
+  const size_t pool_bytes = (size_t)e->n_pages * e->NKV * page_tokens * 2;
+  for (LayerW& w : e->L) {
+    XB_TRY(dmalloc((void**)&w.k_pool, pool_bytes));
+    XB_TRY(dmalloc((void**)&w.v_pool, pool_bytes));
+  }
+  e->free_pages.clear();
+  for (int p = e->n_pages - 1; p >= 0; --p) e->free_pages.push_back(p);
+  e->slot_pages.assign(n_slots, std::vector<int>());
+  e->slot_len.assign(n_slots, 0);
+  e->h_page_table.assign((size_t)n_slots * e->max_pages, 0);
+  XB_TRY(dmalloc((void**)&e->d_page_table, e->h_page_table.size() * 4));
+  XB_CUDA(cudaMemset(e->d_page_table, 0, e->h_page_table.size() * 4));
+  e->c.kv_pages_total = e->n_pages;
+  e->c.kv_pages_free = e->free_pages.size();
+  return 0;
+}
+
+extern "C" int xb_kv_release_slot(xb_engine* e, int slot) {
+  XB_CHECK(e != nullptr && slot >= 0 && slot < e->n_slots, "bad slot %d", slot);
+  for (int p : e->slot_pages[slot]) e->free_pages.push_back(p);
+  e->slot_pages[slot].clear();
+  e->slot_len[slot] = 0;
+  e->c.kv_pages_free = e->free_pages.size();
+  return 0;
+}
+
+extern "C" int xb_kv_slot_len(xb_engine* e, int slot, int* len) {
+  XB_CHECK(e != nullptr && len != nullptr && slot >= 0 && slot < e->n_slots, "bad slot %d", slot);
+  *len = e->slot_len[slot];
+  return 0;
+}
+
+// ----------------------------------------------------------------------------- forward
+static int get_plan(xb_engine* e, int site, int layer, const bf16* x, long long ldx, const bf16* w, int T, int N, int K,
+                    void* out, long long ld_out, const bf16* bias, int round_bf16, const GemmPlan** pp) {
+  const long long key = (((long long)site * 4096 + layer) << 32) | (unsigned)T;
+  auto it = e->plans.find(key);
+  if (it == e->plans.end()) {
+    GemmPlan p;
+    XB_TRY(xb_gemm_plan(&p, x, ldx, w, T, N, K, out, ld_out, bias, round_bf16, e->num_sms, 0));
+    if (out == e->gemm_out) {
+      const size_t need = p.args.mode == XB_GEMM_SKINNY ? (size_t)p.args.splits * T * N * 4 : (size_t)T * N * 2;
+      XB_CHECK(need <= e->gemm_out_bytes, "gemm workspace too small: need %zu have %zu", need, e->gemm_out_bytes);
+    }
+    it = e->plans.emplace(key, p).first;
+  }
+  *pp = &it->second;
+  return 0;
+}
+
+template <int HD>
+static int launch_attn(xb_engine* e, const LayerW& w, const BatchMeta& m, int T, int n_splits, cudaStream_t st) {
+  const xb_model_desc& d = e->d;
+  const int G = d.n_heads / d.n_kv_heads;
+  const float scale = 1.0f / sqrtf((float)d.head_dim);
+  dim3 grid(T, d.n_kv_heads, n_splits);
+#define XB_ATTN_CASE(GG)                                                                                            \
+  case GG:                                                                                                          \
+    xb_attn_split_kernel<HD, GG><<<grid, 128, 0, st>>>(e->q, w.k_pool, w.v_pool, m, e->o_part, e->ml_part, e->attn, \
+                                                       d.n_heads, d.n_kv_heads, n_splits, scale);                   \
+    break;
+  switch (G) {
+    XB_ATTN_CASE(1) XB_ATTN_CASE(2) XB_ATTN_CASE(3) XB_ATTN_CASE(4) XB_ATTN_CASE(5) XB_ATTN_CASE(6) XB_ATTN_CASE(7)
+    XB_ATTN_CASE(8)
+    default: return xb_fail(1, "GQA group size %d not supported (1..8)", G);
+  }
+#undef XB_ATTN_CASE
+  XB_CUDA(cudaGetLastError());
+  LAUNCH_COUNT(e);
+  if (n_splits > 1) {
+    xb_attn_combine_kernel<<<T * d.n_heads, d.head_dim, 0, st>>>(e->o_part, e->ml_part, e->attn, n_splits, d.head_dim);
+    XB_CUDA(cudaGetLastError());
+    LAUNCH_COUNT(e);
+  }
+  return 0;
+}
+
+static int launch_resid_norm(xb_engine* e, const GemmPlan* gp, int T, const bf16* nw, cudaStream_t st) {
+  const xb_model_desc& d = e->d;
+  const size_t smem = (size_t)d.dim * sizeof(float);
+  if (gp->args.mode == XB_GEMM_SKINNY) {
+    xb_resid_norm_kernel<256, 0><<<T, 256, smem, st>>>((const float*)e->gemm_out, gp->args.splits, (long long)T * d.dim,
+                                                        nullptr, e->h, nw, e->hn, d.dim, d.norm_eps, d.rmsnorm_two_round);
+  } else {
+    xb_resid_norm_kernel<256, 1><<<T, 256, smem, st>>>(nullptr, 1, 0, (const bf16*)e->gemm_out, e->h, nw, e->hn, d.dim,
+                                                        d.norm_eps, d.rmsnorm_two_round);
+  }
+  XB_CUDA(cudaGetLastError());
+  LAUNCH_COUNT(e);
+  return 0;
+}
+
+extern "C" int xb_forward(xb_engine* e, const xb_batch* b, void* out, void* const* taps, void* stream) {
+  XB_CHECK(e != nullptr && b != nullptr && out != nullptr, "null argument");
+  const xb_model_desc& d = e->d;
+  cudaStream_t st = (cudaStream_t)stream;
+  XB_CUDA(cudaSetDevice(e->device));
+  XB_CHECK(e->n_slots > 0, "xb_kv_reserve must be called before xb_forward");
+  XB_CHECK(b->n_seqs > 0 && b->n_seqs <= d.max_seqs, "n_seqs %d out of range (max %d)", b->n_seqs, d.max_seqs);
+  const bool first = d.start_layer == 0, last = d.end_layer == d.n_layers - 1;
+  XB_CHECK(first ? (b->tokens != nullptr) : (b->hidden_in != nullptr),
+           first ? "first shard needs token ids" : "non-first shard needs a hidden state");
+  // ---- host-side batch bookkeeping
+  int T = 0, max_ctx = 0;
+  for (int i = 0; i < b->n_seqs; ++i) {
+    const int slot = b->slot_ids[i], ql = b->q_lens[i], pos = b->positions[i];
+    XB_CHECK(slot >= 0 && slot < e->n_slots, "seq %d: slot %d out of range", i, slot);
+    XB_CHECK(ql > 0 && pos >= 0, "seq %d: bad q_len %d / position %d", i, ql, pos);
+    XB_CHECK(pos <= e->slot_len[slot], "seq %d: position %d leaves a gap after cached length %d", i, pos, e->slot_len[slot]);
+    XB_CHECK(pos + ql <= e->max_pages * e->page_tokens, "seq %d: %d tokens exceed the reserved %d per slot", i, pos + ql,
+             e->max_pages * e->page_tokens);
+    XB_CHECK(pos + ql <= d.max_positions, "seq %d: position %d beyond the RoPE table (%d rows)", i, pos + ql, d.max_positions);
+    for (int j = 0; j < i; ++j) XB_CHECK(b->slot_ids[j] != slot, "slot %d appears twice in one batch", slot);
+    T += ql;
+    if (pos + ql > max_ctx) max_ctx = pos + ql;
+  }
+  XB_CHECK(T <= d.max_batch_tokens, "batch carries %d token rows, engine was created for %d", T, d.max_batch_tokens);
+  std::vector<int>& hm = e->h_meta;
+  hm.assign((size_t)2 * T + 2 * b->n_seqs, 0);
+  int* tok_seq = hm.data();
+  int* tok_pos = tok_seq + T;
+  int* seq_slot = tok_pos + T;
+  int* seq_last = seq_slot + b->n_seqs;
+  int r = 0;
+  for (int i = 0; i < b->n_seqs; ++i) {
+    const int slot = b->slot_ids[i], ql = b->q_lens[i], pos = b->positions[i];
+    // grow the slot's page list (pages come from the shared free list: non-contiguous)
+    const int need_pages = (pos + ql + e->page_tokens - 1) / e->page_tokens;
+    std::vector<int>& pages = e->slot_pages[slot];
+    if ((int)pages.size() < need_pages) {
+      const int old = (int)pages.size();
+      while ((int)pages.size() < need_pages) {
+        XB_CHECK(!e->free_pages.empty(), "KV page pool exhausted");
+        const int p = e->free_pages.back();
+        e->free_pages.pop_back();
+        e->h_page_table[(size_t)slot * e->max_pages + pages.size()] = p;
+        pages.push_back(p);
+      }
+      XB_CUDA(cudaMemcpyAsync(e->d_page_table + (size_t)slot * e->max_pages + old,
+                              e->h_page_table.data() + (size_t)slot * e->max_pages + old, (need_pages - old) * 4,
+                              cudaMemcpyHostToDevice, st));
+    }
+    for (int j = 0; j < ql; ++j) {
+      tok_seq[r] = i;
+      tok_pos[r] = pos + j;
+      ++r;
+    }
+    seq_slot[i] = slot;
+    seq_last[i] = r - 1;
+    e->slot_len[slot] = pos + ql;
+  }
+  e->c.kv_pages_free = e->free_pages.size();
+  XB_CUDA(cudaMemcpyAsync(e->d_tok_seq, tok_seq, T * 4, cudaMemcpyHostToDevice, st));
+  XB_CUDA(cudaMemcpyAsync(e->d_tok_pos, tok_pos, T * 4, cudaMemcpyHostToDevice, st));
+  XB_CUDA(cudaMemcpyAsync(e->d_seq_slot, seq_slot, b->n_seqs * 4, cudaMemcpyHostToDevice, st));
+  XB_CUDA(cudaMemcpyAsync(e->d_seq_last, seq_last, b->n_seqs * 4, cudaMemcpyHostToDevice, st));
+  BatchMeta m;
+  m.tok_seq = e->d_tok_seq;
+  m.tok_pos = e->d_tok_pos;
+  m.seq_slot = e->d_seq_slot;
+  m.seq_last = e->d_seq_last;
+  m.page_table = e->d_page_table;
+  m.max_pages = e->max_pages;
+  m.page_tokens = e->page_tokens;
+
+  const int D = d.dim, I = d.inter_dim, hd = d.head_dim;
+  const size_t norm_smem = (size_t)D * sizeof(float);
+  // ---- stage input
+  if (first) {
+    xb_embed_norm_kernel<256><<<T, 256, 0, st>>>(b->tokens, e->embed, e->L[0].sa_norm, e->h, e->hn, D, d.vocab, d.norm_eps,
+                                                  d.rmsnorm_two_round);
+  } else {
+    XB_CUDA(cudaMemcpyAsync(e->h, b->hidden_in, (size_t)T * D * 2, cudaMemcpyDeviceToDevice, st));
+    xb_resid_norm_kernel<256, 2><<<T, 256, norm_smem, st>>>(nullptr, 0, 0, nullptr, e->h, e->L[0].sa_norm, e->hn, D,
+                                                             d.norm_eps, d.rmsnorm_two_round);
+  }
+  XB_CUDA(cudaGetLastError());
+  LAUNCH_COUNT(e);
+
+  // kv splits: enough blocks to fill the GPU at decode, none needed when T is large
+  int n_splits = 1;
+  {
+    const int blocks = T * d.n_kv_heads;
+    const int pages = (max_ctx + e->page_tokens - 1) / e->page_tokens;
+    if (blocks < 2 * e->num_sms) {
+      n_splits = (2 * e->num_sms + blocks - 1) / blocks;
+      if (n_splits > pages) n_splits = pages;
+      if (n_splits > e->max_attn_splits) n_splits = e->max_attn_splits;
+      if (n_splits < 1) n_splits = 1;
+    }
+  }
+
+  for (int l = 0; l < e->nl; ++l) {
+    const LayerW& w = e->L[l];
+    const GemmPlan* gp;
+    // q/k/v projections as one GEMM (general_mha.py:83-97)
+    XB_TRY(get_plan(e, SITE_QKV, l, e->hn, D, w.wqkv, T, e->NQKV, D, e->gemm_out, e->NQKV, w.bqkv, 0, &gp));
+    XB_TRY(xb_gemm_run(*gp, st));
+    LAUNCH_COUNT(e);
+    {
+      dim3 grid(T, d.n_heads + 2 * d.n_kv_heads);
+      if (gp->args.mode == XB_GEMM_SKINNY)
+        xb_qkv_finalize_kernel<0><<<grid, hd / 2, 0, st>>>((const float*)e->gemm_out, gp->args.splits, (long long)T * e->NQKV,
+                                                            nullptr, w.bqkv, e->rope, e->q, w.k_pool, w.v_pool, m, d.n_heads,
+                                                            d.n_kv_heads, hd, d.rope_kind);
+      else
+        xb_qkv_finalize_kernel<1><<<grid, hd / 2, 0, st>>>(nullptr, 1, 0, (const bf16*)e->gemm_out, nullptr, e->rope, e->q,
+                                                            w.k_pool, w.v_pool, m, d.n_heads, d.n_kv_heads, hd, d.rope_kind);
+      XB_CUDA(cudaGetLastError());
+      LAUNCH_COUNT(e);
+    }
+    if (hd == 128) XB_TRY(launch_attn<128>(e, w, m, T, n_splits, st));
+    else XB_TRY(launch_attn<64>(e, w, m, T, n_splits, st));
+    // output projection + residual + mlp_norm
+    XB_TRY(get_plan(e, SITE_O, l, e->attn, e->NQ, w.wo, T, D, e->NQ, e->gemm_out, D, nullptr, 0, &gp));
+    XB_TRY(xb_gemm_run(*gp, st));
+    LAUNCH_COUNT(e);
+    XB_TRY(launch_resid_norm(e, gp, T, w.mlp_norm, st));
+    // gate/up as one GEMM, SiLU*up, down projection (llm_utils.py:513-522)
+    XB_TRY(get_plan(e, SITE_GU, l, e->hn, D, w.wgu, T, 2 * I, D, e->gemm_out, 2 * I, nullptr, 0, &gp));
+    XB_TRY(xb_gemm_run(*gp, st));
+    LAUNCH_COUNT(e);
+    {
+      const long long n = (long long)T * I;
+      const int blocks = (int)((n + 255) / 256);
+      if (gp->args.mode == XB_GEMM_SKINNY)
+        xb_silu_mul_kernel<0><<<blocks, 256, 0, st>>>((const float*)e->gemm_out, gp->args.splits, (long long)T * 2 * I, nullptr,
+                                                       e->act, T, I);
+      else
+        xb_silu_mul_kernel<1><<<blocks, 256, 0, st>>>(nullptr, 1, 0, (const bf16*)e->gemm_out, e->act, T, I);
+      XB_CUDA(cudaGetLastError());
+      LAUNCH_COUNT(e);
+    }
+    XB_TRY(get_plan(e, SITE_DOWN, l, e->act, I, w.wdown, T, D, I, e->gemm_out, D, nullptr, 0, &gp));
+    XB_TRY(xb_gemm_run(*gp, st));
+    LAUNCH_COUNT(e);
+    const bf16* next_norm = (l + 1 < e->nl) ? e->L[l + 1].sa_norm : (last ? e->final_norm : nullptr);
+    XB_TRY(launch_resid_norm(e, gp, T, next_norm, st));
+    if (taps != nullptr && taps[l] != nullptr)
+      XB_CUDA(cudaMemcpyAsync(taps[l], e->h, (size_t)T * D * 2, cudaMemcpyDeviceToDevice, st));
+  }
+
+  if (last) {
+    // final norm was fused above; LM head on the last position of each sequence only
+    xb_gather_rows_kernel<<<b->n_seqs, 256, 0, st>>>(e->hn, e->d_seq_last, e->last_rows, D);
+    XB_CUDA(cudaGetLastError());
+    LAUNCH_COUNT(e);
+    const bf16* head = d.tied_head ? e->embed : e->lm_head;
+    XB_CHECK(b->n_seqs <= 128, "LM head path supports up to 128 sequences per call");
+    // `out` is caller memory: plan per (n_seqs, out pointer)
+    GemmPlan p;
+    XB_TRY(xb_gemm_plan(&p, e->last_rows, D, head, b->n_seqs, d.vocab, D, out, d.vocab, nullptr, 1, e->num_sms, 1));
+    XB_TRY(xb_gemm_run(p, st));
+    LAUNCH_COUNT(e);
+  } else {
+    XB_CUDA(cudaMemcpyAsync(out, e->h, (size_t)T * D * 2, cudaMemcpyDeviceToDevice, st));
+  }
+  e->c.forwards++;
+  return 0;
+}
+
+// ----------------------------------------------------------------------------- sampling
+extern "C" int xb_sample(xb_engine* e, const float* logits, int n, float temp, int top_k, float top_p, const float* q,
+                         uint64_t seed, int32_t* tokens_out, void* stream) {
+  XB_CHECK(e != nullptr && logits != nullptr && tokens_out != nullptr && n > 0, "bad argument");
+  XB_CUDA(cudaSetDevice(e->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (temp <= 0.f) {
+    xb_argmax_kernel<1024><<<n, 1024, 0, st>>>(logits, e->d.vocab, tokens_out);
+  } else {
+    xb_sample_kernel<1024><<<n, 1024, 0, st>>>(logits, e->d.vocab, temp, top_k, top_p, q, (unsigned long long)seed, tokens_out);
+  }
+  XB_CUDA(cudaGetLastError());
+  LAUNCH_COUNT(e);
+  return 0;
+}
+
+extern "C" int xb_get_counters(xb_engine* e, xb_counters* out) {
+  XB_CHECK(e != nullptr && out != nullptr, "null argument");
+  *out = e->c;
+  return 0;
+}
+
+// ----------------------------------------------------------------------------- kernel-level test hook
+__global__ void xb_reduce_partials_kernel(const float* __restrict__ part, int splits, long long n, float* __restrict__ y,
+                                          int round_bf16) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float a = 0.f;
+  for (int s = 0; s < splits; ++s) a += part[s * n + i];
+  y[i] = round_bf16 ? rbf(a) : a;
+}
+__global__ void xb_bf16_to_f32_kernel(const bf16* __restrict__ x, long long n, float* __restrict__ y) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) y[i] = bf2f(x[i]);
+}
+
+extern "C" int xb_debug_linear(const void* x, const void* w, int T, int N, int K, float* y, float* scratch,
+                               int use_tensor_cores, int force_splits, int round_bf16, void* stream) {
+  XB_CHECK(x && w && y && scratch && T > 0 && N > 0 && K > 0, "bad argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  int dev = 0, sms = 148;
+  XB_CUDA(cudaGetDevice(&dev));
+  XB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  if (!use_tensor_cores) {
+    dim3 grid((N + 3) / 4, (T + 7) / 8);
+    xb_linear_check_kernel<<<grid, 128, 0, st>>>((const bf16*)x, (const bf16*)w, y, T, N, K);
+    XB_CUDA(cudaGetLastError());
+    return 0;
+  }
+  GemmPlan p;
+  XB_TRY(xb_gemm_plan(&p, (const bf16*)x, K, (const bf16*)w, T, N, K, scratch, N, nullptr, 0, sms, force_splits));
+  XB_TRY(xb_gemm_run(p, st));
+  const long long n = (long long)T * N;
+  const int blocks = (int)((n + 255) / 256);
+  if (p.args.mode == XB_GEMM_SKINNY)
+    xb_reduce_partials_kernel<<<blocks, 256, 0, st>>>(scratch, p.args.splits, n, y, round_bf16);
+  else
+    xb_bf16_to_f32_kernel<<<blocks, 256, 0, st>>>((const bf16*)scratch, n, y);
+  XB_CUDA(cudaGetLastError());
+  return 0;
+}

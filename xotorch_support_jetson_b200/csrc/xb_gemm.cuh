@@ -1,0 +1,371 @@
+// Linear layers of the layer-range forward as ONE warp-specialised tcgen05 kernel.
+//
+// Replaces the per-projection cuBLAS calls behind torchtune's nn.Linear modules that the
+// reference builds at xotorch/inference/torch/models/general_mha.py:83-102 (q/k/v/o) and
+// xotorch/inference/torch/models/llm_utils.py:513-522 (gate/up/down), and the LM head at
+// llm_utils.py:425-435.
+//
+//   D[128 x BN] (fp32, TMEM) += A[128 x 64] (bf16, smem) * B[BN x 64]^T (bf16, smem)
+//
+// Both operands are K-major and arrive by TMA into 128B-swizzled tiles; one elected thread
+// issues tcgen05.mma; four epilogue warps drain TMEM with tcgen05.ld.  The kernel is
+// persistent over work units (a_tile, b_tile, k_split) and double-buffers the accumulator
+// so the epilogue of unit i overlaps the mainloop of unit i+1.
+//
+// Two ways of mapping a Linear  y[T,N] = x[T,K] * W[N,K]^T  onto it:
+//   MODE_SKINNY  (decode, T <= 128): A = W tile (128 output features), B = x (all T tokens).
+//       HBM-bound weight streaming; K is split across CTAs so every SM pulls weights;
+//       output = fp32 partial sums  out[split][t][n]  reduced by the consumer kernel.
+//   MODE_WIDE    (prefill): A = x tile (128 tokens), B = W tile (BN features);
+//       tensor-bound; output = bf16  out[t][n] (+ bias, rounded once like nn.Linear).
+#pragma once
+#include "xb_common.cuh"
+
+enum { XB_GEMM_SKINNY = 0, XB_GEMM_WIDE = 1 };
+
+struct GemmArgs {
+  int a_tiles, b_tiles, k_blocks, splits;
+  int a_rows, b_rows;      // valid rows of the A / B global matrices
+  int mode;
+  int round_bf16;          // SKINNY: round the fp32 result to bf16 precision (splits == 1 only)
+  void* out;
+  long long ld_out;        // SKINNY: N (floats per token row); WIDE: elements per token row
+  const bf16* bias;        // WIDE: per-feature bias or nullptr
+};
+
+template <int BN, int STAGES>
+struct GemmCfg {
+  static constexpr int A_BYTES = 128 * 64 * 2;
+  static constexpr int B_BYTES = BN * 64 * 2;
+  static constexpr int ACC_STAGES = (2 * BN <= 512) ? 2 : 1;
+  static constexpr int TM_COLS_RAW = ACC_STAGES * BN;
+  static constexpr int TM_COLS = TM_COLS_RAW <= 32 ? 32 : TM_COLS_RAW <= 64 ? 64 : TM_COLS_RAW <= 128 ? 128 : TM_COLS_RAW <= 256 ? 256 : 512;
+  static constexpr int SMEM_BYTES = STAGES * (A_BYTES + B_BYTES) + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(192, 1)
+xb_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmArgs g) {
+  using Cfg = GemmCfg<BN, STAGES>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + STAGES * Cfg::A_BYTES;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(sB + STAGES * Cfg::B_BYTES);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tfull_bar = empty_bar + STAGES;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int i = 0; i < STAGES; ++i) {
+        mbar_init(&full_bar[i], 1);
+        mbar_init(&empty_bar[i], 1);
+      }
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&tfull_bar[i], 1);
+        mbar_init(&tempty_bar[i], 4);
+      }
+      fence_mbar_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, Cfg::TM_COLS);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int total_units = g.a_tiles * g.b_tiles * g.splits;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
+        const int s = u % g.splits;
+        const int tile = u / g.splits;
+        const int ta = tile % g.a_tiles;
+        const int tb = tile / g.a_tiles;
+        const int kb0 = (int)(((long long)s * g.k_blocks) / g.splits);
+        const int kb1 = (int)(((long long)(s + 1) * g.k_blocks) / g.splits);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_expect_tx(&full_bar[stage], Cfg::A_BYTES + Cfg::B_BYTES);
+          tma_load_2d(sA + stage * Cfg::A_BYTES, &tmA, &full_bar[stage], kb * 64, ta * 128);
+          tma_load_2d(sB + stage * Cfg::B_BYTES, &tmB, &full_bar[stage], kb * 64, tb * BN);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (one thread) =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BN);
+      int stage = 0, acc = 0;
+      uint32_t phase = 0, acc_phase = 0;
+      for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
+        const int s = u % g.splits;
+        const int kb0 = (int)(((long long)s * g.k_blocks) / g.splits);
+        const int kb1 = (int)(((long long)(s + 1) * g.k_blocks) / g.splits);
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);   // epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&full_bar[stage], phase);         // TMA bytes have landed
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(sA + stage * Cfg::A_BYTES);
+          const uint32_t b_addr = smem_u32(sB + stage * Cfg::B_BYTES);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {               // 4 x (K = 16) per 64-wide k-block
+            tc_mma_bf16(d_tmem, umma_desc_sw128(a_addr + k * 32), umma_desc_sw128(b_addr + k * 32), idesc,
+                        (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          tc_commit(&empty_bar[stage]);               // frees the smem slot when the MMAs retire
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        tc_commit(&tfull_bar[acc]);                   // accumulator complete -> epilogue
+        if (++acc == Cfg::ACC_STAGES) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else {
+    // ===================== epilogue warps 2..5: TMEM -> registers -> global =====================
+    const int quad = warp & 3;                        // TMEM lane quadrant this warp may read
+    const int row_in_tile = quad * 32 + lane;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
+      const int s = u % g.splits;
+      const int tile = u / g.splits;
+      const int ta = tile % g.a_tiles;
+      const int tb = tile / g.a_tiles;
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t t_addr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN);
+      const int arow = ta * 128 + row_in_tile;
+#pragma unroll 1
+      for (int c = 0; c < BN; c += 16) {
+        uint32_t v[16];
+        tmem_ld16(t_addr + c, v);
+        tmem_ld_wait();
+        if (g.mode == XB_GEMM_SKINNY) {
+          // arow = output feature n, column = token t; lanes write consecutive n (coalesced)
+          float* out = reinterpret_cast<float*>(g.out);
+          if (arow < g.a_rows) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const int t = tb * BN + c + j;
+              if (t < g.b_rows) {
+                float x = __uint_as_float(v[j]);
+                if (g.round_bf16) x = rbf(x);
+                out[((long long)s * g.b_rows + t) * g.ld_out + arow] = x;
+              }
+            }
+          }
+        } else {
+          // arow = token t, columns = 16 consecutive features
+          bf16* out = reinterpret_cast<bf16*>(g.out);
+          const int n0 = tb * BN + c;
+          if (arow < g.a_rows && n0 < g.b_rows) {
+            float x[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) x[j] = __uint_as_float(v[j]);
+            if (g.bias != nullptr) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j)
+                if (n0 + j < g.b_rows) x[j] += bf2f(g.bias[n0 + j]);
+            }
+            bf16* dst = out + (long long)arow * g.ld_out + n0;
+            if (n0 + 16 <= g.b_rows && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+              uint4 p0, p1;
+              p0.x = f2_to_bf2(x[0], x[1]);   p0.y = f2_to_bf2(x[2], x[3]);
+              p0.z = f2_to_bf2(x[4], x[5]);   p0.w = f2_to_bf2(x[6], x[7]);
+              p1.x = f2_to_bf2(x[8], x[9]);   p1.y = f2_to_bf2(x[10], x[11]);
+              p1.z = f2_to_bf2(x[12], x[13]); p1.w = f2_to_bf2(x[14], x[15]);
+              reinterpret_cast<uint4*>(dst)[0] = p0;
+              reinterpret_cast<uint4*>(dst)[1] = p1;
+            } else {
+              for (int j = 0; j < 16; ++j)
+                if (n0 + j < g.b_rows) dst[j] = f2bf(x[j]);
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+      if (++acc == Cfg::ACC_STAGES) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, Cfg::TM_COLS);
+  }
+}
+
+// ----------------------------------------------------------------------------- CUDA-core checker
+// Plain fp32-accumulate Linear used by the kernel-level tests (xb_debug_linear) to check the
+// tcgen05 path on the GPU itself.  out[t][n] = sum_k x[t][k] * w[n][k]; one warp per (n, 8 tokens).
+__global__ void xb_linear_check_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, float* __restrict__ out,
+                                       int T, int N, int K) {
+  const int n = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int t0 = blockIdx.y * 8;
+  const int lane = threadIdx.x & 31;
+  if (n >= N) return;
+  float acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+  for (int k = lane * 2; k < K; k += 64) {
+    const float2 wv = bf2_to_f2(*reinterpret_cast<const uint32_t*>(w + (long long)n * K + k));
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      if (t0 + i < T) {
+        const float2 xv = bf2_to_f2(*reinterpret_cast<const uint32_t*>(x + (long long)(t0 + i) * K + k));
+        acc[i] = fmaf(xv.x, wv.x, acc[i]);
+        acc[i] = fmaf(xv.y, wv.y, acc[i]);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float v = warp_sum(acc[i]);
+    if (lane == 0 && t0 + i < T) out[(long long)(t0 + i) * N + n] = v;
+  }
+}
+
+// ----------------------------------------------------------------------------- host side
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled xb_get_encode_fn() {
+  static PFN_encodeTiled fn = nullptr;
+  if (fn == nullptr) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_encodeTiled>(p);
+  }
+  return fn;
+}
+
+// 2-D bf16 row-major [rows, cols] tensor, box = [box_rows, 64 cols], 128B swizzle, zero fill out of bounds
+static int xb_make_tmap(CUtensorMap* m, const void* ptr, long long rows, long long cols, long long ld_elems, int box_rows) {
+  PFN_encodeTiled fn = xb_get_encode_fn();
+  XB_CHECK(fn != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
+  XB_CHECK((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (ld_elems * 2) % 16 == 0,
+           "TMA operand must be 16-byte aligned with a 16-byte multiple row pitch (ptr=%p ld=%lld)", ptr, ld_elems);
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)ld_elems * 2};
+  cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  XB_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (rows=%lld cols=%lld box_rows=%d)", (int)r,
+           rows, cols, box_rows);
+  return 0;
+}
+
+template <int BN, int STAGES>
+static int xb_gemm_launch_t(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, int grid, cudaStream_t st) {
+  using Cfg = GemmCfg<BN, STAGES>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    XB_CUDA(cudaFuncSetAttribute(xb_gemm_tcgen05_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 Cfg::SMEM_BYTES));
+    attr_set = true;
+  }
+  xb_gemm_tcgen05_kernel<BN, STAGES><<<grid, 192, Cfg::SMEM_BYTES, st>>>(tmA, tmB, g);
+  XB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// A planned Linear: tensor maps + unit decomposition, built once per (site, token count).
+struct GemmPlan {
+  CUtensorMap tmA, tmB;
+  GemmArgs args;
+  int bn;
+  int grid;
+};
+
+static int xb_pick_bn_skinny(int T) { return T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : 128; }
+
+// y[T,N] = x[T,K] W[N,K]^T.  T <= 128 -> SKINNY (fp32 partials [splits][T][N] into `out`);
+// otherwise WIDE (bf16 [T, ld_out] into `out`).
+static int xb_gemm_plan(GemmPlan* p, const bf16* x, long long ldx, const bf16* w, int T, int N, int K, void* out,
+                        long long ld_out, const bf16* bias, int round_bf16, int num_sms, int force_splits) {
+  XB_CHECK(K % 8 == 0, "K=%d must be a multiple of 8", K);
+  GemmArgs& g = p->args;
+  g.k_blocks = (K + 63) / 64;
+  g.out = out;
+  g.ld_out = ld_out;
+  g.bias = bias;
+  g.round_bf16 = round_bf16;
+  if (T <= 128) {
+    const int bn = xb_pick_bn_skinny(T);
+    p->bn = bn;
+    g.mode = XB_GEMM_SKINNY;
+    g.a_tiles = (N + 127) / 128;
+    g.b_tiles = 1;
+    g.a_rows = N;
+    g.b_rows = T;
+    int splits = force_splits;
+    if (splits <= 0) {
+      // enough units that every SM streams weights, bounded so the fp32 partials stay a
+      // small fraction (<~6%) of the weight bytes and every unit keeps >= 4 k-blocks
+      splits = (2 * num_sms + g.a_tiles - 1) / g.a_tiles;
+      int cap_traffic = (int)((0.03 * K) / (T > 0 ? T : 1));
+      if (cap_traffic < 1) cap_traffic = 1;
+      int cap_k = g.k_blocks / 4;
+      if (cap_k < 1) cap_k = 1;
+      if (splits > cap_traffic) splits = cap_traffic;
+      if (splits > cap_k) splits = cap_k;
+      if (splits > 16) splits = 16;
+      if (splits < 1) splits = 1;
+    }
+    if (round_bf16) splits = 1;
+    if (splits > g.k_blocks) splits = g.k_blocks;
+    g.splits = splits;
+    XB_TRY(xb_make_tmap(&p->tmA, w, N, K, K, 128));
+    XB_TRY(xb_make_tmap(&p->tmB, x, T, K, ldx, bn));
+  } else {
+    p->bn = 256;
+    g.mode = XB_GEMM_WIDE;
+    g.a_tiles = (T + 127) / 128;
+    g.b_tiles = (N + 255) / 256;
+    g.a_rows = T;
+    g.b_rows = N;
+    g.splits = 1;
+    XB_TRY(xb_make_tmap(&p->tmA, x, T, K, ldx, 128));
+    XB_TRY(xb_make_tmap(&p->tmB, w, N, K, K, 256));
+  }
+  const int units = g.a_tiles * g.b_tiles * g.splits;
+  const int per_sm = (p->bn <= 64) ? 2 : 1;   // smem allows two resident CTAs for the small-BN configs
+  p->grid = units < num_sms * per_sm ? units : num_sms * per_sm;
+  return 0;
+}
+
+static int xb_gemm_run(const GemmPlan& p, cudaStream_t st) {
+  switch (p.bn) {
+    case 16:  return xb_gemm_launch_t<16, 5>(p.tmA, p.tmB, p.args, p.grid, st);
+    case 32:  return xb_gemm_launch_t<32, 5>(p.tmA, p.tmB, p.args, p.grid, st);
+    case 64:  return xb_gemm_launch_t<64, 4>(p.tmA, p.tmB, p.args, p.grid, st);
+    case 128: return xb_gemm_launch_t<128, 6>(p.tmA, p.tmB, p.args, p.grid, st);
+    case 256: return xb_gemm_launch_t<256, 4>(p.tmA, p.tmB, p.args, p.grid, st);
+  }
+  return xb_fail(1, "unsupported BN %d", p.bn);
+}

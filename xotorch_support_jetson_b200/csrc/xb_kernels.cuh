@@ -1,0 +1,559 @@
+// Memory-bound kernels of the layer-range forward: embedding gather, fused
+// (split-K reduce +) residual + RMSNorm, QKV finalize (bias + RoPE + paged-KV append),
+// SiLU*up, split-KV attention over the paged cache, and on-device sampling.
+//
+// Every "rounding point" follows the reference's eager bf16 graph:
+// each nn.Linear output, RoPE output, attention output, residual sum, RMSNorm output,
+// SiLU output and the gate*up product are rounded to bf16 exactly once.
+#pragma once
+#include "xb_common.cuh"
+#include <math.h>
+
+// Per-forward metadata living in device memory at fixed addresses (so captured graphs can
+// be replayed after the host refreshes the contents).
+struct BatchMeta {
+  const int* tok_seq;     // [T]   sequence index of each token row
+  const int* tok_pos;     // [T]   absolute position of each token row
+  const int* seq_slot;    // [n_seqs] KV slot of each sequence
+  const int* seq_last;    // [n_seqs] row index of the last token of each sequence
+  const int* page_table;  // [n_slots, max_pages] page ids
+  int max_pages;
+  int page_tokens;
+};
+
+// ----------------------------------------------------------------------------- reductions
+template <int NT>
+__device__ __forceinline__ float block_sum(float v, float* red) {
+  v = warp_sum(v);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  __syncthreads();
+  if (l == 0) red[w] = v;
+  __syncthreads();
+  float t = (threadIdx.x < NT / 32) ? red[threadIdx.x] : 0.f;
+  if (w == 0) {
+    t = warp_sum(t);
+    if (l == 0) red[0] = t;
+  }
+  __syncthreads();
+  return red[0];
+}
+
+// torchtune RMSNorm (reference builds it at general_mha.py:116-117,130):
+//   x_normed = (x_fp32 * rsqrt(mean(x_fp32^2) + eps)).type_as(x);  out = x_normed * scale
+// two_round = 1 reproduces both bf16 roundings; 0 = F.rms_norm-style single rounding.
+__device__ __forceinline__ float rms_apply(float x, float inv, float w, int two_round) {
+  return two_round ? rbf(rbf(x * inv) * w) : rbf(x * inv * w);
+}
+
+// ----------------------------------------------------------------------------- embed + norm
+// h[t] = tok_embeddings[token[t]] (llm_utils.py:399-400); hn[t] = sa_norm(h[t]).
+template <int NT>
+__global__ void __launch_bounds__(NT) xb_embed_norm_kernel(const int* __restrict__ tokens, const bf16* __restrict__ emb,
+                                                           const bf16* __restrict__ nw, bf16* __restrict__ h,
+                                                           bf16* __restrict__ hn, int D, int V, float eps, int two_round) {
+  __shared__ float red[32];
+  const int t = blockIdx.x;
+  int tok = tokens[t];
+  tok = tok < 0 ? 0 : (tok >= V ? V - 1 : tok);
+  const bf16* src = emb + (long long)tok * D;
+  float ss = 0.f;
+  for (int i = threadIdx.x * 2; i < D; i += NT * 2) {
+    const uint32_t u = *reinterpret_cast<const uint32_t*>(src + i);
+    *reinterpret_cast<uint32_t*>(h + (long long)t * D + i) = u;
+    const float2 f = bf2_to_f2(u);
+    ss += f.x * f.x + f.y * f.y;
+  }
+  ss = block_sum<NT>(ss, red);
+  const float inv = 1.0f / sqrtf(ss / (float)D + eps);
+  for (int i = threadIdx.x * 2; i < D; i += NT * 2) {
+    const float2 f = bf2_to_f2(*reinterpret_cast<const uint32_t*>(src + i));
+    const float2 w = bf2_to_f2(*reinterpret_cast<const uint32_t*>(nw + i));
+    *reinterpret_cast<uint32_t*>(hn + (long long)t * D + i) =
+        f2_to_bf2(rms_apply(f.x, inv, w.x, two_round), rms_apply(f.y, inv, w.y, two_round));
+  }
+}
+
+// ----------------------------------------------------------------------------- residual + norm
+// y   = Linear output: bf16(sum over splits of fp32 partials)   (SRC = 0)
+//       or an already-rounded bf16 tensor                         (SRC = 1)
+//       or absent (plain norm of h, stage input)                  (SRC = 2)
+// h   = bf16(h + y)            (TransformerSelfAttentionLayer residual)
+// hn  = RMSNorm(h) * nw        (the next consumer's norm; skipped when nw == nullptr)
+template <int NT, int SRC>
+__global__ void __launch_bounds__(NT) xb_resid_norm_kernel(const float* __restrict__ part, int splits, long long split_stride,
+                                                           const bf16* __restrict__ y, bf16* __restrict__ h,
+                                                           const bf16* __restrict__ nw, bf16* __restrict__ hn, int D,
+                                                           float eps, int two_round) {
+  __shared__ float red[32];
+  extern __shared__ float row[];  // D floats: the new residual row
+  const int t = blockIdx.x;
+  float ss = 0.f;
+  for (int i = threadIdx.x * 2; i < D; i += NT * 2) {
+    const long long o = (long long)t * D + i;
+    float2 hv = bf2_to_f2(*reinterpret_cast<const uint32_t*>(h + o));
+    if (SRC == 0) {
+      float a = 0.f, b = 0.f;
+      for (int s = 0; s < splits; ++s) {
+        const float2 p = *reinterpret_cast<const float2*>(part + s * split_stride + o);
+        a += p.x;
+        b += p.y;
+      }
+      hv.x = rbf(hv.x + rbf(a));
+      hv.y = rbf(hv.y + rbf(b));
+    } else if (SRC == 1) {
+      const float2 yv = bf2_to_f2(*reinterpret_cast<const uint32_t*>(y + o));
+      hv.x = rbf(hv.x + yv.x);
+      hv.y = rbf(hv.y + yv.y);
+    }
+    if (SRC != 2) *reinterpret_cast<uint32_t*>(h + o) = f2_to_bf2(hv.x, hv.y);
+    row[i] = hv.x;
+    row[i + 1] = hv.y;
+    ss += hv.x * hv.x + hv.y * hv.y;
+  }
+  if (nw == nullptr) return;
+  ss = block_sum<NT>(ss, red);
+  const float inv = 1.0f / sqrtf(ss / (float)D + eps);
+  for (int i = threadIdx.x * 2; i < D; i += NT * 2) {
+    const float2 w = bf2_to_f2(*reinterpret_cast<const uint32_t*>(nw + i));
+    *reinterpret_cast<uint32_t*>(hn + (long long)t * D + i) =
+        f2_to_bf2(rms_apply(row[i], inv, w.x, two_round), rms_apply(row[i + 1], inv, w.y, two_round));
+  }
+}
+
+// ----------------------------------------------------------------------------- QKV finalize
+// One block per (token, head) over the fused [q | k | v] projection output.
+//   value = bf16(sum_splits(partial) + bias)        (nn.Linear rounding; SRC = 0)
+//         = already-rounded bf16                    (SRC = 1, bias added in the GEMM epilogue)
+//   q,k heads: RoPE at the token's position, table = [pos][hd/2][cos,sin] fp32
+//     rope_kind 0: interleaved pairs (2i,2i+1), fp32 math, one rounding (Llama3ScaledRoPE /
+//                  RotaryPositionalEmbeddings as built at general_mha.py:35-40,58-63)
+//     rope_kind 1: half-split pairs (i,i+hd/2), every product and the sum rounded to bf16
+//                  (Qwen2RotaryPositionalEmbeddings, general_mha.py:47-51)
+//   q -> q_out[t][h*hd..]; k,v -> the paged cache (KVCache.update, llm_utils.py:320-345)
+template <int SRC>
+__global__ void xb_qkv_finalize_kernel(const float* __restrict__ part, int splits, long long split_stride,
+                                       const bf16* __restrict__ y, const bf16* __restrict__ bias,
+                                       const float* __restrict__ rope, bf16* __restrict__ q_out, bf16* __restrict__ k_pool,
+                                       bf16* __restrict__ v_pool, BatchMeta m, int H, int KV, int hd, int rope_kind) {
+  const int t = blockIdx.x;
+  const int head = blockIdx.y;              // [0,H) q heads, [H,H+KV) k heads, [H+KV,H+2KV) v heads
+  const int i = threadIdx.x;                // pair index, hd/2 threads
+  const int NQKV = (H + 2 * KV) * hd;
+  const int half = hd >> 1;
+  int e0, e1;
+  if (rope_kind == 0) { e0 = 2 * i; e1 = 2 * i + 1; } else { e0 = i; e1 = i + half; }
+  const long long base = (long long)t * NQKV + (long long)head * hd;
+  float x0, x1;
+  if (SRC == 0) {
+    float a = 0.f, b = 0.f;
+    for (int s = 0; s < splits; ++s) {
+      a += part[s * split_stride + base + e0];
+      b += part[s * split_stride + base + e1];
+    }
+    if (bias != nullptr) {
+      a += bf2f(bias[head * hd + e0]);
+      b += bf2f(bias[head * hd + e1]);
+    }
+    x0 = rbf(a);
+    x1 = rbf(b);
+  } else {
+    x0 = bf2f(y[base + e0]);
+    x1 = bf2f(y[base + e1]);
+  }
+  const int pos = m.tok_pos[t];
+  if (head < H + KV) {
+    const float2 cs = *reinterpret_cast<const float2*>(rope + ((long long)pos * half + i) * 2);
+    float o0, o1;
+    if (rope_kind == 0) {
+      o0 = rbf(__fsub_rn(__fmul_rn(x0, cs.x), __fmul_rn(x1, cs.y)));
+      o1 = rbf(__fadd_rn(__fmul_rn(x1, cs.x), __fmul_rn(x0, cs.y)));
+    } else {
+      const float c = rbf(cs.x), s = rbf(cs.y);
+      o0 = rbf(__fadd_rn(rbf(__fmul_rn(x0, c)), rbf(__fmul_rn(-x1, s))));
+      o1 = rbf(__fadd_rn(rbf(__fmul_rn(x1, c)), rbf(__fmul_rn(x0, s))));
+    }
+    x0 = o0;
+    x1 = o1;
+  }
+  if (head < H) {
+    bf16* dst = q_out + (long long)t * H * hd + (long long)head * hd;
+    dst[e0] = f2bf(x0);
+    dst[e1] = f2bf(x1);
+  } else {
+    const int slot = m.seq_slot[m.tok_seq[t]];
+    const int page = m.page_table[(long long)slot * m.max_pages + pos / m.page_tokens];
+    const int off = pos % m.page_tokens;
+    const int kvh = (head - H) % KV;
+    bf16* pool = (head < H + KV) ? k_pool : v_pool;
+    bf16* dst = pool + (((long long)page * KV + kvh) * m.page_tokens + off) * hd;
+    dst[e0] = f2bf(x0);
+    dst[e1] = f2bf(x1);
+  }
+}
+
+// ----------------------------------------------------------------------------- SiLU(gate) * up
+// FeedForward (llm_utils.py:513-522): w2(silu(w1 x) * w3 x); silu output and the product
+// are separate bf16 ops in the reference.  Input = fused [gate | up] projection.
+template <int SRC>
+__global__ void xb_silu_mul_kernel(const float* __restrict__ part, int splits, long long split_stride,
+                                   const bf16* __restrict__ y, bf16* __restrict__ act, int T, int I) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long long)T * I) return;
+  const int t = (int)(idx / I), i = (int)(idx % I);
+  const long long og = (long long)t * 2 * I + i, ou = og + I;
+  float g, u;
+  if (SRC == 0) {
+    g = 0.f; u = 0.f;
+    for (int s = 0; s < splits; ++s) {
+      g += part[s * split_stride + og];
+      u += part[s * split_stride + ou];
+    }
+    g = rbf(g);
+    u = rbf(u);
+  } else {
+    g = bf2f(y[og]);
+    u = bf2f(y[ou]);
+  }
+  const float sg = rbf(g / (1.0f + expf(-g)));
+  act[idx] = f2bf(sg * u);
+}
+
+// ----------------------------------------------------------------------------- attention over the paged cache
+// One block per (token row, kv head, kv split).  The G = H/KV query heads that share the
+// kv head are processed together so K and V are read once per group (the reference
+// materialises the expanded [B,H,C,hd] copies instead).  Keys [0, pos] are
+// attended (causal); masked/unfilled cache slots of the reference contribute exp(-inf)=0.
+// 16 lanes x 8 dims cover one 128-wide row with one 128-bit load per lane; a warp walks
+// two keys per step.  fp32 online softmax; partial (m, l, acc) per split.
+template <int HD, int G>
+__global__ void __launch_bounds__(128) xb_attn_split_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pool,
+                                                            const bf16* __restrict__ v_pool, BatchMeta m,
+                                                            float* __restrict__ o_part, float* __restrict__ ml_part,
+                                                            bf16* __restrict__ out, int H, int KV, int n_splits,
+                                                            float scale) {
+  constexpr int LPK = HD / 8;            // lanes per key row (16 for hd=128, 8 for hd=64)
+  constexpr int KPW = 32 / LPK;          // keys per warp step
+  const int t = blockIdx.x, kvh = blockIdx.y, sp = blockIdx.z;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int sub = lane / LPK;            // which key of the step
+  const int dl = lane % LPK;             // which 8-dim slice
+  const int pos = m.tok_pos[t];
+  const int ctx = pos + 1;
+  const int slot = m.seq_slot[m.tok_seq[t]];
+  const int* pt = m.page_table + (long long)slot * m.max_pages;
+  const int P = m.page_tokens;
+  // split the context in chunks of whole pages
+  const int n_pages = (ctx + P - 1) / P;
+  const int pg0 = (int)(((long long)sp * n_pages) / n_splits);
+  const int pg1 = (int)(((long long)(sp + 1) * n_pages) / n_splits);
+  const int k_begin = pg0 * P;
+  const int k_end = min(pg1 * P, ctx);
+
+  float qf[G][8];
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    const uint4 u = *reinterpret_cast<const uint4*>(q + ((long long)t * H + (kvh * G + g)) * HD + dl * 8);
+    float2 a = bf2_to_f2(u.x), b = bf2_to_f2(u.y), c = bf2_to_f2(u.z), d = bf2_to_f2(u.w);
+    qf[g][0] = a.x; qf[g][1] = a.y; qf[g][2] = b.x; qf[g][3] = b.y;
+    qf[g][4] = c.x; qf[g][5] = c.y; qf[g][6] = d.x; qf[g][7] = d.y;
+  }
+  float mx[G], l[G], acc[G][8];
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    mx[g] = -INFINITY;
+    l[g] = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[g][j] = 0.f;
+  }
+
+  for (int kb = k_begin + warp * KPW; kb < k_end; kb += 4 * KPW) {
+    const int key = kb + sub;
+    const bool valid = key < k_end;
+    uint4 ku = make_uint4(0, 0, 0, 0), vu = make_uint4(0, 0, 0, 0);
+    if (valid) {
+      const int page = pt[key / P];
+      const long long off = (((long long)page * KV + kvh) * P + (key % P)) * HD + dl * 8;
+      ku = ld_nc_v4(k_pool + off);
+      vu = ld_nc_v4(v_pool + off);
+    }
+    float kf[8], vf[8];
+    {
+      float2 a = bf2_to_f2(ku.x), b = bf2_to_f2(ku.y), c = bf2_to_f2(ku.z), d = bf2_to_f2(ku.w);
+      kf[0] = a.x; kf[1] = a.y; kf[2] = b.x; kf[3] = b.y; kf[4] = c.x; kf[5] = c.y; kf[6] = d.x; kf[7] = d.y;
+      a = bf2_to_f2(vu.x); b = bf2_to_f2(vu.y); c = bf2_to_f2(vu.z); d = bf2_to_f2(vu.w);
+      vf[0] = a.x; vf[1] = a.y; vf[2] = b.x; vf[3] = b.y; vf[4] = c.x; vf[5] = c.y; vf[6] = d.x; vf[7] = d.y;
+    }
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      float s = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s = fmaf(qf[g][j], kf[j], s);
+#pragma unroll
+      for (int o = LPK / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+      s = valid ? s * scale : -INFINITY;
+      const float mn = fmaxf(mx[g], s);
+      if (mn > -INFINITY) {
+        const float corr = __expf(mx[g] - mn);
+        const float p = __expf(s - mn);
+        l[g] = l[g] * corr + p;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[g][j] = fmaf(p, vf[j], acc[g][j] * corr);
+        mx[g] = mn;
+      }
+    }
+  }
+
+  // merge the KPW key lanes of each warp, then the 4 warps, through shared memory
+  __shared__ float s_m[4 * KPW][G];
+  __shared__ float s_l[4 * KPW][G];
+  __shared__ float s_acc[4 * KPW][G][HD];
+  const int part = warp * KPW + sub;
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    if (dl == 0) { s_m[part][g] = mx[g]; s_l[part][g] = l[g]; }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s_acc[part][g][dl * 8 + j] = acc[g][j];
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < G * HD; idx += 128) {
+    const int g = idx / HD, d = idx % HD;
+    float M = -INFINITY;
+#pragma unroll
+    for (int p = 0; p < 4 * KPW; ++p) M = fmaxf(M, s_m[p][g]);
+    float L = 0.f, A = 0.f;
+    if (M > -INFINITY) {
+#pragma unroll
+      for (int p = 0; p < 4 * KPW; ++p) {
+        const float w = __expf(s_m[p][g] - M);
+        L += s_l[p][g] * w;
+        A += s_acc[p][g][d] * w;
+      }
+    }
+    const int h = kvh * G + g;
+    if (n_splits == 1) {
+      out[((long long)t * H + h) * HD + d] = f2bf(L > 0.f ? A / L : 0.f);
+    } else {
+      const long long o = ((long long)t * H + h) * n_splits + sp;
+      o_part[o * HD + d] = A;
+      if (d == 0) { ml_part[o * 2] = M; ml_part[o * 2 + 1] = L; }
+    }
+  }
+}
+
+// merge the kv splits of one (token, head): out = sum_s e^{m_s-M} acc_s / sum_s e^{m_s-M} l_s
+__global__ void xb_attn_combine_kernel(const float* __restrict__ o_part, const float* __restrict__ ml_part,
+                                       bf16* __restrict__ out, int n_splits, int hd) {
+  const long long th = blockIdx.x;  // t*H + h
+  const int d = threadIdx.x;
+  float M = -INFINITY;
+  for (int s = 0; s < n_splits; ++s) M = fmaxf(M, ml_part[(th * n_splits + s) * 2]);
+  float L = 0.f, A = 0.f;
+  for (int s = 0; s < n_splits; ++s) {
+    const float ms = ml_part[(th * n_splits + s) * 2];
+    if (ms > -INFINITY) {
+      const float w = __expf(ms - M);
+      L += ml_part[(th * n_splits + s) * 2 + 1] * w;
+      A += o_part[(th * n_splits + s) * hd + d] * w;
+    }
+  }
+  out[th * hd + d] = f2bf(L > 0.f ? A / L : 0.f);
+}
+
+// ----------------------------------------------------------------------------- misc
+// rows[i] = src[idx[i]]  (last-position gather before the LM head: the reference runs the
+// head on all s positions and slices [:, -1], sharded_inference_engine.py:366)
+__global__ void xb_gather_rows_kernel(const bf16* __restrict__ src, const int* __restrict__ idx, bf16* __restrict__ dst, int D) {
+  const int r = blockIdx.x;
+  const bf16* s = src + (long long)idx[r] * D;
+  for (int i = threadIdx.x * 2; i < D; i += blockDim.x * 2)
+    *reinterpret_cast<uint32_t*>(dst + (long long)r * D + i) = *reinterpret_cast<const uint32_t*>(s + i);
+}
+
+// ----------------------------------------------------------------------------- sampling
+// Restates torchtune.generation.sample as the reference calls it
+// (sharded_inference_engine.py:208-228): logits / max(temp, 1e-5); values below the
+// k-th largest -> -inf; softmax; argmax(probs / q), q ~ Exp(1).
+__device__ __forceinline__ uint32_t float_order_key(float f) {
+  const uint32_t u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);   // monotone: larger float -> larger key
+}
+__device__ __forceinline__ float key_to_float(uint32_t k) {
+  const uint32_t u = (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k;
+  return __uint_as_float(u);
+}
+__device__ __forceinline__ uint32_t mix32(uint64_t x) {
+  x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33;
+  return (uint32_t)(x >> 11);
+}
+
+// first-index argmax of each row (greedy): one block per row
+template <int NT>
+__global__ void __launch_bounds__(NT) xb_argmax_kernel(const float* __restrict__ logits, int V, int* __restrict__ out) {
+  __shared__ float sv[NT / 32];
+  __shared__ int si[NT / 32];
+  const float* row = logits + (long long)blockIdx.x * V;
+  float best = -INFINITY;
+  int bi = 0x7fffffff;
+  for (int i = threadIdx.x; i < V; i += NT) {
+    const float v = row[i];
+    if (v > best || (v == best && i < bi)) { best = v; bi = i; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+  }
+  if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = best; si[threadIdx.x >> 5] = bi; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < NT / 32; ++w)
+      if (sv[w] > best || (sv[w] == best && si[w] < bi)) { best = sv[w]; bi = si[w]; }
+    out[blockIdx.x] = bi == 0x7fffffff ? 0 : bi;
+  }
+}
+
+// temperature / top-k / top-p sampling: one block per row.
+//  1. radix-select (4 passes of 8 bits over order-preserving keys) the k-th largest scaled logit
+//  2. softmax over the kept set; optional nucleus cut: keep the smallest set of largest
+//     probabilities whose mass reaches top_p (second radix descent, on mass instead of count)
+//  3. argmax(p / q), q = caller-supplied Exp(1) noise (reference-exact) or counter-hash noise
+template <int NT>
+__global__ void __launch_bounds__(NT) xb_sample_kernel(const float* __restrict__ logits, int V, float temp, int top_k,
+                                                       float top_p, const float* __restrict__ q_noise,
+                                                       unsigned long long seed, int* __restrict__ out) {
+  __shared__ unsigned int hist[256];
+  __shared__ float fhist[256];
+  __shared__ uint32_t s_prefix;
+  __shared__ int s_need;
+  __shared__ float s_needf;
+  __shared__ float red[32];
+  __shared__ float sv[NT / 32];
+  __shared__ int si[NT / 32];
+  const int rowi = blockIdx.x;
+  const float* row = logits + (long long)rowi * V;
+  const float inv_t = 1.0f / fmaxf(temp, 1e-5f);
+
+  // ---- 1. pivot = k-th largest scaled logit
+  uint32_t pivot_key = 0;
+  if (top_k > 0 && top_k < V) {
+    uint32_t prefix = 0;
+    int need = top_k;
+    for (int pass = 0; pass < 4; ++pass) {
+      const int shift = 24 - 8 * pass;
+      for (int i = threadIdx.x; i < 256; i += NT) hist[i] = 0;
+      __syncthreads();
+      const uint32_t mask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
+      for (int i = threadIdx.x; i < V; i += NT) {
+        const uint32_t key = float_order_key(row[i] * inv_t);
+        if ((key & mask) == (prefix & mask)) atomicAdd(&hist[(key >> shift) & 255], 1u);
+      }
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        int n = need;
+        int b = 255;
+        for (; b > 0; --b) {
+          if ((int)hist[b] >= n) break;
+          n -= (int)hist[b];
+        }
+        s_prefix = prefix | ((uint32_t)b << shift);
+        s_need = n;
+      }
+      __syncthreads();
+      prefix = s_prefix;
+      need = s_need;
+      __syncthreads();
+    }
+    pivot_key = prefix;
+  }
+  const float pivot = (top_k > 0 && top_k < V) ? key_to_float(pivot_key) : -INFINITY;
+
+  // ---- 2. softmax statistics over kept values (logits >= pivot)
+  float mxv = -INFINITY;
+  for (int i = threadIdx.x; i < V; i += NT) {
+    const float v = row[i] * inv_t;
+    if (v >= pivot) mxv = fmaxf(mxv, v);
+  }
+  mxv = warp_max(mxv);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = mxv;
+  __syncthreads();
+  mxv = red[0];
+  for (int w = 1; w < NT / 32; ++w) mxv = fmaxf(mxv, red[w]);
+  __syncthreads();
+  float sum = 0.f;
+  for (int i = threadIdx.x; i < V; i += NT) {
+    const float v = row[i] * inv_t;
+    if (v >= pivot) sum += expf(v - mxv);
+  }
+  sum = block_sum<NT>(sum, red);
+
+  // ---- 2b. nucleus: largest probability threshold whose upper set has mass >= top_p
+  float p_cut = 0.f;
+  if (top_p > 0.f && top_p < 1.f) {
+    uint32_t prefix = 0;
+    float needf = top_p * sum;   // in un-normalised mass
+    for (int pass = 0; pass < 4; ++pass) {
+      const int shift = 24 - 8 * pass;
+      for (int i = threadIdx.x; i < 256; i += NT) fhist[i] = 0.f;
+      __syncthreads();
+      const uint32_t mask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
+      for (int i = threadIdx.x; i < V; i += NT) {
+        const float v = row[i] * inv_t;
+        if (v >= pivot) {
+          const float e = expf(v - mxv);
+          const uint32_t key = float_order_key(e);
+          if ((key & mask) == (prefix & mask)) atomicAdd(&fhist[(key >> shift) & 255], e);
+        }
+      }
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        float n = needf;
+        int b = 255;
+        for (; b > 0; --b) {
+          if (fhist[b] >= n) break;
+          n -= fhist[b];
+        }
+        s_prefix = prefix | ((uint32_t)b << shift);
+        s_needf = n;
+      }
+      __syncthreads();
+      prefix = s_prefix;
+      needf = s_needf;
+      __syncthreads();
+    }
+    p_cut = key_to_float(prefix);
+  }
+
+  // ---- 3. argmax(p / q)
+  float best = -INFINITY;
+  int bi = 0x7fffffff;
+  for (int i = threadIdx.x; i < V; i += NT) {
+    const float v = row[i] * inv_t;
+    if (v < pivot) continue;
+    const float e = expf(v - mxv);
+    if (e < p_cut) continue;
+    float qv;
+    if (q_noise != nullptr) {
+      qv = q_noise[(long long)rowi * V + i];
+    } else {
+      const uint32_t r = mix32(seed * 0x9E3779B97F4A7C15ULL + ((unsigned long long)rowi << 32) + (unsigned)i);
+      const float u = ((float)(r & 0xffffff) + 0.5f) * (1.0f / 16777216.0f);
+      qv = -logf(u);
+    }
+    const float sc = (e / sum) / qv;
+    if (sc > best || (sc == best && i < bi)) { best = sc; bi = i; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+  }
+  if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = best; si[threadIdx.x >> 5] = bi; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < NT / 32; ++w)
+      if (sv[w] > best || (sv[w] == best && si[w] < bi)) { best = sv[w]; bi = si[w]; }
+    out[rowi] = bi == 0x7fffffff ? 0 : bi;
+  }
+}

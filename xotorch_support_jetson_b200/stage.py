@@ -1,0 +1,222 @@
+"""One pipeline stage = one layer range of one model on one B200, over the C ABI.
+
+``StageRuntime`` is the synchronous, device-tensor level under the async
+``B200ShardInferenceEngine``: it owns the native engine handle, loads the shard's
+weights (the work of ``load_model_weights_torchtune``,
+``xotorch/inference/torch/models/llm_utils.py:136-284`` -- here only the tensors of
+the layer range are read from the safetensors files), and runs forward / sample calls
+on torch CUDA tensors without any numpy round trip.
+"""
+import ctypes as C
+import json
+from pathlib import Path
+from typing import Dict, List, Optional, Sequence
+
+import torch
+
+from . import _cabi
+from .model_config import has_qkv_bias, load_model_config, model_family, rope_table, uses_tied_head
+from .shard import Shard
+
+
+def _permute(t: torch.Tensor, n_heads: int, head_dim: int, dim: int) -> torch.Tensor:
+  """HF half-split q/k rows -> torchtune interleaved rows (reference llm_utils.py:126-134)."""
+  return t.view(n_heads, 2, head_dim // 2, dim).transpose(1, 2).reshape(head_dim * n_heads, dim)
+
+
+class _SafetensorsIndex:
+  """name -> file lookup over every ``*.safetensors`` in a directory, reading lazily."""
+
+  def __init__(self, path: Path):
+    from safetensors import safe_open
+    self.files = sorted(Path(path).glob("*.safetensors"))
+    if not self.files:
+      raise FileNotFoundError(f"No safetensors files found in {path}")
+    self._open = safe_open
+    self.where: Dict[str, Path] = {}
+    for f in self.files:
+      with safe_open(str(f), framework="pt") as h:
+        for k in h.keys():
+          self.where[k] = f
+    self._handles = {}
+
+  def has(self, name: str) -> bool:
+    return name in self.where
+
+  def get(self, name: str) -> torch.Tensor:
+    f = self.where[name]
+    h = self._handles.get(f)
+    if h is None:
+      h = self._open(str(f), framework="pt")
+      self._handles[f] = h
+    return h.get_tensor(name)
+
+
+class StageRuntime:
+  def __init__(self, shard: Shard, config: dict, device: int = 0, max_batch_tokens: int = 4096,
+               max_seqs: int = 32, max_tokens_per_seq: int = 4096, page_tokens: int = 64,
+               rope_table_bf16: bool = True, rmsnorm_two_round: bool = True, max_positions: Optional[int] = None):
+    if not torch.cuda.is_available():
+      raise RuntimeError("B200 engine needs a CUDA device: there is no CPU fallback")
+    self.lib = _cabi.load()
+    self.shard = shard
+    self.config = config
+    self.device = torch.device("cuda", device)
+    self.family = model_family(shard.model_id)
+    self.tied = uses_tied_head(shard.model_id)
+    self.qkv_bias = has_qkv_bias(shard.model_id, config)
+    self.max_seqs = max_seqs
+    self.max_batch_tokens = max_batch_tokens
+    self.max_tokens_per_seq = max_tokens_per_seq
+    if max_positions is None:
+      max_positions = min(config["max_seq_len"], max(max_tokens_per_seq, 8))
+    self.max_positions = max_positions
+    d = _cabi.ModelDesc(
+      n_layers=shard.n_layers, start_layer=shard.start_layer, end_layer=shard.end_layer,
+      dim=config["embed_dim"], n_heads=config["num_heads"], n_kv_heads=config["num_kv_heads"],
+      head_dim=config["head_dim"], inter_dim=config["intermediate_dim"], vocab=config["vocab_size"],
+      norm_eps=config["norm_eps"],
+      rope_kind=_cabi.ROPE_HALF_SPLIT if self.family == "qwen" else _cabi.ROPE_INTERLEAVED,
+      rmsnorm_two_round=int(rmsnorm_two_round), qkv_bias=int(self.qkv_bias), tied_head=int(self.tied),
+      max_positions=max_positions, max_batch_tokens=max_batch_tokens, max_seqs=max_seqs)
+    self.desc = d
+    self._h = C.c_void_p()
+    _cabi.check(self.lib.xb_engine_create(C.byref(d), device, C.byref(self._h)))
+    tab = rope_table(self.family, config, max_positions, bf16_rounded=rope_table_bf16)
+    self._load(-1, _cabi.W_ROPE_TABLE, tab)
+    _cabi.check(self.lib.xb_kv_reserve(self._h, max_seqs, max_tokens_per_seq, page_tokens))
+    self.page_tokens = page_tokens
+    self.dim = config["embed_dim"]
+    self.vocab = config["vocab_size"]
+
+  # -- lifetime
+  def close(self):
+    if getattr(self, "_h", None) is not None and self._h.value:
+      self.lib.xb_engine_destroy(self._h)
+      self._h = C.c_void_p()
+
+  def __del__(self):
+    try:
+      self.close()
+    except Exception:
+      pass
+
+  # -- weights
+  def _load(self, layer: int, kind: int, t: torch.Tensor):
+    t = t.contiguous()
+    if kind != _cabi.W_ROPE_TABLE:
+      t = t.to(torch.bfloat16)
+    _cabi.check(self.lib.xb_load_weight(self._h, layer, kind, C.c_void_p(t.data_ptr()), t.numel() * t.element_size()))
+
+  def load_hf_tensors(self, get, has):
+    """Feed HF-named tensors (callable ``get(name)``) for this shard's layer range."""
+    cfg, sh = self.config, self.shard
+    H, KV, hd, D = cfg["num_heads"], cfg["num_kv_heads"], cfg["head_dim"], cfg["embed_dim"]
+    llama = self.family == "llama"
+    for l in range(sh.start_layer, sh.end_layer + 1):
+      p = f"model.layers.{l}."
+      q, k = get(p + "self_attn.q_proj.weight"), get(p + "self_attn.k_proj.weight")
+      if llama:  # reference permutes q/k for Llama only (llm_utils.py:213-231)
+        q, k = _permute(q, H, hd, D), _permute(k, KV, hd, D)
+      self._load(l, _cabi.W_Q, q)
+      self._load(l, _cabi.W_K, k)
+      self._load(l, _cabi.W_V, get(p + "self_attn.v_proj.weight"))
+      self._load(l, _cabi.W_O, get(p + "self_attn.o_proj.weight"))
+      self._load(l, _cabi.W_GATE, get(p + "mlp.gate_proj.weight"))
+      self._load(l, _cabi.W_UP, get(p + "mlp.up_proj.weight"))
+      self._load(l, _cabi.W_DOWN, get(p + "mlp.down_proj.weight"))
+      self._load(l, _cabi.W_SA_NORM, get(p + "input_layernorm.weight"))
+      self._load(l, _cabi.W_MLP_NORM, get(p + "post_attention_layernorm.weight"))
+      if self.qkv_bias:
+        for nm, kind in (("q_proj", _cabi.W_Q_BIAS), ("k_proj", _cabi.W_K_BIAS), ("v_proj", _cabi.W_V_BIAS)):
+          if has(p + f"self_attn.{nm}.bias"):
+            self._load(l, kind, get(p + f"self_attn.{nm}.bias"))
+    if sh.is_first_layer() or (sh.is_last_layer() and self.tied):
+      self._load(-1, _cabi.W_EMBED, get("model.embed_tokens.weight"))
+    if sh.is_last_layer():
+      self._load(-1, _cabi.W_FINAL_NORM, get("model.norm.weight"))
+      if not self.tied:
+        self._load(-1, _cabi.W_LM_HEAD, get("lm_head.weight"))
+
+  def load_dir(self, path: Path):
+    idx = _SafetensorsIndex(path)
+    self.load_hf_tensors(idx.get, idx.has)
+
+  def load_state(self, state: Dict[str, torch.Tensor]):
+    self.load_hf_tensors(state.__getitem__, state.__contains__)
+
+  # -- compute
+  def forward(self, slot_ids: Sequence[int], q_lens: Sequence[int], positions: Sequence[int],
+              tokens: Optional[torch.Tensor] = None, hidden: Optional[torch.Tensor] = None,
+              out: Optional[torch.Tensor] = None, taps: Optional[List[torch.Tensor]] = None) -> torch.Tensor:
+    """tokens: int32 [T] (first shard) / hidden: bf16 [T, D].  Returns bf16 [T, D] hidden
+    or fp32 [n_seqs, V] logits (last shard).  Enqueued on the current torch stream."""
+    n = len(slot_ids)
+    T = int(sum(q_lens))
+    arr = (C.c_int32 * n)
+    b = _cabi.Batch(n_seqs=n, slot_ids=arr(*slot_ids), q_lens=arr(*q_lens), positions=arr(*positions),
+                    tokens=None, hidden_in=None)
+    if tokens is not None:
+      assert tokens.dtype == torch.int32 and tokens.is_cuda and tokens.numel() == T
+      b.tokens = tokens.data_ptr()
+    if hidden is not None:
+      assert hidden.dtype == torch.bfloat16 and hidden.is_cuda and hidden.numel() == T * self.dim and hidden.is_contiguous()
+      b.hidden_in = hidden.data_ptr()
+    if out is None:
+      if self.shard.is_last_layer():
+        out = torch.empty((n, self.vocab), dtype=torch.float32, device=self.device)
+      else:
+        out = torch.empty((T, self.dim), dtype=torch.bfloat16, device=self.device)
+    tap_ptrs = None
+    if taps is not None:
+      tap_ptrs = (C.c_void_p * len(taps))(*[t.data_ptr() for t in taps])
+    stream = torch.cuda.current_stream(self.device).cuda_stream
+    _cabi.check(self.lib.xb_forward(self._h, C.byref(b), C.c_void_p(out.data_ptr()), tap_ptrs, C.c_void_p(stream)))
+    return out
+
+  def sample(self, logits: torch.Tensor, temp: float = 0.0, top_k: int = 0, top_p: float = 0.0,
+             q: Optional[torch.Tensor] = None, seed: int = 0, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    assert logits.dtype == torch.float32 and logits.is_cuda and logits.is_contiguous()
+    n = logits.shape[0]
+    if out is None:
+      out = torch.empty((n,), dtype=torch.int32, device=self.device)
+    stream = torch.cuda.current_stream(self.device).cuda_stream
+    _cabi.check(self.lib.xb_sample(self._h, C.c_void_p(logits.data_ptr()), n, float(temp), int(top_k), float(top_p),
+                                   C.c_void_p(q.data_ptr()) if q is not None else None, int(seed),
+                                   C.c_void_p(out.data_ptr()), C.c_void_p(stream)))
+    return out
+
+  def release_slot(self, slot: int):
+    _cabi.check(self.lib.xb_kv_release_slot(self._h, slot))
+
+  def slot_len(self, slot: int) -> int:
+    v = C.c_int()
+    _cabi.check(self.lib.xb_kv_slot_len(self._h, slot, C.byref(v)))
+    return v.value
+
+  def counters(self) -> dict:
+    c = _cabi.Counters()
+    _cabi.check(self.lib.xb_get_counters(self._h, C.byref(c)))
+    return {k: int(getattr(c, k)) for k, _ in c._fields_}
+
+
+def stage_from_dir(path: Path, shard: Shard, **kw) -> StageRuntime:
+  cfg = load_model_config(Path(path) / "config.json")
+  st = StageRuntime(shard, cfg, **kw)
+  st.load_dir(Path(path))
+  return st
+
+
+def debug_linear(x: torch.Tensor, w: torch.Tensor, use_tensor_cores: bool = True, force_splits: int = 0,
+                 round_bf16: bool = False) -> torch.Tensor:
+  """Kernel-level hook (xb_debug_linear): fp32 [T, N] = x[T, K] @ w[N, K]^T."""
+  lib = _cabi.load()
+  T, K = x.shape
+  N = w.shape[0]
+  y = torch.empty((T, N), dtype=torch.float32, device=x.device)
+  scratch = torch.empty((16 * T * N,), dtype=torch.float32, device=x.device)
+  stream = torch.cuda.current_stream(x.device).cuda_stream
+  _cabi.check(lib.xb_debug_linear(C.c_void_p(x.data_ptr()), C.c_void_p(w.data_ptr()), T, N, K, C.c_void_p(y.data_ptr()),
+                                  C.c_void_p(scratch.data_ptr()), int(use_tensor_cores), int(force_splits), int(round_bf16),
+                                  C.c_void_p(stream)))
+  return y
