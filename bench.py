@@ -1,0 +1,441 @@
+#!/usr/bin/env python
+"""bench.py -- decode / prefill throughput of the layer-range forward on B200.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+
+Workload (BASELINE.json configs[2], the one the metric is quoted on): Llama-3.1-8B bf16,
+random-init weights, synthetic 2048-token prompts, decode at context 2048.., batch 32 per
+pipeline micro-batch.  A "step" is one decode step of every in-flight sequence.  At N GPUs
+the model is an N-stage layer pipeline (the ranges the reference's ring strategy assigns)
+with N micro-batches of 32 sequences in flight: per-GPU work is fixed -> "weak" scaling.
+
+One JSON line on stdout (rank 0).  `value` = decode tokens/s with ids resident in HBM;
+`e2e` = the same metric through the public API with host buffers; `roofline` = the
+dominant kernel (tcgen05 weight-streaming Linear) against the measured HBM peak;
+`cpu_baseline` = the oracle (reference-equivalent eager PyTorch) on the host cores;
+`extra` carries decode bs=1 and prefill tok/s with their roofline fractions.
+
+`--impl reference` times the reference's own CPU path (the oracle port -- torchtune is not
+installable here) on the same config with a bounded per-step sample.
+"""
+import argparse
+import asyncio
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+MODEL = "llama-3.1-8b"
+PROMPT_LEN = 2048
+BATCH = 32
+
+
+def measured_peaks():
+  p = ROOT / "MEASURED_PEAKS.json"
+  if p.exists():
+    d = json.loads(p.read_text())
+    return {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d["bf16_tflops"], "bf16_tflops_sustained": d["bf16_tflops_sustained"],
+            "source": "measured"}
+  return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+
+
+class ClockSampler:
+  """nvidia-smi clocks / throttle reasons during the timed region."""
+  Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+       "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+  def __init__(self, gpu_index: int):
+    self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+    self.p = None
+    self.idx = gpu_index
+
+  def start(self):
+    try:
+      self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                                 "-i", str(self.idx)], stdout=self.f, stderr=subprocess.DEVNULL)
+    except Exception:
+      self.p = None
+
+  def stop(self) -> dict:
+    if self.p is None:
+      return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+    time.sleep(0.25)
+    self.p.terminate()
+    try:
+      self.p.wait(timeout=5)
+    except Exception:
+      self.p.kill()
+    self.f.flush()
+    rows = [r.split(",") for r in Path(self.f.name).read_text().strip().splitlines() if r.strip()]
+    os.unlink(self.f.name)
+    sm, smax, reasons = [], [], set()
+    names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+    for r in rows:
+      try:
+        sm.append(float(r[1]))
+        smax.append(float(r[2]))
+        for n, v in zip(names, r[5:9]):
+          if "Active" in v and "Not" not in v:
+            reasons.add(n)
+      except Exception:
+        pass
+    busy = [x for x in sm if x > 0]
+    return {"sm_mhz": statistics.median(busy) if busy else None, "sm_max_mhz": max(smax) if smax else None,
+            "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------- reference / CPU baseline
+def cpu_decode_sample(hf_cfg, sample_batch: int, ctx: int, steps: int, warmup: int, weights_cpu=None, seed: int = 0):
+  """Times the oracle (reference-exact eager PyTorch: per-op bf16 modules, contiguous
+  [B, KV, prompt+1024, hd] cache, GQA expand, full-cache masked SDPA, top-k-35 sampler) on
+  the host cores: `steps` decode steps of `sample_batch` sequences at context `ctx`.  The
+  cache is filled with synthetic K/V instead of running the 2048-token prefill on the CPU
+  (the decode cost does not depend on the cached values)."""
+  import torch
+  from oracle import torch_oracle as O
+  torch.set_num_threads(os.cpu_count() or 1)
+  cfg = O.model_config_from_hf(hf_cfg)
+  nl = cfg["num_layers"]
+  if weights_cpu is None:
+    from xotorch_support_jetson_b200.synth import random_hf_state
+    weights_cpu = random_hf_state(hf_cfg, seed=seed)
+  model = O.OracleShardModel(cfg, MODEL, 0, nl - 1, weights_cpu, O.OracleOptions())
+  eng = O.OracleEngine(model)
+  B = sample_batch
+  g = torch.Generator().manual_seed(1234)
+  prompt = torch.randint(1, cfg["vocab_size"], (B, ctx), generator=g)
+  eng.start_request(prompt)          # allocates the [B, KV, ctx+1024, hd] caches, mask and input_pos
+  for l in model.k_cache:
+    model.k_cache[l][:, :, :ctx].normal_(0, 0.5, generator=g)
+    model.v_cache[l][:, :, :ctx].normal_(0, 0.5, generator=g)
+  model.cache_pos = ctx
+  eng.curr_pos = ctx
+  import numpy as np
+  tok = np.ones((B, 1), dtype=np.int64)
+  times = []
+  for i in range(warmup + steps):
+    t0 = time.perf_counter()
+    logits = eng.infer_tensor(tok)
+    tok = eng.sample(logits, temp=0.0, top_k=35).astype(np.int64).reshape(B, 1)
+    times.append(time.perf_counter() - t0)
+  t = sum(times[warmup:])
+  return B * steps / t, t / steps
+
+
+def run_reference(args):
+  """`--impl reference`: the reference's CPU implementation of the path (oracle port) on this
+  box's host cores, same config/metric/unit; each step = a bounded sample of the batch."""
+  rank = int(os.environ.get("RANK", "0"))
+  if rank != 0:
+    return
+  from xotorch_support_jetson_b200.models import model_cards
+  hf_cfg = model_cards[args.model]["hf_config"]
+  cores = os.cpu_count() or 1
+  sb = args.ref_batch
+  steps, warm = args.steps, min(args.warmup, 2)
+  # keep the whole run within a few minutes: calibrate on one step
+  import torch  # noqa: F401
+  t0 = time.perf_counter()
+  val, per_step = cpu_decode_sample(hf_cfg, sb, args.prompt_len, 1, 1)
+  setup_s = time.perf_counter() - t0
+  budget = 150.0
+  if per_step * (steps + warm) > budget:
+    steps = max(2, int(budget / per_step) - warm)
+  val, per_step = cpu_decode_sample(hf_cfg, sb, args.prompt_len, steps, warm)
+  sample = (f"{steps} decode steps of {sb} of the {args.batch * args.gpus} sequences at context {args.prompt_len} "
+            f"(synthetic KV cache, no CPU prefill), oracle port in reference-exact mode")
+  line = {
+    "impl": "reference", "metric": "decode_tok_s", "value": val, "unit": "tok/s", "n_gpus": args.gpus, "steps": steps,
+    "warmup": warm, "ms_per_step": per_step * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+    "dtype": "bf16", "data": "synthetic",
+    "config": workload_config(args),
+    "cpu_baseline": {"value": val, "unit": "tok/s", "cores": cores, "kind": "port", "sample": sample},
+    "e2e": {"value": val, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    "setup_s": setup_s,
+  }
+  print(json.dumps(line), flush=True)
+
+
+def workload_config(args):
+  return {"workload": f"{args.model} bf16 random-init, {args.prompt_len}-token synthetic prompts, greedy decode from context "
+                      f"{args.prompt_len}, batch {args.batch} per micro-batch x {args.gpus} micro-batches in flight "
+                      f"({args.gpus}-stage layer pipeline, ring partition)",
+          "global_batch": args.batch * args.gpus, "prompt_len": args.prompt_len, "parallelism": f"pp{args.gpus}",
+          "l2_policy": "inputs larger than L2 (weights 15 GB per pass >> 126 MB L2)"}
+
+
+# ----------------------------------------------------------------------------- B200 arm
+def run_b200(args):
+  import torch
+  import torch.distributed as dist
+  import __graft_entry__ as graft
+  rank = int(os.environ.get("RANK", "0"))
+  world = int(os.environ.get("WORLD_SIZE", "1"))
+  local = int(os.environ.get("LOCAL_RANK", "0"))
+  if world != args.gpus:
+    if world == 1 and args.gpus > 1:
+      raise SystemExit(f"--gpus {args.gpus} needs torchrun with {args.gpus} ranks")
+    args.gpus = world
+  torch.cuda.set_device(local)
+  if world > 1:
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+  graft.build()
+  from xotorch_support_jetson_b200.model_config import load_model_config  # noqa: F401
+  from xotorch_support_jetson_b200.models import model_cards
+  from xotorch_support_jetson_b200.pipeline import PipelineRunner
+  from xotorch_support_jetson_b200 import model_config as mc
+
+  hf_cfg = model_cards[args.model]["hf_config"]
+  # same mapping load_model_config applies to a config.json on disk
+  with tempfile.TemporaryDirectory() as td:
+    (Path(td) / "config.json").write_text(json.dumps(hf_cfg))
+    cfg = mc.load_model_config(Path(td) / "config.json")
+  B, M, L = args.batch, world, args.prompt_len
+  K, W = args.steps, args.warmup
+  peaks = measured_peaks()
+  max_ctx = L + 2 * (K + W) + 80
+  runner = PipelineRunner(args.model, hf_cfg, cfg, rank, world, local, B, M, max_ctx, max_batch_tokens=args.max_batch_tokens,
+                          dist=dist if world > 1 else None, seed=0)
+  dev = runner.device
+  g = torch.Generator(device=dev).manual_seed(1234)
+  prompts = [torch.randint(1, cfg["vocab_size"], (B, L), generator=g, device=dev, dtype=torch.int32) for _ in range(M)]
+
+  def barrier():
+    torch.cuda.synchronize()
+    if world > 1:
+      dist.barrier()
+    torch.cuda.synchronize()
+
+  def timed(fn):
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(runner.stream)
+    fn()
+    e1.record(runner.stream)
+    barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+      dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms.item())
+
+  c0 = runner.stage.counters()
+  # ---- prefill: one untimed pass (builds launch plans), then a timed pass on fresh slots
+  runner.prefill(prompts)
+  if world > 1 and runner.first:
+    with torch.cuda.stream(runner.stream):
+      for m in range(M):
+        dist.recv(runner.tok[m], src=world - 1)
+  barrier()
+  runner.reset()
+  prefill_ms = timed(lambda: runner.prefill(prompts))
+  prefill_tok_s = B * M * L / (prefill_ms * 1e-3)
+
+  # ---- decode: W warm-up steps then exactly K timed steps
+  runner.decode(W)
+  clocks = ClockSampler(local)
+  if rank == 0:
+    clocks.start()
+  l0 = runner.stage.counters()["launches"]
+  decode_ms = timed(lambda: runner.decode(K))
+  launches = runner.stage.counters()["launches"] - l0
+  clk = clocks.stop() if rank == 0 else None
+  value = B * M * K / (decode_ms * 1e-3)
+  ctx_avg = L + W + (K - 1) / 2.0
+
+  # ---- end-to-end leg with host buffers
+  e2e = None
+  if world > 1:
+    host_in = [torch.zeros(B, dtype=torch.int32).pin_memory() for _ in range(M)]
+    host_out = [torch.zeros(B, dtype=torch.int32).pin_memory() for _ in range(M)]
+    e2e_ms = timed(lambda: runner.decode(K, host_tokens=host_in, host_out=host_out))
+    e2e = {"value": B * M * K / (e2e_ms * 1e-3), "unit": "tok/s", "h2d_bytes_per_step": 4 * B * M, "d2h_bytes_per_step": 2 * 4 * B * M,
+           "api": "PipelineRunner.decode with pinned host id buffers (ids D2H+H2D on rank 0, sampled ids D2H on the last rank, every step)"}
+    runner.drain()
+  else:
+    runner.drain()
+
+  # ---- roofline of the dominant kernel: the tcgen05 Linear streaming this stage's weights
+  st = runner.stage
+  cnt = st.counters()
+  with torch.cuda.stream(runner.stream):
+    st.bench_linears(B, 2)
+  iters = 20
+  nl_box = [0]
+
+  def lin():
+    with torch.cuda.stream(runner.stream):
+      nl_box[0] = st.bench_linears(B, iters)
+
+  lin_ms = timed(lin)
+  n_lin = nl_box[0]
+  wbytes = cnt["weight_bytes"]
+  lin_launch_us = lin_ms * 1e3 / n_lin
+  achieved = wbytes * iters / (lin_ms * 1e-3) / 1e9
+  roofline = {"bound": "hbm", "kernel": "xb_gemm_tcgen05_kernel (skinny weight-streaming Linear)", "achieved": achieved,
+              "peak": peaks["hbm_gbs"], "peak_source": peaks["source"] + " (MEASURED_PEAKS.json hbm_gbs)" if peaks["source"] == "measured" else "fallback",
+              "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": None,
+              "bytes_per_launch": wbytes / (n_lin / iters), "launch_us": lin_launch_us,
+              "launches_per_step": n_lin // iters}
+  prof = ROOT / "profiles" / "r01_ncu_traffic.json"
+  if prof.exists():
+    try:
+      roofline["traffic"] = json.loads(prof.read_text()).get("gemm_dram_bytes_per_launch")
+    except Exception:
+      pass
+  # whole decode step against the HBM roofline (weights once per micro-batch + KV of every sequence)
+  step_bytes = M * wbytes + B * M * ctx_avg * cnt["kv_bytes_per_pos"]
+  step_frac = (step_bytes / (decode_ms * 1e-3 / K) / 1e9) / peaks["hbm_gbs"]
+
+  extra = {"prefill_tok_s": prefill_tok_s, "prefill_ms": prefill_ms,
+           "decode_step_hbm_frac": step_frac, "decode_step_bytes_per_gpu": step_bytes,
+           "decode_ctx_avg": ctx_avg}
+  # prefill against the tensor roofline (algorithmic FLOPs)
+  D, H, KV, hd, I, V = cfg["embed_dim"], cfg["num_heads"], cfg["num_kv_heads"], cfg["head_dim"], cfg["intermediate_dim"], cfg["vocab_size"]
+  nl_total = cfg["num_layers"]
+  T_all = B * M * L
+  flops = 2.0 * T_all * nl_total * (2 * D * H * hd + 2 * D * KV * hd + 3 * D * I) + 2.0 * B * M * L * L * H * hd * nl_total + 2.0 * B * M * V * D
+  extra["prefill_tflops_per_gpu"] = flops / world / (prefill_ms * 1e-3) / 1e12
+  extra["prefill_tensor_frac"] = extra["prefill_tflops_per_gpu"] / peaks["bf16_tflops_sustained"]
+
+  # ---- decode bs=1 (latency-bound single stream), same pipeline
+  runner.reset()
+  barrier()
+  r1 = PipelineRunnerView(runner)
+  bs1 = r1.run_bs1(prompts[0][:1], W, K, timed, dist if world > 1 else None)
+  extra.update(bs1)
+  if world == 1:
+    b1_bytes = wbytes + (L + W + (K - 1) / 2.0) * cnt["kv_bytes_per_pos"]
+    extra["decode_bs1_hbm_frac"] = (b1_bytes / (1.0 / bs1["decode_bs1_tok_s"])) / 1e9 / peaks["hbm_gbs"]
+
+  # ---- N=1: end-to-end through the InferenceEngine API with host numpy buffers
+  cpu_base = None
+  if world == 1:
+    runner.reset()
+    e2e = e2e_engine_api(runner, cfg, prompts[0], K, W)
+    if rank == 0 and not args.no_cpu_baseline:
+      t0 = time.perf_counter()
+      val, per_step = cpu_decode_sample(hf_cfg, args.ref_batch, L, args.cpu_steps, 1)
+      cpu_base = {"value": val, "unit": "tok/s", "cores": os.cpu_count() or 1, "kind": "port",
+                  "sample": f"{args.cpu_steps} decode steps of {args.ref_batch} sequences at context {L} (synthetic KV cache), "
+                            f"oracle port in reference-exact mode, {time.perf_counter() - t0:.0f}s incl. weight init"}
+
+  if rank == 0:
+    line = {
+      "metric": "decode_tok_s", "value": value, "unit": "tok/s", "n_gpus": world, "steps": K, "warmup": W,
+      "ms_per_step": decode_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+      "data": "synthetic", "config": workload_config(args), "clocks": clk, "e2e": e2e, "gpu_launches": launches,
+      "roofline": roofline, "cpu_baseline": cpu_base, "extra": extra,
+    }
+    print(json.dumps(line), flush=True)
+  runner.close()
+  if world > 1:
+    dist.destroy_process_group()
+
+
+class PipelineRunnerView:
+  """bs=1 single-stream decode on the slots of an existing runner (micro-batch 0, slot 0)."""
+
+  def __init__(self, runner):
+    self.r = runner
+
+  def run_bs1(self, prompt, W, K, timed, dist):
+    import torch
+    r = self.r
+    L = prompt.shape[1]
+    tok = torch.zeros(1, dtype=torch.int32, device=r.device)
+    logits = torch.empty((1, r.vocab), dtype=torch.float32, device=r.device) if r.last else None
+    pos = [0]
+
+    def fwd(q_len, tokens):
+      with torch.cuda.stream(r.stream):
+        hid = None
+        if not r.first:
+          hid = r.h_in[:q_len]
+          dist.recv(hid, src=r.rank - 1)
+        if r.last:
+          lg = r.stage.forward([0], [q_len], [pos[0]], tokens=tokens if r.first else None, hidden=hid, out=logits)
+          r.stage.sample(lg, temp=0.0, out=tok)
+          if r.world > 1:
+            dist.send(tok, dst=0)
+        else:
+          out = r.stage.forward([0], [q_len], [pos[0]], tokens=tokens if r.first else None, hidden=hid, out=r.h_out[:q_len])
+          dist.send(out, dst=r.rank + 1)
+          if r.first:
+            dist.recv(tok, src=r.world - 1)
+        pos[0] += q_len
+
+    fwd(L, prompt.reshape(-1))
+
+    def steps(n):
+      for _ in range(n):
+        fwd(1, tok)
+
+    steps(W)
+    ms = timed(lambda: steps(K))
+    return {"decode_bs1_tok_s": K / (ms * 1e-3), "decode_bs1_ms_per_tok": ms / K}
+
+
+def e2e_engine_api(runner, cfg, prompt, K, W):
+  """decode tok/s through B200ShardInferenceEngine.infer_tensor + sample with HOST numpy
+  buffers: every step uploads the ids, downloads the [B, vocab] fp32 logits the reference's
+  API returns, uploads them again for sample() and downloads the sampled ids."""
+  import numpy as np
+  import torch
+  from xotorch_support_jetson_b200.b200_engine import B200ShardInferenceEngine
+  eng = B200ShardInferenceEngine(shard_downloader=None)
+  eng.attach_stage(runner.shard, runner.stage, cfg)
+  B = prompt.shape[0]
+  toks = prompt.cpu().numpy().astype(np.int64)
+
+  async def go():
+    logits, state = await eng.infer_tensor("bench", runner.shard, toks, None)
+    tok = await eng.sample(logits, temp=0.0)
+    for _ in range(W):
+      logits, state = await eng.infer_tensor("bench", runner.shard, tok.reshape(B, 1), state)
+      tok = await eng.sample(logits, temp=0.0)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(K):
+      logits, state = await eng.infer_tensor("bench", runner.shard, tok.reshape(B, 1), state)
+      tok = await eng.sample(logits, temp=0.0)
+    torch.cuda.synchronize()
+    return time.perf_counter() - t0
+
+  dt = asyncio.run(go())
+  V = cfg["vocab_size"]
+  eng.end_request("bench")
+  return {"value": B * K / dt, "unit": "tok/s", "h2d_bytes_per_step": B * 4 + B * V * 4, "d2h_bytes_per_step": B * V * 4 + B * 4,
+          "api": "B200ShardInferenceEngine.infer_tensor(np ids) -> np fp32 logits [B,V]; .sample(np logits) -> np ids (reference plugin API, host buffers)"}
+
+
+def main():
+  ap = argparse.ArgumentParser()
+  ap.add_argument("--gpus", type=int, default=1)
+  ap.add_argument("--steps", type=int, default=64)
+  ap.add_argument("--warmup", type=int, default=4)
+  ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+  ap.add_argument("--model", default=MODEL)
+  ap.add_argument("--batch", type=int, default=BATCH)
+  ap.add_argument("--prompt-len", type=int, default=PROMPT_LEN)
+  ap.add_argument("--max-batch-tokens", type=int, default=8192)
+  ap.add_argument("--ref-batch", type=int, default=4, help="sequences per step in the CPU sample")
+  ap.add_argument("--cpu-steps", type=int, default=6)
+  ap.add_argument("--no-cpu-baseline", action="store_true")
+  args = ap.parse_args()
+  if args.warmup < 3 and args.impl == "b200":
+    args.warmup = 3
+  if args.impl == "reference":
+    run_reference(args)
+  else:
+    run_b200(args)
+
+
+if __name__ == "__main__":
+  main()

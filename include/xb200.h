@@ -109,6 +109,8 @@ int xb_kv_slot_len(xb_engine* e, int slot, int* len);
 
 /* Replaces ShardTransformerDecoder.forward (llm_utils.py:367-440) with the intended
  * hand-off semantics (a non-last shard returns the OUTPUT of its last layer).
+ * Decode-only batches (every q_len == 1) on a non-default stream are replayed from a CUDA
+ * graph captured on the second call of each (n_seqs, kv-split) shape.
  * out: device bf16 [T, dim] on a non-last shard; device fp32 [n_seqs, vocab] logits of the
  * last position of each sequence on a last shard (bf16-rounded values, as the reference's
  * `model_logits[:, -1].float()`, sharded_inference_engine.py:366).
@@ -133,6 +135,13 @@ int xb_get_counters(xb_engine* e, xb_counters* out);
  * scratch: device fp32, at least 16*T*N elements. */
 int xb_debug_linear(const void* x, const void* w, int T, int N, int K, float* y, float* scratch,
                     int use_tensor_cores, int force_splits, int round_bf16, void* stream);
+
+/* Measurement hook (bench.py roofline leg): enqueue the Linear kernels of one forward over
+ * T token rows -- q/k/v, o, gate/up, down per layer (general_mha.py:83-102,
+ * llm_utils.py:513-522) and the LM head on a last shard (llm_utils.py:425-435) -- `iters`
+ * times back to back on `stream`, on the engine's own weights.  The caller brackets the
+ * call with CUDA events; *n_launches receives the number of kernels enqueued. */
+int xb_bench_linears(xb_engine* e, int T, int iters, int* n_launches, void* stream);
 
 #ifdef __cplusplus
 }

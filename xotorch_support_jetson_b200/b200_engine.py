@@ -85,9 +85,22 @@ class B200ShardInferenceEngine(InferenceEngine):
       self.free_slots = list(range(self.max_seqs - 1, -1, -1))
       self.rng = torch.Generator(device=st.device)
       self.rng.manual_seed(1234)
+      self._stream = torch.cuda.Stream(device=st.device)  # non-default stream: decode steps replay CUDA graphs
 
     await asyncio.get_running_loop().run_in_executor(self.executor, start_model)
     self.shard = shard
+
+  def attach_stage(self, shard: Shard, stage: StageRuntime, config: dict, tokenizer=None):
+    """Adopt an already-loaded StageRuntime (weights resident in HBM) instead of loading the
+    shard from a checkpoint directory -- in-memory / synthetic weights, benchmarks."""
+    self.stage, self.shard, self.model_config = stage, shard, config
+    self.max_seqs, self.max_batch_tokens = stage.max_seqs, stage.max_batch_tokens
+    self.tokenizer = tokenizer or SyntheticTokenizer(config["vocab_size"])
+    self.requests.clear()
+    self.free_slots = list(range(self.max_seqs - 1, -1, -1))
+    self.rng = torch.Generator(device=stage.device)
+    self.rng.manual_seed(1234)
+    self._stream = torch.cuda.Stream(device=stage.device)
 
   async def _resolve_tokenizer(self, path):
     try:
@@ -119,6 +132,10 @@ class B200ShardInferenceEngine(InferenceEngine):
   # ------------------------------------------------------------------ sampling
   async def sample(self, x: np.ndarray, temp=TEMP, top_k=TOP_K, top_p: float = 0.0) -> np.ndarray:
     def sample_wrapper():
+      with torch.cuda.stream(self._stream):
+        return sample_body()
+
+    def sample_body():
       st = self.stage
       logits = torch.as_tensor(np.ascontiguousarray(x, dtype=np.float32)).to(st.device)
       if logits.ndim == 1:
@@ -163,11 +180,46 @@ class B200ShardInferenceEngine(InferenceEngine):
         self.stage.release_slot(s)
         self.free_slots.append(s)
 
+  def _forward_chunked(self, st: StageRuntime, req: _Request, dev_in: torch.Tensor, bsz: int, s: int, pos: int,
+                       is_tokens: bool) -> torch.Tensor:
+    """One logical forward over [bsz, s] rows, split so that no native call carries more
+    than max_batch_tokens rows: whole sequences per call, or position chunks of one
+    sequence (chunked prefill) when a single sequence is longer than that."""
+    cap = st.max_batch_tokens
+    last = self.shard.is_last_layer()
+    if bsz * s <= cap:
+      flat = dev_in.reshape(-1) if is_tokens else dev_in.reshape(bsz * s, -1)
+      return st.forward(req.slots, [s] * bsz, [pos] * bsz, **({"tokens": flat} if is_tokens else {"hidden": flat}))
+    outs = []
+    if s <= cap:
+      per = max(1, cap // s)
+      for b0 in range(0, bsz, per):
+        b1 = min(bsz, b0 + per)
+        part = dev_in[b0:b1]
+        flat = part.reshape(-1) if is_tokens else part.reshape((b1 - b0) * s, -1)
+        outs.append(st.forward(req.slots[b0:b1], [s] * (b1 - b0), [pos] * (b1 - b0),
+                               **({"tokens": flat} if is_tokens else {"hidden": flat})))
+      return torch.cat(outs, dim=0)
+    for b in range(bsz):
+      seq_out = []
+      for c0 in range(0, s, cap):
+        c1 = min(s, c0 + cap)
+        part = dev_in[b, c0:c1]
+        flat = part.reshape(-1) if is_tokens else part.reshape(c1 - c0, -1)
+        o = st.forward([req.slots[b]], [c1 - c0], [pos + c0], **({"tokens": flat} if is_tokens else {"hidden": flat}))
+        seq_out.append(o)
+      outs.append(seq_out[-1] if last else torch.cat(seq_out, dim=0))
+    return torch.cat(outs, dim=0)
+
   async def infer_tensor(self, request_id: str, shard: Shard, input_data: np.ndarray,
                          inference_state: Optional[dict] = None) -> tuple[np.ndarray, Optional[dict]]:
     await self.ensure_shard(shard)
 
     def infer_wrapper():
+      with torch.cuda.stream(self._stream):
+        return infer_body()
+
+    def infer_body():
       st = self.stage
       x = np.asarray(input_data)
       if x.ndim == 2:
@@ -184,12 +236,11 @@ class B200ShardInferenceEngine(InferenceEngine):
         req = self._start_request(request_id, bsz)
       pos = req.pos if state_pos is None else int(state_pos)
       if x.ndim == 2:
-        toks = torch.as_tensor(np.ascontiguousarray(x, dtype=np.int32)).to(st.device).reshape(-1)
-        out = st.forward(req.slots, [s] * bsz, [pos] * bsz, tokens=toks)
+        dev_in = torch.as_tensor(np.ascontiguousarray(x, dtype=np.int32)).to(st.device, non_blocking=True)
         req.tokens = x.astype(np.int64) if (req.tokens is None or s > 1) else np.concatenate([req.tokens, x.astype(np.int64)], axis=-1)
       else:
-        hid = torch.as_tensor(np.ascontiguousarray(x, dtype=np.float32)).to(st.device).to(torch.bfloat16).reshape(bsz * s, -1)
-        out = st.forward(req.slots, [s] * bsz, [pos] * bsz, hidden=hid)
+        dev_in = torch.as_tensor(np.ascontiguousarray(x, dtype=np.float32)).to(st.device, non_blocking=True).to(torch.bfloat16)
+      out = self._forward_chunked(st, req, dev_in, bsz, s, pos, x.ndim == 2)
       req.pos = pos + s
       new_state = {"curr_pos": pos if not shard.is_last_layer() else pos + s}
       if req.tokens is not None:

@@ -6,6 +6,7 @@
 #include "xb_kernels.cuh"
 
 #include <stdarg.h>
+#include <stdlib.h>
 #include <map>
 #include <vector>
 
@@ -45,9 +46,22 @@ struct xb_engine {
   std::vector<int> slot_len;
   std::vector<int> h_page_table;
   int* d_page_table = nullptr;
-  // batch meta (device)
+  // batch meta: one device block [tok_seq | tok_pos | seq_slot | seq_last], refreshed by ONE
+  // H2D copy per forward from a ring of pinned host buffers
+  int* d_meta = nullptr;
   int *d_tok_seq = nullptr, *d_tok_pos = nullptr, *d_seq_slot = nullptr, *d_seq_last = nullptr;
-  std::vector<int> h_meta;
+  static constexpr int META_RING = 8;
+  int* h_meta_ring[META_RING] = {nullptr};
+  cudaEvent_t meta_ev[META_RING] = {nullptr};
+  int meta_next = 0;
+  size_t meta_ints = 0;
+  // engine-owned input/output staging so captured graphs see fixed addresses
+  int* in_tokens = nullptr;
+  float* logits = nullptr;
+  // decode-step graphs keyed by (n_seqs, n_splits)
+  struct StepGraph { cudaGraphExec_t exec = nullptr; int warmed = 0; uint64_t launches = 0; };
+  std::map<long long, StepGraph> graphs;
+  int use_graphs = 1;
   // workspaces
   bf16 *h = nullptr, *hn = nullptr, *q = nullptr, *attn = nullptr, *act = nullptr, *last_rows = nullptr;
   void* gemm_out = nullptr;
@@ -135,12 +149,26 @@ extern "C" int xb_engine_create(const xb_model_desc* desc, int device, xb_engine
   e->gemm_out_bytes = T * maxN * 2;
   if (e->gemm_out_bytes < ((size_t)64 << 20)) e->gemm_out_bytes = (size_t)64 << 20;
   XB_TRY(dmalloc(&e->gemm_out, e->gemm_out_bytes));
-  XB_TRY(dmalloc((void**)&e->o_part, T * d.n_heads * e->max_attn_splits * d.head_dim * sizeof(float)));
-  XB_TRY(dmalloc((void**)&e->ml_part, T * d.n_heads * e->max_attn_splits * 2 * sizeof(float)));
-  XB_TRY(dmalloc((void**)&e->d_tok_seq, T * 4));
-  XB_TRY(dmalloc((void**)&e->d_tok_pos, T * 4));
-  XB_TRY(dmalloc((void**)&e->d_seq_slot, (size_t)d.max_seqs * 4));
-  XB_TRY(dmalloc((void**)&e->d_seq_last, (size_t)d.max_seqs * 4));
+  // kv splits > 1 are only used while T * n_kv_heads < 2 * num_sms (see xb_forward)
+  const size_t Tsplit = T < (size_t)2 * e->num_sms ? T : (size_t)2 * e->num_sms;
+  XB_TRY(dmalloc((void**)&e->o_part, Tsplit * d.n_heads * e->max_attn_splits * d.head_dim * sizeof(float)));
+  XB_TRY(dmalloc((void**)&e->ml_part, Tsplit * d.n_heads * e->max_attn_splits * 2 * sizeof(float)));
+  e->meta_ints = 2 * T + 2 * (size_t)d.max_seqs;
+  XB_TRY(dmalloc((void**)&e->d_meta, e->meta_ints * 4));
+  e->d_tok_seq = e->d_meta;
+  e->d_tok_pos = e->d_meta + T;
+  e->d_seq_slot = e->d_meta + 2 * T;
+  e->d_seq_last = e->d_meta + 2 * T + d.max_seqs;
+  for (int i = 0; i < xb_engine::META_RING; ++i) {
+    XB_CUDA(cudaMallocHost((void**)&e->h_meta_ring[i], e->meta_ints * 4));
+    XB_CUDA(cudaEventCreateWithFlags(&e->meta_ev[i], cudaEventDisableTiming));
+  }
+  XB_TRY(dmalloc((void**)&e->in_tokens, T * 4));
+  if (last) XB_TRY(dmalloc((void**)&e->logits, (size_t)d.max_seqs * d.vocab * sizeof(float)));
+  {
+    const char* g = getenv("XB_GRAPHS");
+    if (g != nullptr && g[0] == '0') e->use_graphs = 0;
+  }
   *out = e;
   return 0;
 }
@@ -154,8 +182,14 @@ extern "C" int xb_engine_destroy(xb_engine* e) {
     cudaFree(w.sa_norm); cudaFree(w.mlp_norm); cudaFree(w.k_pool); cudaFree(w.v_pool);
   }
   cudaFree(e->embed); cudaFree(e->final_norm); cudaFree(e->lm_head); cudaFree(e->rope);
-  cudaFree(e->d_page_table); cudaFree(e->d_tok_seq); cudaFree(e->d_tok_pos); cudaFree(e->d_seq_slot);
-  cudaFree(e->d_seq_last); cudaFree(e->h); cudaFree(e->hn); cudaFree(e->q); cudaFree(e->attn); cudaFree(e->act);
+  cudaFree(e->d_page_table); cudaFree(e->d_meta); cudaFree(e->in_tokens); cudaFree(e->logits);
+  for (int i = 0; i < xb_engine::META_RING; ++i) {
+    if (e->h_meta_ring[i]) cudaFreeHost(e->h_meta_ring[i]);
+    if (e->meta_ev[i]) cudaEventDestroy(e->meta_ev[i]);
+  }
+  for (auto& kv : e->graphs)
+    if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+  cudaFree(e->h); cudaFree(e->hn); cudaFree(e->q); cudaFree(e->attn); cudaFree(e->act);
   cudaFree(e->last_rows); cudaFree(e->gemm_out); cudaFree(e->o_part); cudaFree(e->ml_part);
   delete e;
   return 0;
@@ -213,6 +247,10 @@ extern "C" int xb_kv_reserve(xb_engine* e, int n_slots, int max_tokens_per_slot,
   }
   cudaFree(e->d_page_table);
   e->d_page_table = nullptr;
+  // captured decode graphs hold the old pool / page-table addresses
+  for (auto& kv : e->graphs)
+    if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+  e->graphs.clear();
   e->n_slots = n_slots;
   e->page_tokens = page_tokens;
   e->max_pages = (max_tokens_per_slot + page_tokens - 1) / page_tokens;
@@ -309,70 +347,13 @@ static int launch_resid_norm(xb_engine* e, const GemmPlan* gp, int T, const bf16
   return 0;
 }
 
-extern "C" int xb_forward(xb_engine* e, const xb_batch* b, void* out, void* const* taps, void* stream) {
-  XB_CHECK(e != nullptr && b != nullptr && out != nullptr, "null argument");
+// All kernel launches of one forward over T token rows.  Reads e->in_tokens (first shard) or
+// e->h (other shards); leaves the residual stream in e->h and, on a last shard, the logits
+// of each sequence's last position in e->logits.  Pure stream work on fixed addresses, so it
+// can be captured into a CUDA graph.
+static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, void* const* taps, cudaStream_t st) {
   const xb_model_desc& d = e->d;
-  cudaStream_t st = (cudaStream_t)stream;
-  XB_CUDA(cudaSetDevice(e->device));
-  XB_CHECK(e->n_slots > 0, "xb_kv_reserve must be called before xb_forward");
-  XB_CHECK(b->n_seqs > 0 && b->n_seqs <= d.max_seqs, "n_seqs %d out of range (max %d)", b->n_seqs, d.max_seqs);
   const bool first = d.start_layer == 0, last = d.end_layer == d.n_layers - 1;
-  XB_CHECK(first ? (b->tokens != nullptr) : (b->hidden_in != nullptr),
-           first ? "first shard needs token ids" : "non-first shard needs a hidden state");
-  // ---- host-side batch bookkeeping
-  int T = 0, max_ctx = 0;
-  for (int i = 0; i < b->n_seqs; ++i) {
-    const int slot = b->slot_ids[i], ql = b->q_lens[i], pos = b->positions[i];
-    XB_CHECK(slot >= 0 && slot < e->n_slots, "seq %d: slot %d out of range", i, slot);
-    XB_CHECK(ql > 0 && pos >= 0, "seq %d: bad q_len %d / position %d", i, ql, pos);
-    XB_CHECK(pos <= e->slot_len[slot], "seq %d: position %d leaves a gap after cached length %d", i, pos, e->slot_len[slot]);
-    XB_CHECK(pos + ql <= e->max_pages * e->page_tokens, "seq %d: %d tokens exceed the reserved %d per slot", i, pos + ql,
-             e->max_pages * e->page_tokens);
-    XB_CHECK(pos + ql <= d.max_positions, "seq %d: position %d beyond the RoPE table (%d rows)", i, pos + ql, d.max_positions);
-    for (int j = 0; j < i; ++j) XB_CHECK(b->slot_ids[j] != slot, "slot %d appears twice in one batch", slot);
-    T += ql;
-    if (pos + ql > max_ctx) max_ctx = pos + ql;
-  }
-  XB_CHECK(T <= d.max_batch_tokens, "batch carries %d token rows, engine was created for %d", T, d.max_batch_tokens);
-  std::vector<int>& hm = e->h_meta;
-  hm.assign((size_t)2 * T + 2 * b->n_seqs, 0);
-  int* tok_seq = hm.data();
-  int* tok_pos = tok_seq + T;
-  int* seq_slot = tok_pos + T;
-  int* seq_last = seq_slot + b->n_seqs;
-  int r = 0;
-  for (int i = 0; i < b->n_seqs; ++i) {
-    const int slot = b->slot_ids[i], ql = b->q_lens[i], pos = b->positions[i];
-    // grow the slot's page list (pages come from the shared free list: non-contiguous)
-    const int need_pages = (pos + ql + e->page_tokens - 1) / e->page_tokens;
-    std::vector<int>& pages = e->slot_pages[slot];
-    if ((int)pages.size() < need_pages) {
-      const int old = (int)pages.size();
-      while ((int)pages.size() < need_pages) {
-        XB_CHECK(!e->free_pages.empty(), "KV page pool exhausted");
-        const int p = e->free_pages.back();
-        e->free_pages.pop_back();
-        e->h_page_table[(size_t)slot * e->max_pages + pages.size()] = p;
-        pages.push_back(p);
-      }
-      XB_CUDA(cudaMemcpyAsync(e->d_page_table + (size_t)slot * e->max_pages + old,
-                              e->h_page_table.data() + (size_t)slot * e->max_pages + old, (need_pages - old) * 4,
-                              cudaMemcpyHostToDevice, st));
-    }
-    for (int j = 0; j < ql; ++j) {
-      tok_seq[r] = i;
-      tok_pos[r] = pos + j;
-      ++r;
-    }
-    seq_slot[i] = slot;
-    seq_last[i] = r - 1;
-    e->slot_len[slot] = pos + ql;
-  }
-  e->c.kv_pages_free = e->free_pages.size();
-  XB_CUDA(cudaMemcpyAsync(e->d_tok_seq, tok_seq, T * 4, cudaMemcpyHostToDevice, st));
-  XB_CUDA(cudaMemcpyAsync(e->d_tok_pos, tok_pos, T * 4, cudaMemcpyHostToDevice, st));
-  XB_CUDA(cudaMemcpyAsync(e->d_seq_slot, seq_slot, b->n_seqs * 4, cudaMemcpyHostToDevice, st));
-  XB_CUDA(cudaMemcpyAsync(e->d_seq_last, seq_last, b->n_seqs * 4, cudaMemcpyHostToDevice, st));
   BatchMeta m;
   m.tok_seq = e->d_tok_seq;
   m.tok_pos = e->d_tok_pos;
@@ -381,33 +362,17 @@ extern "C" int xb_forward(xb_engine* e, const xb_batch* b, void* out, void* cons
   m.page_table = e->d_page_table;
   m.max_pages = e->max_pages;
   m.page_tokens = e->page_tokens;
-
   const int D = d.dim, I = d.inter_dim, hd = d.head_dim;
   const size_t norm_smem = (size_t)D * sizeof(float);
-  // ---- stage input
   if (first) {
-    xb_embed_norm_kernel<256><<<T, 256, 0, st>>>(b->tokens, e->embed, e->L[0].sa_norm, e->h, e->hn, D, d.vocab, d.norm_eps,
+    xb_embed_norm_kernel<256><<<T, 256, 0, st>>>(e->in_tokens, e->embed, e->L[0].sa_norm, e->h, e->hn, D, d.vocab, d.norm_eps,
                                                   d.rmsnorm_two_round);
   } else {
-    XB_CUDA(cudaMemcpyAsync(e->h, b->hidden_in, (size_t)T * D * 2, cudaMemcpyDeviceToDevice, st));
     xb_resid_norm_kernel<256, 2><<<T, 256, norm_smem, st>>>(nullptr, 0, 0, nullptr, e->h, e->L[0].sa_norm, e->hn, D,
                                                              d.norm_eps, d.rmsnorm_two_round);
   }
   XB_CUDA(cudaGetLastError());
   LAUNCH_COUNT(e);
-
-  // kv splits: enough blocks to fill the GPU at decode, none needed when T is large
-  int n_splits = 1;
-  {
-    const int blocks = T * d.n_kv_heads;
-    const int pages = (max_ctx + e->page_tokens - 1) / e->page_tokens;
-    if (blocks < 2 * e->num_sms) {
-      n_splits = (2 * e->num_sms + blocks - 1) / blocks;
-      if (n_splits > pages) n_splits = pages;
-      if (n_splits > e->max_attn_splits) n_splits = e->max_attn_splits;
-      if (n_splits < 1) n_splits = 1;
-    }
-  }
 
   for (int l = 0; l < e->nl; ++l) {
     const LayerW& w = e->L[l];
@@ -461,20 +426,186 @@ extern "C" int xb_forward(xb_engine* e, const xb_batch* b, void* out, void* cons
 
   if (last) {
     // final norm was fused above; LM head on the last position of each sequence only
-    xb_gather_rows_kernel<<<b->n_seqs, 256, 0, st>>>(e->hn, e->d_seq_last, e->last_rows, D);
+    xb_gather_rows_kernel<<<n_seqs, 256, 0, st>>>(e->hn, e->d_seq_last, e->last_rows, D);
     XB_CUDA(cudaGetLastError());
     LAUNCH_COUNT(e);
     const bf16* head = d.tied_head ? e->embed : e->lm_head;
-    XB_CHECK(b->n_seqs <= 128, "LM head path supports up to 128 sequences per call");
-    // `out` is caller memory: plan per (n_seqs, out pointer)
-    GemmPlan p;
-    XB_TRY(xb_gemm_plan(&p, e->last_rows, D, head, b->n_seqs, d.vocab, D, out, d.vocab, nullptr, 1, e->num_sms, 1));
-    XB_TRY(xb_gemm_run(p, st));
+    const GemmPlan* gp;
+    XB_TRY(get_plan(e, SITE_HEAD, 0, e->last_rows, D, head, n_seqs, d.vocab, D, e->logits, d.vocab, nullptr, 1, &gp));
+    XB_TRY(xb_gemm_run(*gp, st));
     LAUNCH_COUNT(e);
+  }
+  return 0;
+}
+
+extern "C" int xb_forward(xb_engine* e, const xb_batch* b, void* out, void* const* taps, void* stream) {
+  XB_CHECK(e != nullptr && b != nullptr, "null argument");
+  const xb_model_desc& d = e->d;
+  cudaStream_t st = (cudaStream_t)stream;
+  XB_CUDA(cudaSetDevice(e->device));
+  XB_CHECK(e->n_slots > 0, "xb_kv_reserve must be called before xb_forward");
+  XB_CHECK(b->n_seqs > 0 && b->n_seqs <= d.max_seqs, "n_seqs %d out of range (max %d)", b->n_seqs, d.max_seqs);
+  const bool first = d.start_layer == 0, last = d.end_layer == d.n_layers - 1;
+  XB_CHECK(first ? (b->tokens != nullptr) : (b->hidden_in != nullptr),
+           first ? "first shard needs token ids" : "non-first shard needs a hidden state");
+  XB_CHECK(!last || b->n_seqs <= 128, "LM head path supports up to 128 sequences per call");
+  // ---- host-side batch bookkeeping
+  int T = 0, max_ctx = 0;
+  bool decode_only = true;
+  for (int i = 0; i < b->n_seqs; ++i) {
+    const int slot = b->slot_ids[i], ql = b->q_lens[i], pos = b->positions[i];
+    XB_CHECK(slot >= 0 && slot < e->n_slots, "seq %d: slot %d out of range", i, slot);
+    XB_CHECK(ql > 0 && pos >= 0, "seq %d: bad q_len %d / position %d", i, ql, pos);
+    XB_CHECK(pos <= e->slot_len[slot], "seq %d: position %d leaves a gap after cached length %d", i, pos, e->slot_len[slot]);
+    XB_CHECK(pos + ql <= e->max_pages * e->page_tokens, "seq %d: %d tokens exceed the reserved %d per slot", i, pos + ql,
+             e->max_pages * e->page_tokens);
+    XB_CHECK(pos + ql <= d.max_positions, "seq %d: position %d beyond the RoPE table (%d rows)", i, pos + ql, d.max_positions);
+    for (int j = 0; j < i; ++j) XB_CHECK(b->slot_ids[j] != slot, "slot %d appears twice in one batch", slot);
+    T += ql;
+    if (ql != 1) decode_only = false;
+    if (pos + ql > max_ctx) max_ctx = pos + ql;
+  }
+  XB_CHECK(T <= d.max_batch_tokens, "batch carries %d token rows, engine was created for %d", T, d.max_batch_tokens);
+  // pinned staging buffer from the ring (wait until its previous upload has been consumed)
+  const int ring = e->meta_next;
+  e->meta_next = (e->meta_next + 1) % xb_engine::META_RING;
+  XB_CUDA(cudaEventSynchronize(e->meta_ev[ring]));
+  int* hm = e->h_meta_ring[ring];
+  const size_t Tmax = d.max_batch_tokens;
+  int* tok_seq = hm;
+  int* tok_pos = hm + Tmax;
+  int* seq_slot = hm + 2 * Tmax;
+  int* seq_last = hm + 2 * Tmax + d.max_seqs;
+  int r = 0;
+  for (int i = 0; i < b->n_seqs; ++i) {
+    const int slot = b->slot_ids[i], ql = b->q_lens[i], pos = b->positions[i];
+    // grow the slot's page list (pages come from the shared free list: non-contiguous)
+    const int need_pages = (pos + ql + e->page_tokens - 1) / e->page_tokens;
+    std::vector<int>& pages = e->slot_pages[slot];
+    if ((int)pages.size() < need_pages) {
+      const int old = (int)pages.size();
+      while ((int)pages.size() < need_pages) {
+        XB_CHECK(!e->free_pages.empty(), "KV page pool exhausted");
+        const int p = e->free_pages.back();
+        e->free_pages.pop_back();
+        e->h_page_table[(size_t)slot * e->max_pages + pages.size()] = p;
+        pages.push_back(p);
+      }
+      XB_CUDA(cudaMemcpyAsync(e->d_page_table + (size_t)slot * e->max_pages + old,
+                              e->h_page_table.data() + (size_t)slot * e->max_pages + old, (need_pages - old) * 4,
+                              cudaMemcpyHostToDevice, st));
+    }
+    for (int j = 0; j < ql; ++j) {
+      tok_seq[r] = i;
+      tok_pos[r] = pos + j;
+      ++r;
+    }
+    seq_slot[i] = slot;
+    seq_last[i] = r - 1;
+    e->slot_len[slot] = pos + ql;
+  }
+  e->c.kv_pages_free = e->free_pages.size();
+  if (T * 4 <= 2048) {
+    // small batch: one contiguous upload of the whole block would move mostly padding;
+    // the four pieces are tiny, send them separately
+    XB_CUDA(cudaMemcpyAsync(e->d_tok_seq, tok_seq, T * 4, cudaMemcpyHostToDevice, st));
+    XB_CUDA(cudaMemcpyAsync(e->d_tok_pos, tok_pos, T * 4, cudaMemcpyHostToDevice, st));
+    XB_CUDA(cudaMemcpyAsync(e->d_seq_slot, seq_slot, (size_t)2 * d.max_seqs * 4, cudaMemcpyHostToDevice, st));
   } else {
-    XB_CUDA(cudaMemcpyAsync(out, e->h, (size_t)T * D * 2, cudaMemcpyDeviceToDevice, st));
+    XB_CUDA(cudaMemcpyAsync(e->d_meta, hm, e->meta_ints * 4, cudaMemcpyHostToDevice, st));
+  }
+  XB_CUDA(cudaEventRecord(e->meta_ev[ring], st));
+
+  // ---- inputs to fixed addresses
+  if (first) XB_CUDA(cudaMemcpyAsync(e->in_tokens, b->tokens, (size_t)T * 4, cudaMemcpyDeviceToDevice, st));
+  else XB_CUDA(cudaMemcpyAsync(e->h, b->hidden_in, (size_t)T * d.dim * 2, cudaMemcpyDeviceToDevice, st));
+
+  // kv splits: enough blocks to fill the GPU at decode, none needed when T is large
+  int n_splits = 1;
+  {
+    const int blocks = T * d.n_kv_heads;
+    const int pages = (max_ctx + e->page_tokens - 1) / e->page_tokens;
+    if (blocks < 2 * e->num_sms) {
+      n_splits = (2 * e->num_sms + blocks - 1) / blocks;
+      if (n_splits > pages) n_splits = pages;
+      if (n_splits > e->max_attn_splits) n_splits = e->max_attn_splits;
+      if (n_splits < 1) n_splits = 1;
+    }
+  }
+
+  if (decode_only && e->use_graphs && taps == nullptr && st != nullptr && st != cudaStreamLegacy) {
+    // decode step: replay a captured graph (first call of a shape runs eagerly to build the
+    // launch plans and set kernel attributes, second call captures)
+    const long long key = ((long long)b->n_seqs << 16) | n_splits;
+    xb_engine::StepGraph& sg = e->graphs[key];
+    if (sg.exec == nullptr && sg.warmed) {
+      cudaGraph_t graph = nullptr;
+      const uint64_t before = e->c.launches;
+      XB_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+      const int rc = run_body(e, T, b->n_seqs, n_splits, nullptr, st);
+      cudaError_t ce = cudaStreamEndCapture(st, &graph);
+      if (rc != 0) { if (graph) cudaGraphDestroy(graph); return rc; }
+      XB_CUDA(ce);
+      sg.launches = e->c.launches - before;
+      e->c.launches = before;
+      XB_CUDA(cudaGraphInstantiate(&sg.exec, graph, 0));
+      XB_CUDA(cudaGraphDestroy(graph));
+    }
+    if (sg.exec != nullptr) {
+      XB_CUDA(cudaGraphLaunch(sg.exec, st));
+      e->c.launches += sg.launches;
+    } else {
+      XB_TRY(run_body(e, T, b->n_seqs, n_splits, nullptr, st));
+      sg.warmed = 1;
+    }
+  } else {
+    XB_TRY(run_body(e, T, b->n_seqs, n_splits, taps, st));
+  }
+
+  if (out != nullptr) {
+    if (last) XB_CUDA(cudaMemcpyAsync(out, e->logits, (size_t)b->n_seqs * d.vocab * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    else XB_CUDA(cudaMemcpyAsync(out, e->h, (size_t)T * d.dim * 2, cudaMemcpyDeviceToDevice, st));
   }
   e->c.forwards++;
+  return 0;
+}
+
+// Timing hook for the roofline measurement: launches the Linear kernels of one forward over T
+// token rows (QKV, O, gate/up, down per layer, + LM head on a last shard) `iters` times,
+// back to back on `stream`, on the engine's own weights and workspaces.  The caller brackets
+// the call with CUDA events; the launch count is returned in *n_launches.
+extern "C" int xb_bench_linears(xb_engine* e, int T, int iters, int* n_launches, void* stream) {
+  XB_CHECK(e != nullptr && T > 0 && T <= e->d.max_batch_tokens && iters > 0, "bad argument");
+  const xb_model_desc& d = e->d;
+  cudaStream_t st = (cudaStream_t)stream;
+  XB_CUDA(cudaSetDevice(e->device));
+  const bool last = d.end_layer == d.n_layers - 1;
+  const int D = d.dim, I = d.inter_dim;
+  int n = 0;
+  for (int it = 0; it < iters; ++it) {
+    for (int l = 0; l < e->nl; ++l) {
+      const LayerW& w = e->L[l];
+      const GemmPlan* gp;
+      XB_TRY(get_plan(e, SITE_QKV, l, e->hn, D, w.wqkv, T, e->NQKV, D, e->gemm_out, e->NQKV, w.bqkv, 0, &gp));
+      XB_TRY(xb_gemm_run(*gp, st));
+      XB_TRY(get_plan(e, SITE_O, l, e->attn, e->NQ, w.wo, T, D, e->NQ, e->gemm_out, D, nullptr, 0, &gp));
+      XB_TRY(xb_gemm_run(*gp, st));
+      XB_TRY(get_plan(e, SITE_GU, l, e->hn, D, w.wgu, T, 2 * I, D, e->gemm_out, 2 * I, nullptr, 0, &gp));
+      XB_TRY(xb_gemm_run(*gp, st));
+      XB_TRY(get_plan(e, SITE_DOWN, l, e->act, I, w.wdown, T, D, I, e->gemm_out, D, nullptr, 0, &gp));
+      XB_TRY(xb_gemm_run(*gp, st));
+      n += 4;
+    }
+    if (last && T <= d.max_seqs && T <= 128) {
+      const bf16* head = d.tied_head ? e->embed : e->lm_head;
+      const GemmPlan* gp;
+      XB_TRY(get_plan(e, SITE_HEAD, 0, e->last_rows, D, head, T, d.vocab, D, e->logits, d.vocab, nullptr, 1, &gp));
+      XB_TRY(xb_gemm_run(*gp, st));
+      n += 1;
+    }
+  }
+  e->c.launches += n;
+  if (n_launches) *n_launches = n;
   return 0;
 }
 

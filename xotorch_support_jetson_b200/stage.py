@@ -186,6 +186,13 @@ class StageRuntime:
                                    C.c_void_p(out.data_ptr()), C.c_void_p(stream)))
     return out
 
+  def bench_linears(self, T: int, iters: int) -> int:
+    """Enqueue the Linear kernels of one forward `iters` times (xb_bench_linears)."""
+    n = C.c_int()
+    stream = torch.cuda.current_stream(self.device).cuda_stream
+    _cabi.check(self.lib.xb_bench_linears(self._h, int(T), int(iters), C.byref(n), C.c_void_p(stream)))
+    return n.value
+
   def release_slot(self, slot: int):
     _cabi.check(self.lib.xb_kv_release_slot(self._h, slot))
 

@@ -1,0 +1,131 @@
+"""Device capabilities and layer partitioning for one box of B200s.
+
+Mirrors the parts of the reference's ``xotorch/topology`` the hot path depends on:
+``DeviceCapabilities`` / ``DeviceFlops`` (``device_capabilities.py:22-52``), ``Topology``
+(``topology.py:22-45``), ``Partition`` + ``map_partitions_to_shards``
+(``partitioning_strategy.py:11-42``) and ``RingMemoryWeightedPartitioningStrategy``
+(``ring_memory_weighted_partitioning_strategy.py:7-18``).  The one change north_star asks
+for: a multi-GPU host is exposed as ONE NODE PER GPU (the reference collapses all GPUs of
+a host into one node, ``device_capabilities.py:214-252``) and ``CHIP_FLOPS`` knows B200.
+"""
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional
+
+from .shard import Shard
+
+TFLOPS = 1.00
+
+
+@dataclass
+class DeviceFlops:
+  fp32: float
+  fp16: float
+  int8: float
+
+  def to_dict(self):
+    return {"fp32": self.fp32, "fp16": self.fp16, "int8": self.int8}
+
+
+@dataclass
+class DeviceCapabilities:
+  model: str
+  chip: str
+  memory: int  # MB
+  flops: DeviceFlops
+
+  def __post_init__(self):
+    if isinstance(self.flops, dict):
+      self.flops = DeviceFlops(**self.flops)
+
+  def to_dict(self):
+    return {"model": self.model, "chip": self.chip, "memory": self.memory, "flops": self.flops.to_dict()}
+
+
+# dense peaks (TFLOPS); fp16 = bf16/fp16 tensor, int8 slot carries the fp8 tensor figure
+CHIP_FLOPS = {
+  "NVIDIA B200": DeviceFlops(fp32=80.0 * TFLOPS, fp16=2250.0 * TFLOPS, int8=4500.0 * TFLOPS),
+}
+UNKNOWN_DEVICE_CAPABILITIES = DeviceCapabilities(model="Unknown Model", chip="Unknown Chip", memory=0,
+                                                 flops=DeviceFlops(fp32=0, fp16=0, int8=0))
+
+
+def b200_device_capabilities(memory_mb: int = 183359) -> DeviceCapabilities:
+  return DeviceCapabilities(model="Linux Box (NVIDIA B200)", chip="NVIDIA B200", memory=memory_mb,
+                            flops=CHIP_FLOPS["NVIDIA B200"])
+
+
+def local_gpu_capabilities() -> List[DeviceCapabilities]:
+  """One DeviceCapabilities per visible GPU (one node per GPU)."""
+  import torch
+  out = []
+  for i in range(torch.cuda.device_count()):
+    p = torch.cuda.get_device_properties(i)
+    name = p.name
+    out.append(DeviceCapabilities(model=f"Linux Box ({name})", chip=name, memory=p.total_memory // 2**20,
+                                  flops=CHIP_FLOPS.get(name, DeviceFlops(fp32=0, fp16=0, int8=0))))
+  return out
+
+
+class Topology:
+  def __init__(self):
+    self.nodes: Dict[str, DeviceCapabilities] = {}
+    self.active_node_id: Optional[str] = None
+
+  def update_node(self, node_id: str, device_capabilities: DeviceCapabilities):
+    self.nodes[node_id] = device_capabilities
+
+  def get_node(self, node_id: str) -> DeviceCapabilities:
+    return self.nodes.get(node_id)
+
+  def all_nodes(self):
+    return self.nodes.items()
+
+
+@dataclass
+class Partition:
+  node_id: str
+  start: float
+  end: float
+
+
+class RingMemoryWeightedPartitioningStrategy:
+  def partition(self, topology: Topology) -> List[Partition]:
+    nodes = list(topology.all_nodes())
+    nodes.sort(key=lambda x: (x[1].memory, x[0]), reverse=True)
+    total_memory = sum(node[1].memory for node in nodes)
+    partitions = []
+    start = 0
+    for node in nodes:
+      end = round(start + (node[1].memory / total_memory), 5)
+      partitions.append(Partition(node[0], start, end))
+      start = end
+    return partitions
+
+
+def map_partitions_to_shards(partitions: List[Partition], num_layers: int, model_id: str) -> List[Shard]:
+  shards = []
+  for i, partition in enumerate(partitions):
+    start_layer = int(partition.start * num_layers)
+    end_layer = int(partition.end * num_layers) - 1
+    if i == len(partitions) - 1:
+      end_layer = num_layers - 1
+    if start_layer <= end_layer:
+      shards.append(Shard(model_id, start_layer, end_layer, num_layers))
+  if shards and shards[-1].end_layer < num_layers - 1:
+    shards[-1] = Shard(model_id, shards[-1].start_layer, num_layers - 1, num_layers)
+  return shards
+
+
+def box_topology(n_gpus: int, memory_mb: int = 183359) -> Topology:
+  """n equal B200 nodes named so that the ring order (memory desc, node id desc) is gpu0, gpu1, ..."""
+  t = Topology()
+  for i in range(n_gpus):
+    t.update_node(f"gpu{n_gpus - 1 - i:02d}-rank{i}", b200_device_capabilities(memory_mb))
+  return t
+
+
+def pipeline_shards(model_id: str, n_layers: int, n_gpus: int) -> List[Shard]:
+  """Layer ranges of an n_gpus pipeline, exactly what the reference's ring strategy +
+  map_partitions_to_shards assign to n equal-memory peers; entry i belongs to rank i."""
+  parts = RingMemoryWeightedPartitioningStrategy().partition(box_topology(n_gpus))
+  return map_partitions_to_shards(parts, n_layers, model_id)
