@@ -117,9 +117,14 @@ def test_ragged_batch_equals_single_sequence_runs(built_lib):
   t1 = st.sample(lg, temp=0.0)
   lg2 = st.forward([0, 1, 2], [1, 1, 1], lens, tokens=t1)
   torch.cuda.synchronize()
+  # The split-K factor of a Linear depends on the number of token rows in the call, so the
+  # fp32 summation order (and a few bf16 roundings downstream) may differ between a batched
+  # and a single-sequence run: equal within a small fraction of the stated tolerance.
   for i in range(3):
-    assert torch.equal(lg[i], singles[i][0][0]), f"prefill logits of seq {i} differ between batched and single run"
-    assert torch.equal(lg2[i], singles[i][1][0]), f"decode logits of seq {i} differ between batched and single run"
+    a, b = lg[i].cpu().numpy(), singles[i][0][0].cpu().numpy()
+    assert _rel(a, b) < REL_TOL / 2, f"prefill logits of seq {i} differ between batched and single run: {_rel(a, b)}"
+    a, b = lg2[i].cpu().numpy(), singles[i][1][0].cpu().numpy()
+    assert _rel(a, b) < REL_TOL / 2, f"decode logits of seq {i} differ between batched and single run: {_rel(a, b)}"
   st.close()
 
 

@@ -4,6 +4,7 @@
 #include "xb_common.cuh"
 #include "xb_gemm.cuh"
 #include "xb_kernels.cuh"
+#include "xb_attn_mma.cuh"
 
 #include <stdarg.h>
 #include <stdlib.h>
@@ -26,6 +27,7 @@ struct LayerW {
   bf16 *wqkv = nullptr, *bqkv = nullptr, *wo = nullptr, *wgu = nullptr, *wdown = nullptr;
   bf16 *sa_norm = nullptr, *mlp_norm = nullptr;
   bf16 *k_pool = nullptr, *v_pool = nullptr;
+  CUtensorMap tmK, tmV;   // [n_pages*KV*page_tokens, head_dim] views of the pools, boxes of min(page,64) x 64
 };
 
 enum Site { SITE_QKV = 0, SITE_O, SITE_GU, SITE_DOWN, SITE_HEAD };
@@ -50,6 +52,8 @@ struct xb_engine {
   // H2D copy per forward from a ring of pinned host buffers
   int* d_meta = nullptr;
   int *d_tok_seq = nullptr, *d_tok_pos = nullptr, *d_seq_slot = nullptr, *d_seq_last = nullptr;
+  int *d_tile_start = nullptr, *d_tile_len = nullptr;
+  int max_tiles = 0, tile_tokens = 0;   // prefill query tiles: tile_tokens = 128 / group size
   static constexpr int META_RING = 8;
   int* h_meta_ring[META_RING] = {nullptr};
   cudaEvent_t meta_ev[META_RING] = {nullptr};
@@ -67,7 +71,7 @@ struct xb_engine {
   void* gemm_out = nullptr;
   size_t gemm_out_bytes = 0;
   float *o_part = nullptr, *ml_part = nullptr;
-  int max_attn_splits = 16;
+  int max_attn_splits = 32;
   std::map<long long, GemmPlan> plans;
   xb_counters c{};
 };
@@ -97,7 +101,8 @@ extern "C" int xb_engine_create(const xb_model_desc* desc, int device, xb_engine
   XB_CHECK(d.start_layer >= 0 && d.end_layer >= d.start_layer && d.end_layer < d.n_layers, "bad layer range [%d,%d] of %d",
            d.start_layer, d.end_layer, d.n_layers);
   XB_CHECK(d.head_dim == 64 || d.head_dim == 128, "head_dim %d not supported (64 or 128)", d.head_dim);
-  XB_CHECK(d.n_heads % d.n_kv_heads == 0, "n_heads %d not a multiple of n_kv_heads %d", d.n_heads, d.n_kv_heads);
+  XB_CHECK(d.n_heads % d.n_kv_heads == 0 && d.n_heads / d.n_kv_heads <= 8, "n_heads %d must be 1..8 x n_kv_heads %d",
+           d.n_heads, d.n_kv_heads);
   XB_CHECK(d.dim % 8 == 0 && d.inter_dim % 8 == 0, "dim/inter_dim must be multiples of 8");
   XB_CHECK(d.max_batch_tokens > 0 && d.max_seqs > 0 && d.max_positions > 0, "max_batch_tokens/max_seqs/max_positions must be > 0");
   xb_engine* e = new xb_engine();
@@ -153,12 +158,16 @@ extern "C" int xb_engine_create(const xb_model_desc* desc, int device, xb_engine
   const size_t Tsplit = T < (size_t)2 * e->num_sms ? T : (size_t)2 * e->num_sms;
   XB_TRY(dmalloc((void**)&e->o_part, Tsplit * d.n_heads * e->max_attn_splits * d.head_dim * sizeof(float)));
   XB_TRY(dmalloc((void**)&e->ml_part, Tsplit * d.n_heads * e->max_attn_splits * 2 * sizeof(float)));
-  e->meta_ints = 2 * T + 2 * (size_t)d.max_seqs;
+  e->tile_tokens = 128 / (d.n_heads / d.n_kv_heads);
+  e->max_tiles = (int)(T / e->tile_tokens) + d.max_seqs + 1;
+  e->meta_ints = 2 * T + 2 * (size_t)d.max_seqs + 2 * (size_t)e->max_tiles;
   XB_TRY(dmalloc((void**)&e->d_meta, e->meta_ints * 4));
   e->d_tok_seq = e->d_meta;
   e->d_tok_pos = e->d_meta + T;
   e->d_seq_slot = e->d_meta + 2 * T;
   e->d_seq_last = e->d_meta + 2 * T + d.max_seqs;
+  e->d_tile_start = e->d_meta + 2 * T + 2 * d.max_seqs;
+  e->d_tile_len = e->d_tile_start + e->max_tiles;
   for (int i = 0; i < xb_engine::META_RING; ++i) {
     XB_CUDA(cudaMallocHost((void**)&e->h_meta_ring[i], e->meta_ints * 4));
     XB_CUDA(cudaEventCreateWithFlags(&e->meta_ev[i], cudaEventDisableTiming));
@@ -239,6 +248,8 @@ extern "C" int xb_load_weight(xb_engine* e, int layer, int kind, const void* src
 extern "C" int xb_kv_reserve(xb_engine* e, int n_slots, int max_tokens_per_slot, int page_tokens) {
   XB_CHECK(e != nullptr, "null engine");
   XB_CHECK(n_slots > 0 && max_tokens_per_slot > 0 && page_tokens > 0, "bad kv_reserve arguments");
+  XB_CHECK(page_tokens % 8 == 0 && (page_tokens >= 64 ? page_tokens % 64 == 0 : 64 % page_tokens == 0),
+           "page_tokens must be 8, 16, 32 or a multiple of 64 (got %d)", page_tokens);
   XB_CUDA(cudaSetDevice(e->device));
   XB_CUDA(cudaDeviceSynchronize());
   for (LayerW& w : e->L) {
@@ -256,9 +267,17 @@ extern "C" int xb_kv_reserve(xb_engine* e, int n_slots, int max_tokens_per_slot,
   e->max_pages = (max_tokens_per_slot + page_tokens - 1) / page_tokens;
   e->n_pages = n_slots * e->max_pages;
   const size_t pool_bytes = (size_t)e->n_pages * e->NKV * page_tokens * 2;
+  const long long pool_rows = (long long)e->n_pages * e->d.n_kv_heads * page_tokens;
   for (LayerW& w : e->L) {
     XB_TRY(dmalloc((void**)&w.k_pool, pool_bytes));
     XB_TRY(dmalloc((void**)&w.v_pool, pool_bytes));
+    // zeroed ONCE here (never per prompt): rows of a page beyond a sequence's length are
+    // read by the attention tiles and masked; they must hold finite values
+    XB_CUDA(cudaMemset(w.k_pool, 0, pool_bytes));
+    XB_CUDA(cudaMemset(w.v_pool, 0, pool_bytes));
+    const int box_rows = page_tokens < 64 ? page_tokens : 64;
+    XB_TRY(xb_make_tmap(&w.tmK, w.k_pool, pool_rows, e->d.head_dim, e->d.head_dim, box_rows));
+    XB_TRY(xb_make_tmap(&w.tmV, w.v_pool, pool_rows, e->d.head_dim, e->d.head_dim, box_rows));
   }
   e->free_pages.clear();
   for (int p = e->n_pages - 1; p >= 0; --p) e->free_pages.push_back(p);
@@ -305,30 +324,84 @@ static int get_plan(xb_engine* e, int site, int layer, const bf16* x, long long 
   return 0;
 }
 
-template <int HD>
-static int launch_attn(xb_engine* e, const LayerW& w, const BatchMeta& m, int T, int n_splits, cudaStream_t st) {
+template <int HD, int G>
+static int launch_attn_g(xb_engine* e, const LayerW& w, const BatchMeta& m, int T, int n_splits, int n_tiles,
+                         cudaStream_t st) {
   const xb_model_desc& d = e->d;
-  const int G = d.n_heads / d.n_kv_heads;
-  const float scale = 1.0f / sqrtf((float)d.head_dim);
-  dim3 grid(T, d.n_kv_heads, n_splits);
-#define XB_ATTN_CASE(GG)                                                                                            \
-  case GG:                                                                                                          \
-    xb_attn_split_kernel<HD, GG><<<grid, 128, 0, st>>>(e->q, w.k_pool, w.v_pool, m, e->o_part, e->ml_part, e->attn, \
-                                                       d.n_heads, d.n_kv_heads, n_splits, scale);                   \
-    break;
-  switch (G) {
-    XB_ATTN_CASE(1) XB_ATTN_CASE(2) XB_ATTN_CASE(3) XB_ATTN_CASE(4) XB_ATTN_CASE(5) XB_ATTN_CASE(6) XB_ATTN_CASE(7)
-    XB_ATTN_CASE(8)
-    default: return xb_fail(1, "GQA group size %d not supported (1..8)", G);
-  }
-#undef XB_ATTN_CASE
-  XB_CUDA(cudaGetLastError());
-  LAUNCH_COUNT(e);
-  if (n_splits > 1) {
-    xb_attn_combine_kernel<<<T * d.n_heads, d.head_dim, 0, st>>>(e->o_part, e->ml_part, e->attn, n_splits, d.head_dim);
+  const float scale_log2 = (1.0f / sqrtf((float)d.head_dim)) * 1.4426950408889634f;
+  constexpr int NST = 3;
+  if (n_tiles == 0) {
+    // decode: one block per (token, kv head, kv split)
+    using Cfg = AttDecCfg<HD, G, NST>;
+    static bool attr_set = false;
+    if (!attr_set) {
+      XB_CUDA(cudaFuncSetAttribute(xb_attn_decode_mma_kernel<HD, G, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   Cfg::SMEM_BYTES));
+      attr_set = true;
+    }
+    dim3 grid(T, d.n_kv_heads, n_splits);
+    xb_attn_decode_mma_kernel<HD, G, NST><<<grid, 160, Cfg::SMEM_BYTES, st>>>(w.tmK, w.tmV, e->q, m, e->o_part, e->ml_part,
+                                                                              e->attn, d.n_heads, d.n_kv_heads, n_splits,
+                                                                              scale_log2);
+    XB_CUDA(cudaGetLastError());
+    LAUNCH_COUNT(e);
+    if (n_splits > 1) {
+      const int rows = T * d.n_heads;
+      xb_attn_combine2_kernel<HD><<<(rows + 3) / 4, 128, 0, st>>>(e->o_part, e->ml_part, e->attn, n_splits, rows);
+      XB_CUDA(cudaGetLastError());
+      LAUNCH_COUNT(e);
+    }
+  } else {
+    // prefill: one block per (query tile, kv head)
+    using Cfg = AttPreCfg<HD, NST>;
+    static bool attr_set = false;
+    if (!attr_set) {
+      XB_CUDA(cudaFuncSetAttribute(xb_attn_prefill_mma_kernel<HD, G, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   Cfg::SMEM_BYTES));
+      attr_set = true;
+    }
+    dim3 grid(n_tiles, d.n_kv_heads);
+    xb_attn_prefill_mma_kernel<HD, G, NST><<<grid, 288, Cfg::SMEM_BYTES, st>>>(w.tmK, w.tmV, e->q, m, m.tile_start, m.tile_len,
+                                                                               e->attn, d.n_heads, d.n_kv_heads, scale_log2);
     XB_CUDA(cudaGetLastError());
     LAUNCH_COUNT(e);
   }
+  return 0;
+}
+
+template <int HD>
+static int launch_attn(xb_engine* e, const LayerW& w, const BatchMeta& m, int T, int n_splits, int n_tiles, cudaStream_t st) {
+  switch (e->d.n_heads / e->d.n_kv_heads) {
+    case 1: return launch_attn_g<HD, 1>(e, w, m, T, n_splits, n_tiles, st);
+    case 2: return launch_attn_g<HD, 2>(e, w, m, T, n_splits, n_tiles, st);
+    case 3: return launch_attn_g<HD, 3>(e, w, m, T, n_splits, n_tiles, st);
+    case 4: return launch_attn_g<HD, 4>(e, w, m, T, n_splits, n_tiles, st);
+    case 5: return launch_attn_g<HD, 5>(e, w, m, T, n_splits, n_tiles, st);
+    case 6: return launch_attn_g<HD, 6>(e, w, m, T, n_splits, n_tiles, st);
+    case 7: return launch_attn_g<HD, 7>(e, w, m, T, n_splits, n_tiles, st);
+    case 8: return launch_attn_g<HD, 8>(e, w, m, T, n_splits, n_tiles, st);
+  }
+  return xb_fail(1, "GQA group size %d not supported (1..8)", e->d.n_heads / e->d.n_kv_heads);
+}
+
+template <int CL, int NT, int VPT>
+static int launch_resid_norm_cluster(xb_engine* e, const GemmPlan* gp, int T, const bf16* nw, cudaStream_t st) {
+  const xb_model_desc& d = e->d;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(CL, T, 1);
+  cfg.blockDim = dim3(NT, 1, 1);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CL;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  XB_CUDA(cudaLaunchKernelEx(&cfg, xb_resid_norm_cluster_kernel<CL, NT, VPT>, (const float*)e->gemm_out, gp->args.splits,
+                             (long long)T * d.dim, e->h, nw, e->hn, d.dim, d.norm_eps, d.rmsnorm_two_round));
+  LAUNCH_COUNT(e);
   return 0;
 }
 
@@ -336,6 +409,10 @@ static int launch_resid_norm(xb_engine* e, const GemmPlan* gp, int T, const bf16
   const xb_model_desc& d = e->d;
   const size_t smem = (size_t)d.dim * sizeof(float);
   if (gp->args.mode == XB_GEMM_SKINNY) {
+    // decode-sized batches: one 8-block cluster per row (columns split over 8 SMs)
+    if (d.dim % 32 == 0 && d.dim / 8 <= 128 * 4 * 2)
+      return d.dim / 8 <= 128 * 4 ? launch_resid_norm_cluster<8, 128, 1>(e, gp, T, nw, st)
+                                  : launch_resid_norm_cluster<8, 128, 2>(e, gp, T, nw, st);
     xb_resid_norm_kernel<256, 0><<<T, 256, smem, st>>>((const float*)e->gemm_out, gp->args.splits, (long long)T * d.dim,
                                                         nullptr, e->h, nw, e->hn, d.dim, d.norm_eps, d.rmsnorm_two_round);
   } else {
@@ -351,7 +428,7 @@ static int launch_resid_norm(xb_engine* e, const GemmPlan* gp, int T, const bf16
 // e->h (other shards); leaves the residual stream in e->h and, on a last shard, the logits
 // of each sequence's last position in e->logits.  Pure stream work on fixed addresses, so it
 // can be captured into a CUDA graph.
-static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, void* const* taps, cudaStream_t st) {
+static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, void* const* taps, cudaStream_t st) {
   const xb_model_desc& d = e->d;
   const bool first = d.start_layer == 0, last = d.end_layer == d.n_layers - 1;
   BatchMeta m;
@@ -360,6 +437,8 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, void* const* 
   m.seq_slot = e->d_seq_slot;
   m.seq_last = e->d_seq_last;
   m.page_table = e->d_page_table;
+  m.tile_start = e->d_tile_start;
+  m.tile_len = e->d_tile_len;
   m.max_pages = e->max_pages;
   m.page_tokens = e->page_tokens;
   const int D = d.dim, I = d.inter_dim, hd = d.head_dim;
@@ -393,8 +472,8 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, void* const* 
       XB_CUDA(cudaGetLastError());
       LAUNCH_COUNT(e);
     }
-    if (hd == 128) XB_TRY(launch_attn<128>(e, w, m, T, n_splits, st));
-    else XB_TRY(launch_attn<64>(e, w, m, T, n_splits, st));
+    if (hd == 128) XB_TRY(launch_attn<128>(e, w, m, T, n_splits, n_tiles, st));
+    else XB_TRY(launch_attn<64>(e, w, m, T, n_splits, n_tiles, st));
     // output projection + residual + mlp_norm
     XB_TRY(get_plan(e, SITE_O, l, e->attn, e->NQ, w.wo, T, D, e->NQ, e->gemm_out, D, nullptr, 0, &gp));
     XB_TRY(xb_gemm_run(*gp, st));
@@ -476,6 +555,9 @@ extern "C" int xb_forward(xb_engine* e, const xb_batch* b, void* out, void* cons
   int* tok_pos = hm + Tmax;
   int* seq_slot = hm + 2 * Tmax;
   int* seq_last = hm + 2 * Tmax + d.max_seqs;
+  int* tile_start = hm + 2 * Tmax + 2 * d.max_seqs;
+  int* tile_len = tile_start + e->max_tiles;
+  int n_tiles = 0;
   int r = 0;
   for (int i = 0; i < b->n_seqs; ++i) {
     const int slot = b->slot_ids[i], ql = b->q_lens[i], pos = b->positions[i];
@@ -495,6 +577,13 @@ extern "C" int xb_forward(xb_engine* e, const xb_batch* b, void* out, void* cons
                               e->h_page_table.data() + (size_t)slot * e->max_pages + old, (need_pages - old) * 4,
                               cudaMemcpyHostToDevice, st));
     }
+    if (!decode_only) {
+      for (int j = 0; j < ql; j += e->tile_tokens) {
+        tile_start[n_tiles] = r + j;
+        tile_len[n_tiles] = ql - j < e->tile_tokens ? ql - j : e->tile_tokens;
+        ++n_tiles;
+      }
+    }
     for (int j = 0; j < ql; ++j) {
       tok_seq[r] = i;
       tok_pos[r] = pos + j;
@@ -505,9 +594,9 @@ extern "C" int xb_forward(xb_engine* e, const xb_batch* b, void* out, void* cons
     e->slot_len[slot] = pos + ql;
   }
   e->c.kv_pages_free = e->free_pages.size();
-  if (T * 4 <= 2048) {
+  if (decode_only && T * 4 <= 2048) {
     // small batch: one contiguous upload of the whole block would move mostly padding;
-    // the four pieces are tiny, send them separately
+    // the pieces are tiny, send them separately
     XB_CUDA(cudaMemcpyAsync(e->d_tok_seq, tok_seq, T * 4, cudaMemcpyHostToDevice, st));
     XB_CUDA(cudaMemcpyAsync(e->d_tok_pos, tok_pos, T * 4, cudaMemcpyHostToDevice, st));
     XB_CUDA(cudaMemcpyAsync(e->d_seq_slot, seq_slot, (size_t)2 * d.max_seqs * 4, cudaMemcpyHostToDevice, st));
@@ -520,17 +609,18 @@ extern "C" int xb_forward(xb_engine* e, const xb_batch* b, void* out, void* cons
   if (first) XB_CUDA(cudaMemcpyAsync(e->in_tokens, b->tokens, (size_t)T * 4, cudaMemcpyDeviceToDevice, st));
   else XB_CUDA(cudaMemcpyAsync(e->h, b->hidden_in, (size_t)T * d.dim * 2, cudaMemcpyDeviceToDevice, st));
 
-  // kv splits: enough blocks to fill the GPU at decode, none needed when T is large
+  // decode: split each context so that a block streams ~8 key tiles and the grid holds at least
+  // two blocks per SM; prefill: one block per (query tile, kv head), no kv split
   int n_splits = 1;
-  {
+  if (decode_only) {
+    XB_CHECK(T <= 2 * e->num_sms, "decode batch of %d sequences exceeds the %d the split-KV workspace covers", T, 2 * e->num_sms);
     const int blocks = T * d.n_kv_heads;
-    const int pages = (max_ctx + e->page_tokens - 1) / e->page_tokens;
-    if (blocks < 2 * e->num_sms) {
-      n_splits = (2 * e->num_sms + blocks - 1) / blocks;
-      if (n_splits > pages) n_splits = pages;
-      if (n_splits > e->max_attn_splits) n_splits = e->max_attn_splits;
-      if (n_splits < 1) n_splits = 1;
-    }
+    const int tiles = (max_ctx + XB_ATT_TILE - 1) / XB_ATT_TILE;
+    const int fill = (2 * e->num_sms + blocks - 1) / blocks;
+    n_splits = (tiles + 7) / 8 > fill ? (tiles + 7) / 8 : fill;
+    if (n_splits > tiles) n_splits = tiles;
+    if (n_splits > e->max_attn_splits) n_splits = e->max_attn_splits;
+    if (n_splits < 1) n_splits = 1;
   }
 
   if (decode_only && e->use_graphs && taps == nullptr && st != nullptr && st != cudaStreamLegacy) {
@@ -542,7 +632,7 @@ extern "C" int xb_forward(xb_engine* e, const xb_batch* b, void* out, void* cons
       cudaGraph_t graph = nullptr;
       const uint64_t before = e->c.launches;
       XB_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-      const int rc = run_body(e, T, b->n_seqs, n_splits, nullptr, st);
+      const int rc = run_body(e, T, b->n_seqs, n_splits, 0, nullptr, st);
       cudaError_t ce = cudaStreamEndCapture(st, &graph);
       if (rc != 0) { if (graph) cudaGraphDestroy(graph); return rc; }
       XB_CUDA(ce);
@@ -555,11 +645,11 @@ extern "C" int xb_forward(xb_engine* e, const xb_batch* b, void* out, void* cons
       XB_CUDA(cudaGraphLaunch(sg.exec, st));
       e->c.launches += sg.launches;
     } else {
-      XB_TRY(run_body(e, T, b->n_seqs, n_splits, nullptr, st));
+      XB_TRY(run_body(e, T, b->n_seqs, n_splits, 0, nullptr, st));
       sg.warmed = 1;
     }
   } else {
-    XB_TRY(run_body(e, T, b->n_seqs, n_splits, taps, st));
+    XB_TRY(run_body(e, T, b->n_seqs, n_splits, n_tiles, taps, st));
   }
 
   if (out != nullptr) {

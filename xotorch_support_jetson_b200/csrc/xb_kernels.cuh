@@ -1,6 +1,6 @@
 // Memory-bound kernels of the layer-range forward: embedding gather, fused
 // (split-K reduce +) residual + RMSNorm, QKV finalize (bias + RoPE + paged-KV append),
-// SiLU*up, split-KV attention over the paged cache, and on-device sampling.
+// SiLU*up and on-device sampling (attention lives in xb_attn_mma.cuh).
 //
 // Every "rounding point" follows the reference's eager bf16 graph:
 // each nn.Linear output, RoPE output, attention output, residual sum, RMSNorm output,
@@ -17,6 +17,8 @@ struct BatchMeta {
   const int* seq_slot;    // [n_seqs] KV slot of each sequence
   const int* seq_last;    // [n_seqs] row index of the last token of each sequence
   const int* page_table;  // [n_slots, max_pages] page ids
+  const int* tile_start;  // [n_tiles] first token row of each prefill query tile
+  const int* tile_len;    // [n_tiles] tokens in the tile (<= 128 / group size, one sequence)
   int max_pages;
   int page_tokens;
 };
@@ -120,6 +122,78 @@ __global__ void __launch_bounds__(NT) xb_resid_norm_kernel(const float* __restri
   }
 }
 
+// Small-T variant: one CLUSTER of CL blocks per token row, each block owning D/CL columns, so
+// a decode step (T = 1..128 rows) spreads over CL*T SMs instead of T.  The row's sum of
+// squares is exchanged through distributed shared memory.  Same arithmetic and rounding
+// points as xb_resid_norm_kernel<., 0>; the split partials are summed in split order.
+template <int CL, int NT, int VPT>
+__global__ void __launch_bounds__(NT) xb_resid_norm_cluster_kernel(const float* __restrict__ part, int splits,
+                                                                   long long split_stride, bf16* __restrict__ h,
+                                                                   const bf16* __restrict__ nw, bf16* __restrict__ hn,
+                                                                   int D, float eps, int two_round) {
+  __shared__ float red[32];
+  __shared__ float cl_part[CL];
+  const int t = blockIdx.y;
+  uint32_t rank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  const int cols = D / CL;                      // columns of this block (multiple of 4)
+  const int c0 = rank * cols;
+  float v[VPT][4];
+  float ss = 0.f;
+#pragma unroll
+  for (int it = 0; it < VPT; ++it) {
+    const int c = (it * NT + threadIdx.x) * 4;
+    v[it][0] = v[it][1] = v[it][2] = v[it][3] = 0.f;
+    if (c < cols) {
+      const long long o = (long long)t * D + c0 + c;
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int s = 0; s < splits; ++s) {
+        const float4 p = *reinterpret_cast<const float4*>(part + s * split_stride + o);
+        a.x += p.x; a.y += p.y; a.z += p.z; a.w += p.w;
+      }
+      const uint2 hu = *reinterpret_cast<const uint2*>(h + o);
+      const float2 h0 = bf2_to_f2(hu.x), h1 = bf2_to_f2(hu.y);
+      v[it][0] = rbf(h0.x + rbf(a.x));
+      v[it][1] = rbf(h0.y + rbf(a.y));
+      v[it][2] = rbf(h1.x + rbf(a.z));
+      v[it][3] = rbf(h1.y + rbf(a.w));
+      uint2 ho;
+      ho.x = f2_to_bf2(v[it][0], v[it][1]);
+      ho.y = f2_to_bf2(v[it][2], v[it][3]);
+      *reinterpret_cast<uint2*>(h + o) = ho;
+      ss += v[it][0] * v[it][0] + v[it][1] * v[it][1] + v[it][2] * v[it][2] + v[it][3] * v[it][3];
+    }
+  }
+  if (nw == nullptr) return;   // uniform across the cluster
+  ss = block_sum<NT>(ss, red);
+  // publish this block's partial to every block of the cluster (DSMEM store), then cluster barrier
+  if (threadIdx.x < CL) {
+    uint32_t local = smem_u32(&cl_part[rank]);
+    uint32_t remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"((uint32_t)threadIdx.x));
+    asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote), "f"(ss) : "memory");
+  }
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+  float tot = 0.f;
+#pragma unroll
+  for (int i = 0; i < CL; ++i) tot += cl_part[i];
+  const float inv = 1.0f / sqrtf(tot / (float)D + eps);
+#pragma unroll
+  for (int it = 0; it < VPT; ++it) {
+    const int c = (it * NT + threadIdx.x) * 4;
+    if (c < cols) {
+      const long long o = (long long)t * D + c0 + c;
+      const uint2 wu = *reinterpret_cast<const uint2*>(nw + c0 + c);
+      const float2 w0 = bf2_to_f2(wu.x), w1 = bf2_to_f2(wu.y);
+      uint2 r;
+      r.x = f2_to_bf2(rms_apply(v[it][0], inv, w0.x, two_round), rms_apply(v[it][1], inv, w0.y, two_round));
+      r.y = f2_to_bf2(rms_apply(v[it][2], inv, w1.x, two_round), rms_apply(v[it][3], inv, w1.y, two_round));
+      *reinterpret_cast<uint2*>(hn + o) = r;
+    }
+  }
+}
+
 // ----------------------------------------------------------------------------- QKV finalize
 // One block per (token, head) over the fused [q | k | v] projection output.
 //   value = bf16(sum_splits(partial) + bias)        (nn.Linear rounding; SRC = 0)
@@ -216,147 +290,6 @@ __global__ void xb_silu_mul_kernel(const float* __restrict__ part, int splits, l
   }
   const float sg = rbf(g / (1.0f + expf(-g)));
   act[idx] = f2bf(sg * u);
-}
-
-// ----------------------------------------------------------------------------- attention over the paged cache
-// One block per (token row, kv head, kv split).  The G = H/KV query heads that share the
-// kv head are processed together so K and V are read once per group (the reference
-// materialises the expanded [B,H,C,hd] copies instead).  Keys [0, pos] are
-// attended (causal); masked/unfilled cache slots of the reference contribute exp(-inf)=0.
-// 16 lanes x 8 dims cover one 128-wide row with one 128-bit load per lane; a warp walks
-// two keys per step.  fp32 online softmax; partial (m, l, acc) per split.
-template <int HD, int G>
-__global__ void __launch_bounds__(128) xb_attn_split_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pool,
-                                                            const bf16* __restrict__ v_pool, BatchMeta m,
-                                                            float* __restrict__ o_part, float* __restrict__ ml_part,
-                                                            bf16* __restrict__ out, int H, int KV, int n_splits,
-                                                            float scale) {
-  constexpr int LPK = HD / 8;            // lanes per key row (16 for hd=128, 8 for hd=64)
-  constexpr int KPW = 32 / LPK;          // keys per warp step
-  const int t = blockIdx.x, kvh = blockIdx.y, sp = blockIdx.z;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int sub = lane / LPK;            // which key of the step
-  const int dl = lane % LPK;             // which 8-dim slice
-  const int pos = m.tok_pos[t];
-  const int ctx = pos + 1;
-  const int slot = m.seq_slot[m.tok_seq[t]];
-  const int* pt = m.page_table + (long long)slot * m.max_pages;
-  const int P = m.page_tokens;
-  // split the context in chunks of whole pages
-  const int n_pages = (ctx + P - 1) / P;
-  const int pg0 = (int)(((long long)sp * n_pages) / n_splits);
-  const int pg1 = (int)(((long long)(sp + 1) * n_pages) / n_splits);
-  const int k_begin = pg0 * P;
-  const int k_end = min(pg1 * P, ctx);
-
-  float qf[G][8];
-#pragma unroll
-  for (int g = 0; g < G; ++g) {
-    const uint4 u = *reinterpret_cast<const uint4*>(q + ((long long)t * H + (kvh * G + g)) * HD + dl * 8);
-    float2 a = bf2_to_f2(u.x), b = bf2_to_f2(u.y), c = bf2_to_f2(u.z), d = bf2_to_f2(u.w);
-    qf[g][0] = a.x; qf[g][1] = a.y; qf[g][2] = b.x; qf[g][3] = b.y;
-    qf[g][4] = c.x; qf[g][5] = c.y; qf[g][6] = d.x; qf[g][7] = d.y;
-  }
-  float mx[G], l[G], acc[G][8];
-#pragma unroll
-  for (int g = 0; g < G; ++g) {
-    mx[g] = -INFINITY;
-    l[g] = 0.f;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) acc[g][j] = 0.f;
-  }
-
-  for (int kb = k_begin + warp * KPW; kb < k_end; kb += 4 * KPW) {
-    const int key = kb + sub;
-    const bool valid = key < k_end;
-    uint4 ku = make_uint4(0, 0, 0, 0), vu = make_uint4(0, 0, 0, 0);
-    if (valid) {
-      const int page = pt[key / P];
-      const long long off = (((long long)page * KV + kvh) * P + (key % P)) * HD + dl * 8;
-      ku = ld_nc_v4(k_pool + off);
-      vu = ld_nc_v4(v_pool + off);
-    }
-    float kf[8], vf[8];
-    {
-      float2 a = bf2_to_f2(ku.x), b = bf2_to_f2(ku.y), c = bf2_to_f2(ku.z), d = bf2_to_f2(ku.w);
-      kf[0] = a.x; kf[1] = a.y; kf[2] = b.x; kf[3] = b.y; kf[4] = c.x; kf[5] = c.y; kf[6] = d.x; kf[7] = d.y;
-      a = bf2_to_f2(vu.x); b = bf2_to_f2(vu.y); c = bf2_to_f2(vu.z); d = bf2_to_f2(vu.w);
-      vf[0] = a.x; vf[1] = a.y; vf[2] = b.x; vf[3] = b.y; vf[4] = c.x; vf[5] = c.y; vf[6] = d.x; vf[7] = d.y;
-    }
-#pragma unroll
-    for (int g = 0; g < G; ++g) {
-      float s = 0.f;
-#pragma unroll
-      for (int j = 0; j < 8; ++j) s = fmaf(qf[g][j], kf[j], s);
-#pragma unroll
-      for (int o = LPK / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-      s = valid ? s * scale : -INFINITY;
-      const float mn = fmaxf(mx[g], s);
-      if (mn > -INFINITY) {
-        const float corr = __expf(mx[g] - mn);
-        const float p = __expf(s - mn);
-        l[g] = l[g] * corr + p;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) acc[g][j] = fmaf(p, vf[j], acc[g][j] * corr);
-        mx[g] = mn;
-      }
-    }
-  }
-
-  // merge the KPW key lanes of each warp, then the 4 warps, through shared memory
-  __shared__ float s_m[4 * KPW][G];
-  __shared__ float s_l[4 * KPW][G];
-  __shared__ float s_acc[4 * KPW][G][HD];
-  const int part = warp * KPW + sub;
-#pragma unroll
-  for (int g = 0; g < G; ++g) {
-    if (dl == 0) { s_m[part][g] = mx[g]; s_l[part][g] = l[g]; }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) s_acc[part][g][dl * 8 + j] = acc[g][j];
-  }
-  __syncthreads();
-  for (int idx = threadIdx.x; idx < G * HD; idx += 128) {
-    const int g = idx / HD, d = idx % HD;
-    float M = -INFINITY;
-#pragma unroll
-    for (int p = 0; p < 4 * KPW; ++p) M = fmaxf(M, s_m[p][g]);
-    float L = 0.f, A = 0.f;
-    if (M > -INFINITY) {
-#pragma unroll
-      for (int p = 0; p < 4 * KPW; ++p) {
-        const float w = __expf(s_m[p][g] - M);
-        L += s_l[p][g] * w;
-        A += s_acc[p][g][d] * w;
-      }
-    }
-    const int h = kvh * G + g;
-    if (n_splits == 1) {
-      out[((long long)t * H + h) * HD + d] = f2bf(L > 0.f ? A / L : 0.f);
-    } else {
-      const long long o = ((long long)t * H + h) * n_splits + sp;
-      o_part[o * HD + d] = A;
-      if (d == 0) { ml_part[o * 2] = M; ml_part[o * 2 + 1] = L; }
-    }
-  }
-}
-
-// merge the kv splits of one (token, head): out = sum_s e^{m_s-M} acc_s / sum_s e^{m_s-M} l_s
-__global__ void xb_attn_combine_kernel(const float* __restrict__ o_part, const float* __restrict__ ml_part,
-                                       bf16* __restrict__ out, int n_splits, int hd) {
-  const long long th = blockIdx.x;  // t*H + h
-  const int d = threadIdx.x;
-  float M = -INFINITY;
-  for (int s = 0; s < n_splits; ++s) M = fmaxf(M, ml_part[(th * n_splits + s) * 2]);
-  float L = 0.f, A = 0.f;
-  for (int s = 0; s < n_splits; ++s) {
-    const float ms = ml_part[(th * n_splits + s) * 2];
-    if (ms > -INFINITY) {
-      const float w = __expf(ms - M);
-      L += ml_part[(th * n_splits + s) * 2 + 1] * w;
-      A += o_part[(th * n_splits + s) * hd + d] * w;
-    }
-  }
-  out[th * hd + d] = f2bf(L > 0.f ? A / L : 0.f);
 }
 
 // ----------------------------------------------------------------------------- misc
