@@ -170,6 +170,8 @@ __global__ void __launch_bounds__(160) xb_attn_decode_mma_kernel(
 
   const int t = blockIdx.x, kvh = blockIdx.y, sp = blockIdx.z;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_launch_dependents();
+  pdl_wait();
   const int pos = m.tok_pos[t];
   const int slot = m.seq_slot[m.tok_seq[t]];
   const int* pt = m.page_table + (long long)slot * m.max_pages;
@@ -289,6 +291,8 @@ __global__ void __launch_bounds__(128) xb_attn_combine2_kernel(const float* __re
                                                                int n_splits, int n_rows) {
   const long long th = (long long)blockIdx.x * 4 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
+  pdl_launch_dependents();
+  pdl_wait();
   if (th >= n_rows) return;
   float ms = -INFINITY, ls = 0.f;
   if (lane < n_splits) {
@@ -300,16 +304,24 @@ __global__ void __launch_bounds__(128) xb_attn_combine2_kernel(const float* __re
   const float L = warp_sum(ls * w);
   constexpr int VPL = HD / 32;
   float acc[4] = {0.f, 0.f, 0.f, 0.f};
-  for (int s = 0; s < n_splits; ++s) {
-    const float ws = __shfl_sync(0xffffffffu, w, s);
-    const float* src = o_part + (th * n_splits + s) * HD + lane * VPL;
-    if (VPL == 4) {
-      const float4 v = *reinterpret_cast<const float4*>(src);
-      acc[0] = fmaf(ws, v.x, acc[0]); acc[1] = fmaf(ws, v.y, acc[1]);
-      acc[2] = fmaf(ws, v.z, acc[2]); acc[3] = fmaf(ws, v.w, acc[3]);
-    } else {
-      const float2 v = *reinterpret_cast<const float2*>(src);
-      acc[0] = fmaf(ws, v.x, acc[0]); acc[1] = fmaf(ws, v.y, acc[1]);
+  for (int s0 = 0; s0 < n_splits; s0 += 8) {
+    float4 v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {          // 8 independent loads in flight per lane
+      v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (s0 + u < n_splits) {
+        const float* src = o_part + (th * n_splits + s0 + u) * HD + lane * VPL;
+        if (VPL == 4) v[u] = *reinterpret_cast<const float4*>(src);
+        else { const float2 t2 = *reinterpret_cast<const float2*>(src); v[u].x = t2.x; v[u].y = t2.y; }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const float ws = __shfl_sync(0xffffffffu, w, (s0 + u) & 31);
+      if (s0 + u < n_splits) {
+        acc[0] = fmaf(ws, v[u].x, acc[0]); acc[1] = fmaf(ws, v[u].y, acc[1]);
+        acc[2] = fmaf(ws, v[u].z, acc[2]); acc[3] = fmaf(ws, v[u].w, acc[3]);
+      }
     }
   }
   const float invL = L > 0.f ? 1.0f / L : 0.f;
@@ -343,6 +355,8 @@ __global__ void __launch_bounds__(288) xb_attn_prefill_mma_kernel(
 
   const int tile = blockIdx.x, kvh = blockIdx.y;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_launch_dependents();
+  pdl_wait();
   const int t0 = tile_start[tile];
   const int nt = tile_len[tile];
   const int pos0 = m.tok_pos[t0];                       // tokens of a tile have consecutive positions

@@ -66,6 +66,7 @@ struct xb_engine {
   struct StepGraph { cudaGraphExec_t exec = nullptr; int warmed = 0; uint64_t launches = 0; };
   std::map<long long, StepGraph> graphs;
   int use_graphs = 1;
+  int use_pdl = 1;
   // workspaces
   bf16 *h = nullptr, *hn = nullptr, *q = nullptr, *attn = nullptr, *act = nullptr, *last_rows = nullptr;
   void* gemm_out = nullptr;
@@ -78,8 +79,68 @@ struct xb_engine {
 
 #define LAUNCH_COUNT(e) ((e)->c.launches++)
 
+// Launch one kernel of the forward: programmatic dependent launch (the kernel calls
+// griddepcontrol.wait before touching upstream data) and an optional cluster dimension.
+template <typename... KArgs, typename... Args>
+static int launch_k(xb_engine* e, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, int cluster_x,
+                    Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (e->use_pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  if (cluster_x > 1) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = cluster_x;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = na;
+  XB_CUDA(cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...));
+  e->c.launches++;
+  return 0;
+}
+
 static int dmalloc(void** p, size_t bytes) {
   XB_CUDA(cudaMalloc(p, bytes ? bytes : 16));
+  return 0;
+}
+
+// tile-major weight storage: rows padded to 128, K padded to 64, zero filled
+static size_t tiled_elems(size_t rows, size_t K) { return ((rows + 127) / 128) * ((K + 63) / 64) * 8192; }
+static int alloc_tiled(bf16** p, size_t rows, size_t K) {
+  XB_TRY(dmalloc((void**)p, tiled_elems(rows, K) * 2));
+  XB_CUDA(cudaMemset(*p, 0, tiled_elems(rows, K) * 2));
+  return 0;
+}
+// copy `rows` x K row-major bf16 (host or device memory) into rows [row0, row0+rows) of a tiled matrix
+static int store_tiled(bf16* dst, const void* src, size_t row0, size_t rows, size_t K) {
+  XB_CHECK(K % 8 == 0, "K=%zu must be a multiple of 8", K);
+  cudaPointerAttributes pa;
+  const bool on_device = cudaPointerGetAttributes(&pa, src) == cudaSuccess && pa.type == cudaMemoryTypeDevice;
+  cudaGetLastError();
+  const bf16* dsrc = (const bf16*)src;
+  void* staging = nullptr;
+  if (!on_device) {
+    XB_TRY(dmalloc(&staging, rows * K * 2));
+    XB_CUDA(cudaMemcpy(staging, src, rows * K * 2, cudaMemcpyHostToDevice));
+    dsrc = (const bf16*)staging;
+  }
+  const long long n = (long long)rows * (K / 8);
+  xb_tile_weight_kernel<<<(unsigned)((n + 255) / 256), 256>>>(dsrc, dst, (long long)row0, (long long)rows, (int)K,
+                                                              (int)((K + 63) / 64));
+  XB_CUDA(cudaGetLastError());
+  XB_CUDA(cudaDeviceSynchronize());
+  if (staging) cudaFree(staging);
   return 0;
 }
 
@@ -118,10 +179,10 @@ extern "C" int xb_engine_create(const xb_model_desc* desc, int device, xb_engine
   uint64_t wbytes = 0;
   for (int l = 0; l < e->nl; ++l) {
     LayerW& w = e->L[l];
-    XB_TRY(dmalloc((void**)&w.wqkv, (size_t)e->NQKV * D * 2));
-    XB_TRY(dmalloc((void**)&w.wo, D * e->NQ * 2));
-    XB_TRY(dmalloc((void**)&w.wgu, 2 * I * D * 2));
-    XB_TRY(dmalloc((void**)&w.wdown, D * I * 2));
+    XB_TRY(alloc_tiled(&w.wqkv, e->NQKV, D));
+    XB_TRY(alloc_tiled(&w.wo, D, e->NQ));
+    XB_TRY(alloc_tiled(&w.wgu, 2 * I, D));
+    XB_TRY(alloc_tiled(&w.wdown, D, I));
     XB_TRY(dmalloc((void**)&w.sa_norm, D * 2));
     XB_TRY(dmalloc((void**)&w.mlp_norm, D * 2));
     if (d.qkv_bias) {
@@ -131,10 +192,12 @@ extern "C" int xb_engine_create(const xb_model_desc* desc, int device, xb_engine
     wbytes += ((size_t)e->NQKV * D + D * e->NQ + 3 * I * D) * 2;
   }
   const bool first = d.start_layer == 0, last = d.end_layer == d.n_layers - 1;
-  if (first || (last && d.tied_head)) XB_TRY(dmalloc((void**)&e->embed, (size_t)d.vocab * D * 2));
+  // the embedding table stays row-major (row gather); the LM head is tile-major like every
+  // other matrix, so a tied head on a last shard is a second, tiled copy of the table
+  if (first) XB_TRY(dmalloc((void**)&e->embed, (size_t)d.vocab * D * 2));
   if (last) {
     XB_TRY(dmalloc((void**)&e->final_norm, D * 2));
-    if (!d.tied_head) XB_TRY(dmalloc((void**)&e->lm_head, (size_t)d.vocab * D * 2));
+    XB_TRY(alloc_tiled(&e->lm_head, d.vocab, D));
     wbytes += (size_t)d.vocab * D * 2;
   }
   XB_TRY(dmalloc((void**)&e->rope, (size_t)d.max_positions * (d.head_dim / 2) * 2 * sizeof(float)));
@@ -177,6 +240,8 @@ extern "C" int xb_engine_create(const xb_model_desc* desc, int device, xb_engine
   {
     const char* g = getenv("XB_GRAPHS");
     if (g != nullptr && g[0] == '0') e->use_graphs = 0;
+    g = getenv("XB_PDL");
+    if (g != nullptr && g[0] == '0') e->use_pdl = 0;
   }
   *out = e;
   return 0;
@@ -209,20 +274,21 @@ extern "C" int xb_load_weight(xb_engine* e, int layer, int kind, const void* src
   XB_CUDA(cudaSetDevice(e->device));
   const xb_model_desc& d = e->d;
   const size_t D = d.dim, I = d.inter_dim;
-  void* dst = nullptr;
-  size_t want = 0;
+  void* dst = nullptr;          // plain copy target (vectors, embedding, RoPE table)
+  bf16* tdst = nullptr;         // tiled matrix target
+  size_t want = 0, row0 = 0, rows = 0, K = 0;
   if (layer >= 0) {
     XB_CHECK(layer >= d.start_layer && layer <= d.end_layer, "layer %d outside this shard [%d,%d]", layer, d.start_layer,
              d.end_layer);
     LayerW& w = e->L[layer - d.start_layer];
     switch (kind) {
-      case XB_W_Q: dst = w.wqkv; want = (size_t)e->NQ * D * 2; break;
-      case XB_W_K: dst = w.wqkv + (size_t)e->NQ * D; want = (size_t)e->NKV * D * 2; break;
-      case XB_W_V: dst = w.wqkv + (size_t)(e->NQ + e->NKV) * D; want = (size_t)e->NKV * D * 2; break;
-      case XB_W_O: dst = w.wo; want = D * e->NQ * 2; break;
-      case XB_W_GATE: dst = w.wgu; want = I * D * 2; break;
-      case XB_W_UP: dst = w.wgu + I * D; want = I * D * 2; break;
-      case XB_W_DOWN: dst = w.wdown; want = D * I * 2; break;
+      case XB_W_Q: tdst = w.wqkv; row0 = 0; rows = e->NQ; K = D; break;
+      case XB_W_K: tdst = w.wqkv; row0 = e->NQ; rows = e->NKV; K = D; break;
+      case XB_W_V: tdst = w.wqkv; row0 = e->NQ + e->NKV; rows = e->NKV; K = D; break;
+      case XB_W_O: tdst = w.wo; rows = D; K = e->NQ; break;
+      case XB_W_GATE: tdst = w.wgu; row0 = 0; rows = I; K = D; break;
+      case XB_W_UP: tdst = w.wgu; row0 = I; rows = I; K = D; break;
+      case XB_W_DOWN: tdst = w.wdown; rows = D; K = I; break;
       case XB_W_SA_NORM: dst = w.sa_norm; want = D * 2; break;
       case XB_W_MLP_NORM: dst = w.mlp_norm; want = D * 2; break;
       case XB_W_Q_BIAS: XB_CHECK(w.bqkv, "model has no qkv bias"); dst = w.bqkv; want = (size_t)e->NQ * 2; break;
@@ -232,12 +298,27 @@ extern "C" int xb_load_weight(xb_engine* e, int layer, int kind, const void* src
     }
   } else {
     switch (kind) {
-      case XB_W_EMBED: XB_CHECK(e->embed, "this shard holds no embedding"); dst = e->embed; want = (size_t)d.vocab * D * 2; break;
+      case XB_W_EMBED:
+        XB_CHECK(e->embed || (e->lm_head && d.tied_head), "this shard holds no embedding");
+        want = (size_t)d.vocab * D * 2;
+        XB_CHECK(nbytes == want, "embedding: got %zu bytes, expected %zu", nbytes, want);
+        if (e->embed) XB_CUDA(cudaMemcpy(e->embed, src, nbytes, cudaMemcpyDefault));
+        if (e->lm_head && d.tied_head) XB_TRY(store_tiled(e->lm_head, src, 0, d.vocab, D));
+        e->plans.clear();
+        return 0;
       case XB_W_FINAL_NORM: XB_CHECK(e->final_norm, "this shard holds no final norm"); dst = e->final_norm; want = D * 2; break;
-      case XB_W_LM_HEAD: XB_CHECK(e->lm_head, "this shard holds no separate LM head"); dst = e->lm_head; want = (size_t)d.vocab * D * 2; break;
+      case XB_W_LM_HEAD:
+        XB_CHECK(e->lm_head && !d.tied_head, "this shard holds no separate LM head");
+        tdst = e->lm_head; rows = d.vocab; K = D;
+        break;
       case XB_W_ROPE_TABLE: dst = e->rope; want = (size_t)d.max_positions * (d.head_dim / 2) * 2 * sizeof(float); break;
       default: return xb_fail(1, "weight kind %d is not a global kind", kind);
     }
+  }
+  if (tdst != nullptr) {
+    want = rows * K * 2;
+    XB_CHECK(nbytes == want, "weight kind %d layer %d: got %zu bytes, expected %zu", kind, layer, nbytes, want);
+    return store_tiled(tdst, src, row0, rows, K);
   }
   XB_CHECK(nbytes == want, "weight kind %d layer %d: got %zu bytes, expected %zu", kind, layer, nbytes, want);
   XB_CUDA(cudaMemcpy(dst, src, nbytes, cudaMemcpyDefault));
@@ -313,7 +394,7 @@ static int get_plan(xb_engine* e, int site, int layer, const bf16* x, long long 
   auto it = e->plans.find(key);
   if (it == e->plans.end()) {
     GemmPlan p;
-    XB_TRY(xb_gemm_plan(&p, x, ldx, w, T, N, K, out, ld_out, bias, round_bf16, e->num_sms, 0));
+    XB_TRY(xb_gemm_plan(&p, x, ldx, w, 1, T, N, K, out, ld_out, bias, round_bf16, e->num_sms, 0));
     if (out == e->gemm_out) {
       const size_t need = p.args.mode == XB_GEMM_SKINNY ? (size_t)p.args.splits * T * N * 4 : (size_t)T * N * 2;
       XB_CHECK(need <= e->gemm_out_bytes, "gemm workspace too small: need %zu have %zu", need, e->gemm_out_bytes);
@@ -340,16 +421,12 @@ static int launch_attn_g(xb_engine* e, const LayerW& w, const BatchMeta& m, int 
       attr_set = true;
     }
     dim3 grid(T, d.n_kv_heads, n_splits);
-    xb_attn_decode_mma_kernel<HD, G, NST><<<grid, 160, Cfg::SMEM_BYTES, st>>>(w.tmK, w.tmV, e->q, m, e->o_part, e->ml_part,
+    XB_TRY(launch_k(e, xb_attn_decode_mma_kernel<HD, G, NST>, dim3(grid), dim3(160), Cfg::SMEM_BYTES, st, 1, w.tmK, w.tmV, e->q, m, e->o_part, e->ml_part,
                                                                               e->attn, d.n_heads, d.n_kv_heads, n_splits,
-                                                                              scale_log2);
-    XB_CUDA(cudaGetLastError());
-    LAUNCH_COUNT(e);
+                                                                              scale_log2));
     if (n_splits > 1) {
       const int rows = T * d.n_heads;
-      xb_attn_combine2_kernel<HD><<<(rows + 3) / 4, 128, 0, st>>>(e->o_part, e->ml_part, e->attn, n_splits, rows);
-      XB_CUDA(cudaGetLastError());
-      LAUNCH_COUNT(e);
+      XB_TRY(launch_k(e, xb_attn_combine2_kernel<HD>, dim3((rows + 3) / 4), dim3(128), 0, st, 1, e->o_part, e->ml_part, e->attn, n_splits, rows));
     }
   } else {
     // prefill: one block per (query tile, kv head)
@@ -361,10 +438,8 @@ static int launch_attn_g(xb_engine* e, const LayerW& w, const BatchMeta& m, int 
       attr_set = true;
     }
     dim3 grid(n_tiles, d.n_kv_heads);
-    xb_attn_prefill_mma_kernel<HD, G, NST><<<grid, 288, Cfg::SMEM_BYTES, st>>>(w.tmK, w.tmV, e->q, m, m.tile_start, m.tile_len,
-                                                                               e->attn, d.n_heads, d.n_kv_heads, scale_log2);
-    XB_CUDA(cudaGetLastError());
-    LAUNCH_COUNT(e);
+    XB_TRY(launch_k(e, xb_attn_prefill_mma_kernel<HD, G, NST>, dim3(grid), dim3(288), Cfg::SMEM_BYTES, st, 1, w.tmK, w.tmV, e->q, m, m.tile_start, m.tile_len,
+                                                                               e->attn, d.n_heads, d.n_kv_heads, scale_log2));
   }
   return 0;
 }
@@ -387,22 +462,8 @@ static int launch_attn(xb_engine* e, const LayerW& w, const BatchMeta& m, int T,
 template <int CL, int NT, int VPT>
 static int launch_resid_norm_cluster(xb_engine* e, const GemmPlan* gp, int T, const bf16* nw, cudaStream_t st) {
   const xb_model_desc& d = e->d;
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(CL, T, 1);
-  cfg.blockDim = dim3(NT, 1, 1);
-  cfg.dynamicSmemBytes = 0;
-  cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = CL;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  XB_CUDA(cudaLaunchKernelEx(&cfg, xb_resid_norm_cluster_kernel<CL, NT, VPT>, (const float*)e->gemm_out, gp->args.splits,
-                             (long long)T * d.dim, e->h, nw, e->hn, d.dim, d.norm_eps, d.rmsnorm_two_round));
-  LAUNCH_COUNT(e);
-  return 0;
+  return launch_k(e, xb_resid_norm_cluster_kernel<CL, NT, VPT>, dim3(CL, T, 1), dim3(NT), 0, st, CL, (const float*)e->gemm_out,
+                  gp->args.splits, (long long)T * d.dim, e->h, nw, e->hn, d.dim, d.norm_eps, d.rmsnorm_two_round);
 }
 
 static int launch_resid_norm(xb_engine* e, const GemmPlan* gp, int T, const bf16* nw, cudaStream_t st) {
@@ -413,14 +474,12 @@ static int launch_resid_norm(xb_engine* e, const GemmPlan* gp, int T, const bf16
     if (d.dim % 32 == 0 && d.dim / 8 <= 128 * 4 * 2)
       return d.dim / 8 <= 128 * 4 ? launch_resid_norm_cluster<8, 128, 1>(e, gp, T, nw, st)
                                   : launch_resid_norm_cluster<8, 128, 2>(e, gp, T, nw, st);
-    xb_resid_norm_kernel<256, 0><<<T, 256, smem, st>>>((const float*)e->gemm_out, gp->args.splits, (long long)T * d.dim,
-                                                        nullptr, e->h, nw, e->hn, d.dim, d.norm_eps, d.rmsnorm_two_round);
+    XB_TRY(launch_k(e, xb_resid_norm_kernel<256, 0>, dim3(T), dim3(256), smem, st, 1, (const float*)e->gemm_out, gp->args.splits, (long long)T * d.dim,
+                                                        nullptr, e->h, nw, e->hn, d.dim, d.norm_eps, d.rmsnorm_two_round));
   } else {
-    xb_resid_norm_kernel<256, 1><<<T, 256, smem, st>>>(nullptr, 1, 0, (const bf16*)e->gemm_out, e->h, nw, e->hn, d.dim,
-                                                        d.norm_eps, d.rmsnorm_two_round);
+    XB_TRY(launch_k(e, xb_resid_norm_kernel<256, 1>, dim3(T), dim3(256), smem, st, 1, nullptr, 1, 0, (const bf16*)e->gemm_out, e->h, nw, e->hn, d.dim,
+                                                        d.norm_eps, d.rmsnorm_two_round));
   }
-  XB_CUDA(cudaGetLastError());
-  LAUNCH_COUNT(e);
   return 0;
 }
 
@@ -444,58 +503,52 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
   const int D = d.dim, I = d.inter_dim, hd = d.head_dim;
   const size_t norm_smem = (size_t)D * sizeof(float);
   if (first) {
-    xb_embed_norm_kernel<256><<<T, 256, 0, st>>>(e->in_tokens, e->embed, e->L[0].sa_norm, e->h, e->hn, D, d.vocab, d.norm_eps,
-                                                  d.rmsnorm_two_round);
+    XB_TRY(launch_k(e, xb_embed_norm_kernel<256>, dim3(T), dim3(256), 0, st, 1, e->in_tokens, e->embed, e->L[0].sa_norm, e->h, e->hn, D, d.vocab, d.norm_eps,
+                                                  d.rmsnorm_two_round));
   } else {
-    xb_resid_norm_kernel<256, 2><<<T, 256, norm_smem, st>>>(nullptr, 0, 0, nullptr, e->h, e->L[0].sa_norm, e->hn, D,
-                                                             d.norm_eps, d.rmsnorm_two_round);
+    XB_TRY(launch_k(e, xb_resid_norm_kernel<256, 2>, dim3(T), dim3(256), norm_smem, st, 1, nullptr, 0, 0, nullptr, e->h, e->L[0].sa_norm, e->hn, D,
+                                                             d.norm_eps, d.rmsnorm_two_round));
   }
-  XB_CUDA(cudaGetLastError());
-  LAUNCH_COUNT(e);
 
   for (int l = 0; l < e->nl; ++l) {
     const LayerW& w = e->L[l];
     const GemmPlan* gp;
     // q/k/v projections as one GEMM (general_mha.py:83-97)
     XB_TRY(get_plan(e, SITE_QKV, l, e->hn, D, w.wqkv, T, e->NQKV, D, e->gemm_out, e->NQKV, w.bqkv, 0, &gp));
-    XB_TRY(xb_gemm_run(*gp, st));
+    XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
     LAUNCH_COUNT(e);
     {
       dim3 grid(T, d.n_heads + 2 * d.n_kv_heads);
       if (gp->args.mode == XB_GEMM_SKINNY)
-        xb_qkv_finalize_kernel<0><<<grid, hd / 2, 0, st>>>((const float*)e->gemm_out, gp->args.splits, (long long)T * e->NQKV,
+        XB_TRY(launch_k(e, xb_qkv_finalize_kernel<0>, dim3(grid), dim3(hd / 2), 0, st, 1, (const float*)e->gemm_out, gp->args.splits, (long long)T * e->NQKV,
                                                             nullptr, w.bqkv, e->rope, e->q, w.k_pool, w.v_pool, m, d.n_heads,
-                                                            d.n_kv_heads, hd, d.rope_kind);
+                                                            d.n_kv_heads, hd, d.rope_kind));
       else
-        xb_qkv_finalize_kernel<1><<<grid, hd / 2, 0, st>>>(nullptr, 1, 0, (const bf16*)e->gemm_out, nullptr, e->rope, e->q,
-                                                            w.k_pool, w.v_pool, m, d.n_heads, d.n_kv_heads, hd, d.rope_kind);
-      XB_CUDA(cudaGetLastError());
-      LAUNCH_COUNT(e);
+        XB_TRY(launch_k(e, xb_qkv_finalize_kernel<1>, dim3(grid), dim3(hd / 2), 0, st, 1, nullptr, 1, 0, (const bf16*)e->gemm_out, nullptr, e->rope, e->q,
+                                                            w.k_pool, w.v_pool, m, d.n_heads, d.n_kv_heads, hd, d.rope_kind));
     }
     if (hd == 128) XB_TRY(launch_attn<128>(e, w, m, T, n_splits, n_tiles, st));
     else XB_TRY(launch_attn<64>(e, w, m, T, n_splits, n_tiles, st));
     // output projection + residual + mlp_norm
     XB_TRY(get_plan(e, SITE_O, l, e->attn, e->NQ, w.wo, T, D, e->NQ, e->gemm_out, D, nullptr, 0, &gp));
-    XB_TRY(xb_gemm_run(*gp, st));
+    XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
     LAUNCH_COUNT(e);
     XB_TRY(launch_resid_norm(e, gp, T, w.mlp_norm, st));
     // gate/up as one GEMM, SiLU*up, down projection (llm_utils.py:513-522)
     XB_TRY(get_plan(e, SITE_GU, l, e->hn, D, w.wgu, T, 2 * I, D, e->gemm_out, 2 * I, nullptr, 0, &gp));
-    XB_TRY(xb_gemm_run(*gp, st));
+    XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
     LAUNCH_COUNT(e);
     {
       const long long n = (long long)T * I;
       const int blocks = (int)((n + 255) / 256);
       if (gp->args.mode == XB_GEMM_SKINNY)
-        xb_silu_mul_kernel<0><<<blocks, 256, 0, st>>>((const float*)e->gemm_out, gp->args.splits, (long long)T * 2 * I, nullptr,
-                                                       e->act, T, I);
+        XB_TRY(launch_k(e, xb_silu_mul_kernel<0>, dim3(blocks), dim3(256), 0, st, 1, (const float*)e->gemm_out, gp->args.splits, (long long)T * 2 * I, nullptr,
+                                                       e->act, T, I));
       else
-        xb_silu_mul_kernel<1><<<blocks, 256, 0, st>>>(nullptr, 1, 0, (const bf16*)e->gemm_out, e->act, T, I);
-      XB_CUDA(cudaGetLastError());
-      LAUNCH_COUNT(e);
+        XB_TRY(launch_k(e, xb_silu_mul_kernel<1>, dim3(blocks), dim3(256), 0, st, 1, nullptr, 1, 0, (const bf16*)e->gemm_out, e->act, T, I));
     }
     XB_TRY(get_plan(e, SITE_DOWN, l, e->act, I, w.wdown, T, D, I, e->gemm_out, D, nullptr, 0, &gp));
-    XB_TRY(xb_gemm_run(*gp, st));
+    XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
     LAUNCH_COUNT(e);
     const bf16* next_norm = (l + 1 < e->nl) ? e->L[l + 1].sa_norm : (last ? e->final_norm : nullptr);
     XB_TRY(launch_resid_norm(e, gp, T, next_norm, st));
@@ -505,13 +558,11 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
 
   if (last) {
     // final norm was fused above; LM head on the last position of each sequence only
-    xb_gather_rows_kernel<<<n_seqs, 256, 0, st>>>(e->hn, e->d_seq_last, e->last_rows, D);
-    XB_CUDA(cudaGetLastError());
-    LAUNCH_COUNT(e);
-    const bf16* head = d.tied_head ? e->embed : e->lm_head;
+    XB_TRY(launch_k(e, xb_gather_rows_kernel, dim3(n_seqs), dim3(256), 0, st, 1, e->hn, e->d_seq_last, e->last_rows, D));
+    const bf16* head = e->lm_head;
     const GemmPlan* gp;
     XB_TRY(get_plan(e, SITE_HEAD, 0, e->last_rows, D, head, n_seqs, d.vocab, D, e->logits, d.vocab, nullptr, 1, &gp));
-    XB_TRY(xb_gemm_run(*gp, st));
+    XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
     LAUNCH_COUNT(e);
   }
   return 0;
@@ -677,20 +728,20 @@ extern "C" int xb_bench_linears(xb_engine* e, int T, int iters, int* n_launches,
       const LayerW& w = e->L[l];
       const GemmPlan* gp;
       XB_TRY(get_plan(e, SITE_QKV, l, e->hn, D, w.wqkv, T, e->NQKV, D, e->gemm_out, e->NQKV, w.bqkv, 0, &gp));
-      XB_TRY(xb_gemm_run(*gp, st));
+      XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
       XB_TRY(get_plan(e, SITE_O, l, e->attn, e->NQ, w.wo, T, D, e->NQ, e->gemm_out, D, nullptr, 0, &gp));
-      XB_TRY(xb_gemm_run(*gp, st));
+      XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
       XB_TRY(get_plan(e, SITE_GU, l, e->hn, D, w.wgu, T, 2 * I, D, e->gemm_out, 2 * I, nullptr, 0, &gp));
-      XB_TRY(xb_gemm_run(*gp, st));
+      XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
       XB_TRY(get_plan(e, SITE_DOWN, l, e->act, I, w.wdown, T, D, I, e->gemm_out, D, nullptr, 0, &gp));
-      XB_TRY(xb_gemm_run(*gp, st));
+      XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
       n += 4;
     }
     if (last && T <= d.max_seqs && T <= 128) {
-      const bf16* head = d.tied_head ? e->embed : e->lm_head;
+      const bf16* head = e->lm_head;
       const GemmPlan* gp;
       XB_TRY(get_plan(e, SITE_HEAD, 0, e->last_rows, D, head, T, d.vocab, D, e->logits, d.vocab, nullptr, 1, &gp));
-      XB_TRY(xb_gemm_run(*gp, st));
+      XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
       n += 1;
     }
   }
@@ -749,8 +800,8 @@ extern "C" int xb_debug_linear(const void* x, const void* w, int T, int N, int K
     return 0;
   }
   GemmPlan p;
-  XB_TRY(xb_gemm_plan(&p, (const bf16*)x, K, (const bf16*)w, T, N, K, scratch, N, nullptr, 0, sms, force_splits));
-  XB_TRY(xb_gemm_run(p, st));
+  XB_TRY(xb_gemm_plan(&p, (const bf16*)x, K, (const bf16*)w, 0, T, N, K, scratch, N, nullptr, 0, sms, force_splits));
+  XB_TRY(xb_gemm_run(p, st, 0));
   const long long n = (long long)T * N;
   const int blocks = (int)((n + 255) / 256);
   if (p.args.mode == XB_GEMM_SKINNY)

@@ -18,6 +18,14 @@
 //       output = fp32 partial sums  out[split][t][n]  reduced by the consumer kernel.
 //   MODE_WIDE    (prefill): A = x tile (128 tokens), B = W tile (BN features);
 //       tensor-bound; output = bf16  out[t][n] (+ bias, rounded once like nn.Linear).
+//
+// The engine stores weights TILE-MAJOR in HBM ([N/128][K/64][128][64] bf16): every TMA box is
+// one contiguous 16 KB read instead of 128 rows x 128 B at a K*2-byte pitch.
+//
+// Programmatic dependent launch: weights never depend on the preceding kernel, so the producer
+// issues the weight boxes of the first pipeline stages BEFORE griddepcontrol.wait and only the
+// activation boxes / the epilogue stores wait for the upstream grid -- the HBM stream keeps
+// going across kernel boundaries.
 #pragma once
 #include "xb_common.cuh"
 
@@ -28,10 +36,17 @@ struct GemmArgs {
   int a_rows, b_rows;      // valid rows of the A / B global matrices
   int mode;
   int round_bf16;          // SKINNY: round the fp32 result to bf16 precision (splits == 1 only)
+  int w_tiled;             // weight operand is stored tile-major: [N/128][K/64][128][64]
   void* out;
   long long ld_out;        // SKINNY: N (floats per token row); WIDE: elements per token row
   const bf16* bias;        // WIDE: per-feature bias or nullptr
 };
+
+// TMA coordinates (innermost, row) of the [128 x 64] weight box holding rows 128*wt.. of k-block kb
+__device__ __forceinline__ void gemm_w_coord(const GemmArgs& g, int wt, int kb, int& c0, int& c1) {
+  if (g.w_tiled) { c0 = 0; c1 = (wt * g.k_blocks + kb) * 128; }
+  else { c0 = kb * 64; c1 = wt * 128; }
+}
 
 template <int BN, int STAGES>
 struct GemmCfg {
@@ -83,6 +98,7 @@ xb_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();   // the next kernel may start its prologue / weight prefetch now
 
   const int total_units = g.a_tiles * g.b_tiles * g.splits;
 
@@ -91,6 +107,8 @@ xb_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
+      bool waited = false;
+      int pre = 0;   // stages whose weight box was issued ahead of the dependency wait
       for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
         const int s = u % g.splits;
         const int tile = u / g.splits;
@@ -98,14 +116,64 @@ xb_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         const int tb = tile / g.a_tiles;
         const int kb0 = (int)(((long long)s * g.k_blocks) / g.splits);
         const int kb1 = (int)(((long long)(s + 1) * g.k_blocks) / g.splits);
+        if (!waited) {
+          // first unit: weight boxes of up to STAGES k-blocks go out before the upstream grid is done
+          const int npre = (kb1 - kb0) < STAGES ? (kb1 - kb0) : STAGES;
+          for (int i = 0; i < npre; ++i) {
+            mbar_expect_tx(&full_bar[i], Cfg::A_BYTES + Cfg::B_BYTES);
+            int c0, c1;
+            if (g.mode == XB_GEMM_SKINNY) {
+              gemm_w_coord(g, ta, kb0 + i, c0, c1);
+              tma_load_2d(sA + i * Cfg::A_BYTES, &tmA, &full_bar[i], c0, c1);
+            } else {
+#pragma unroll
+              for (int j = 0; j < BN / 128; ++j) {
+                if (g.w_tiled) {
+                  gemm_w_coord(g, tb * (BN / 128) + j, kb0 + i, c0, c1);
+                  tma_load_2d(sB + i * Cfg::B_BYTES + j * Cfg::A_BYTES, &tmB, &full_bar[i], c0, c1);
+                } else if (j == 0) {
+                  tma_load_2d(sB + i * Cfg::B_BYTES, &tmB, &full_bar[i], (kb0 + i) * 64, tb * BN);
+                }
+              }
+            }
+          }
+          pdl_wait();
+          waited = true;
+          pre = npre;
+        }
         for (int kb = kb0; kb < kb1; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
-          mbar_expect_tx(&full_bar[stage], Cfg::A_BYTES + Cfg::B_BYTES);
-          tma_load_2d(sA + stage * Cfg::A_BYTES, &tmA, &full_bar[stage], kb * 64, ta * 128);
-          tma_load_2d(sB + stage * Cfg::B_BYTES, &tmB, &full_bar[stage], kb * 64, tb * BN);
+          const bool w_issued = pre > 0;
+          if (!w_issued) {
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            mbar_expect_tx(&full_bar[stage], Cfg::A_BYTES + Cfg::B_BYTES);
+          } else {
+            --pre;
+          }
+          int c0, c1;
+          if (g.mode == XB_GEMM_SKINNY) {
+            if (!w_issued) {
+              gemm_w_coord(g, ta, kb, c0, c1);
+              tma_load_2d(sA + stage * Cfg::A_BYTES, &tmA, &full_bar[stage], c0, c1);
+            }
+            tma_load_2d(sB + stage * Cfg::B_BYTES, &tmB, &full_bar[stage], kb * 64, tb * BN);
+          } else {
+            tma_load_2d(sA + stage * Cfg::A_BYTES, &tmA, &full_bar[stage], kb * 64, ta * 128);
+            if (!w_issued) {
+#pragma unroll
+              for (int j = 0; j < BN / 128; ++j) {
+                if (g.w_tiled) {
+                  gemm_w_coord(g, tb * (BN / 128) + j, kb, c0, c1);
+                  tma_load_2d(sB + stage * Cfg::B_BYTES + j * Cfg::A_BYTES, &tmB, &full_bar[stage], c0, c1);
+                } else if (j == 0) {
+                  tma_load_2d(sB + stage * Cfg::B_BYTES, &tmB, &full_bar[stage], kb * 64, tb * BN);
+                }
+              }
+            }
+          }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
+      if (!waited) pdl_wait();
     }
   } else if (warp == 1) {
     // ===================== MMA issuer (one thread) =====================
@@ -141,6 +209,7 @@ xb_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     // ===================== epilogue warps 2..5: TMEM -> registers -> global =====================
     const int quad = warp & 3;                        // TMEM lane quadrant this warp may read
     const int row_in_tile = quad * 32 + lane;
+    pdl_wait();                                       // `out` may still be read by the upstream grid
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
@@ -245,6 +314,19 @@ __global__ void xb_linear_check_kernel(const bf16* __restrict__ x, const bf16* _
   }
 }
 
+// row-major rows [row0, row0+rows) x K of a weight matrix -> tile-major storage
+// dst[((r/128)*KB + k/64)*8192 + (r%128)*64 + k%64]; 16 bytes per thread
+__global__ void xb_tile_weight_kernel(const bf16* __restrict__ src, bf16* __restrict__ dst, long long row0, long long rows,
+                                      int K, int KB) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int k8 = K / 8;
+  if (i >= rows * k8) return;
+  const long long r = row0 + i / k8;
+  const int k = (int)(i % k8) * 8;
+  const uint4 v = *reinterpret_cast<const uint4*>(src + (i / k8) * K + k);
+  *reinterpret_cast<uint4*>(dst + ((r >> 7) * KB + (k >> 6)) * 8192 + (r & 127) * 64 + (k & 63)) = v;
+}
+
 // ----------------------------------------------------------------------------- host side
 typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                     const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -281,7 +363,8 @@ static int xb_make_tmap(CUtensorMap* m, const void* ptr, long long rows, long lo
 }
 
 template <int BN, int STAGES>
-static int xb_gemm_launch_t(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, int grid, cudaStream_t st) {
+static int xb_gemm_launch_t(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, int grid, cudaStream_t st,
+                            int pdl) {
   using Cfg = GemmCfg<BN, STAGES>;
   static bool attr_set = false;
   if (!attr_set) {
@@ -289,8 +372,17 @@ static int xb_gemm_launch_t(const CUtensorMap& tmA, const CUtensorMap& tmB, cons
                                  Cfg::SMEM_BYTES));
     attr_set = true;
   }
-  xb_gemm_tcgen05_kernel<BN, STAGES><<<grid, 192, Cfg::SMEM_BYTES, st>>>(tmA, tmB, g);
-  XB_CUDA(cudaGetLastError());
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid, 1, 1);
+  cfg.blockDim = dim3(192, 1, 1);
+  cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  XB_CUDA(cudaLaunchKernelEx(&cfg, xb_gemm_tcgen05_kernel<BN, STAGES>, tmA, tmB, g));
   return 0;
 }
 
@@ -306,8 +398,8 @@ static int xb_pick_bn_skinny(int T) { return T <= 16 ? 16 : T <= 32 ? 32 : T <= 
 
 // y[T,N] = x[T,K] W[N,K]^T.  T <= 128 -> SKINNY (fp32 partials [splits][T][N] into `out`);
 // otherwise WIDE (bf16 [T, ld_out] into `out`).
-static int xb_gemm_plan(GemmPlan* p, const bf16* x, long long ldx, const bf16* w, int T, int N, int K, void* out,
-                        long long ld_out, const bf16* bias, int round_bf16, int num_sms, int force_splits) {
+static int xb_gemm_plan(GemmPlan* p, const bf16* x, long long ldx, const bf16* w, int w_tiled, int T, int N, int K,
+                        void* out, long long ld_out, const bf16* bias, int round_bf16, int num_sms, int force_splits) {
   XB_CHECK(K % 8 == 0, "K=%d must be a multiple of 8", K);
   GemmArgs& g = p->args;
   g.k_blocks = (K + 63) / 64;
@@ -315,6 +407,8 @@ static int xb_gemm_plan(GemmPlan* p, const bf16* x, long long ldx, const bf16* w
   g.ld_out = ld_out;
   g.bias = bias;
   g.round_bf16 = round_bf16;
+  g.w_tiled = w_tiled;
+  const long long w_tiles = (N + 127) / 128;
   if (T <= 128) {
     const int bn = xb_pick_bn_skinny(T);
     p->bn = bn;
@@ -340,7 +434,8 @@ static int xb_gemm_plan(GemmPlan* p, const bf16* x, long long ldx, const bf16* w
     if (round_bf16) splits = 1;
     if (splits > g.k_blocks) splits = g.k_blocks;
     g.splits = splits;
-    XB_TRY(xb_make_tmap(&p->tmA, w, N, K, K, 128));
+    if (w_tiled) XB_TRY(xb_make_tmap(&p->tmA, w, w_tiles * g.k_blocks * 128, 64, 64, 128));
+    else XB_TRY(xb_make_tmap(&p->tmA, w, N, K, K, 128));
     XB_TRY(xb_make_tmap(&p->tmB, x, T, K, ldx, bn));
   } else {
     p->bn = 256;
@@ -351,7 +446,8 @@ static int xb_gemm_plan(GemmPlan* p, const bf16* x, long long ldx, const bf16* w
     g.b_rows = N;
     g.splits = 1;
     XB_TRY(xb_make_tmap(&p->tmA, x, T, K, ldx, 128));
-    XB_TRY(xb_make_tmap(&p->tmB, w, N, K, K, 256));
+    if (w_tiled) XB_TRY(xb_make_tmap(&p->tmB, w, w_tiles * g.k_blocks * 128, 64, 64, 128));
+    else XB_TRY(xb_make_tmap(&p->tmB, w, N, K, K, 256));
   }
   const int units = g.a_tiles * g.b_tiles * g.splits;
   const int per_sm = (p->bn <= 64) ? 2 : 1;   // smem allows two resident CTAs for the small-BN configs
@@ -359,13 +455,13 @@ static int xb_gemm_plan(GemmPlan* p, const bf16* x, long long ldx, const bf16* w
   return 0;
 }
 
-static int xb_gemm_run(const GemmPlan& p, cudaStream_t st) {
+static int xb_gemm_run(const GemmPlan& p, cudaStream_t st, int pdl) {
   switch (p.bn) {
-    case 16:  return xb_gemm_launch_t<16, 5>(p.tmA, p.tmB, p.args, p.grid, st);
-    case 32:  return xb_gemm_launch_t<32, 5>(p.tmA, p.tmB, p.args, p.grid, st);
-    case 64:  return xb_gemm_launch_t<64, 4>(p.tmA, p.tmB, p.args, p.grid, st);
-    case 128: return xb_gemm_launch_t<128, 6>(p.tmA, p.tmB, p.args, p.grid, st);
-    case 256: return xb_gemm_launch_t<256, 4>(p.tmA, p.tmB, p.args, p.grid, st);
+    case 16:  return xb_gemm_launch_t<16, 5>(p.tmA, p.tmB, p.args, p.grid, st, pdl);
+    case 32:  return xb_gemm_launch_t<32, 5>(p.tmA, p.tmB, p.args, p.grid, st, pdl);
+    case 64:  return xb_gemm_launch_t<64, 4>(p.tmA, p.tmB, p.args, p.grid, st, pdl);
+    case 128: return xb_gemm_launch_t<128, 6>(p.tmA, p.tmB, p.args, p.grid, st, pdl);
+    case 256: return xb_gemm_launch_t<256, 4>(p.tmA, p.tmB, p.args, p.grid, st, pdl);
   }
   return xb_fail(1, "unsupported BN %d", p.bn);
 }

@@ -53,6 +53,8 @@ template <int NT>
 __global__ void __launch_bounds__(NT) xb_embed_norm_kernel(const int* __restrict__ tokens, const bf16* __restrict__ emb,
                                                            const bf16* __restrict__ nw, bf16* __restrict__ h,
                                                            bf16* __restrict__ hn, int D, int V, float eps, int two_round) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float red[32];
   const int t = blockIdx.x;
   int tok = tokens[t];
@@ -86,6 +88,8 @@ __global__ void __launch_bounds__(NT) xb_resid_norm_kernel(const float* __restri
                                                            const bf16* __restrict__ y, bf16* __restrict__ h,
                                                            const bf16* __restrict__ nw, bf16* __restrict__ hn, int D,
                                                            float eps, int two_round) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float red[32];
   extern __shared__ float row[];  // D floats: the new residual row
   const int t = blockIdx.x;
@@ -131,6 +135,8 @@ __global__ void __launch_bounds__(NT) xb_resid_norm_cluster_kernel(const float* 
                                                                    long long split_stride, bf16* __restrict__ h,
                                                                    const bf16* __restrict__ nw, bf16* __restrict__ hn,
                                                                    int D, float eps, int two_round) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float red[32];
   __shared__ float cl_part[CL];
   const int t = blockIdx.y;
@@ -209,6 +215,8 @@ __global__ void xb_qkv_finalize_kernel(const float* __restrict__ part, int split
                                        const bf16* __restrict__ y, const bf16* __restrict__ bias,
                                        const float* __restrict__ rope, bf16* __restrict__ q_out, bf16* __restrict__ k_pool,
                                        bf16* __restrict__ v_pool, BatchMeta m, int H, int KV, int hd, int rope_kind) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int t = blockIdx.x;
   const int head = blockIdx.y;              // [0,H) q heads, [H,H+KV) k heads, [H+KV,H+2KV) v heads
   const int i = threadIdx.x;                // pair index, hd/2 threads
@@ -271,6 +279,8 @@ __global__ void xb_qkv_finalize_kernel(const float* __restrict__ part, int split
 template <int SRC>
 __global__ void xb_silu_mul_kernel(const float* __restrict__ part, int splits, long long split_stride,
                                    const bf16* __restrict__ y, bf16* __restrict__ act, int T, int I) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (long long)T * I) return;
   const int t = (int)(idx / I), i = (int)(idx % I);
@@ -296,6 +306,8 @@ __global__ void xb_silu_mul_kernel(const float* __restrict__ part, int splits, l
 // rows[i] = src[idx[i]]  (last-position gather before the LM head: the reference runs the
 // head on all s positions and slices [:, -1], sharded_inference_engine.py:366)
 __global__ void xb_gather_rows_kernel(const bf16* __restrict__ src, const int* __restrict__ idx, bf16* __restrict__ dst, int D) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int r = blockIdx.x;
   const bf16* s = src + (long long)idx[r] * D;
   for (int i = threadIdx.x * 2; i < D; i += blockDim.x * 2)
