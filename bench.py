@@ -184,8 +184,10 @@ def run_b200(args):
       raise SystemExit(f"--gpus {args.gpus} needs torchrun with {args.gpus} ranks")
     args.gpus = world
   torch.cuda.set_device(local)
+  ret_group = None
   if world > 1:
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    ret_group = dist.new_group(ranks=list(range(world)))   # own communicator for the token return edge
   graft.build()
   from xotorch_support_jetson_b200.model_config import load_model_config  # noqa: F401
   from xotorch_support_jetson_b200.models import model_cards
@@ -202,7 +204,7 @@ def run_b200(args):
   peaks = measured_peaks()
   max_ctx = L + 2 * (K + W) + 80
   runner = PipelineRunner(args.model, hf_cfg, cfg, rank, world, local, B, M, max_ctx, max_batch_tokens=args.max_batch_tokens,
-                          dist=dist if world > 1 else None, seed=0)
+                          dist=dist if world > 1 else None, seed=0, ret_group=ret_group)
   dev = runner.device
   g = torch.Generator(device=dev).manual_seed(1234)
   prompts = [torch.randint(1, cfg["vocab_size"], (B, L), generator=g, device=dev, dtype=torch.int32) for _ in range(M)]
@@ -228,10 +230,7 @@ def run_b200(args):
   c0 = runner.stage.counters()
   # ---- prefill: one untimed pass (builds launch plans), then a timed pass on fresh slots
   runner.prefill(prompts)
-  if world > 1 and runner.first:
-    with torch.cuda.stream(runner.stream):
-      for m in range(M):
-        dist.recv(runner.tok[m], src=world - 1)
+  runner.drain()
   barrier()
   runner.reset()
   prefill_ms = timed(lambda: runner.prefill(prompts))
@@ -257,9 +256,7 @@ def run_b200(args):
     e2e_ms = timed(lambda: runner.decode(K, host_tokens=host_in, host_out=host_out))
     e2e = {"value": B * M * K / (e2e_ms * 1e-3), "unit": "tok/s", "h2d_bytes_per_step": 4 * B * M, "d2h_bytes_per_step": 2 * 4 * B * M,
            "api": "PipelineRunner.decode with pinned host id buffers (ids D2H+H2D on rank 0, sampled ids D2H on the last rank, every step)"}
-    runner.drain()
-  else:
-    runner.drain()
+  runner.drain()
 
   # ---- roofline of the dominant kernel: the tcgen05 Linear streaming this stage's weights
   st = runner.stage

@@ -164,3 +164,55 @@ def test_sampler_matches_reference_semantics(built_lib):
     for r in range(8):
       assert got[r].item() in set(si[r][cut[r]].tolist())
   st.close()
+
+
+@pytest.mark.parametrize("mid", ["llama-3.2-tiny", "llama-3.1-tiny", "qwen-2.5-tiny"])
+def test_cuda_path_against_committed_golden(built_lib, mid):
+  """The CUDA forward against tests/golden/oracle_<model>.npz (generated by oracle/gen_golden.py
+  from the oracle in reference-exact mode; nothing under oracle/ is executed here)."""
+  import json
+  from pathlib import Path
+  from xotorch_support_jetson_b200 import model_config as mc
+  from xotorch_support_jetson_b200.models import model_cards
+  from xotorch_support_jetson_b200.shard import Shard
+  from xotorch_support_jetson_b200.stage import StageRuntime
+  from xotorch_support_jetson_b200.synth import random_hf_state
+  g = np.load(Path(__file__).resolve().parent / "golden" / f"oracle_{mid}.npz", allow_pickle=False)
+  meta = json.loads(str(g["meta"]))
+  hf_cfg = model_cards[mid]["hf_config"]
+  import tempfile
+  with tempfile.TemporaryDirectory() as td:
+    (Path(td) / "config.json").write_text(json.dumps(hf_cfg))
+    cfg = mc.load_model_config(Path(td) / "config.json")
+  state = random_hf_state(hf_cfg, seed=meta["seed"], std=meta["std"], norm_jitter=meta["norm_jitter"])
+  nl, D = cfg["num_layers"], cfg["embed_dim"]
+  st = StageRuntime(Shard(mid, 0, nl - 1, nl), cfg, device=0, max_batch_tokens=64, max_seqs=2, max_tokens_per_seq=128, page_tokens=32)
+  st.load_state(state)
+  prompt = torch.from_numpy(g["prompt"]).cuda().reshape(-1)
+  L = prompt.numel()
+  taps = [torch.empty((L, D), dtype=torch.bfloat16, device="cuda") for _ in range(nl)]
+  logits = st.forward([0], [L], [0], tokens=prompt, taps=taps)
+  hid = np.stack([t[-1].float().cpu().numpy() for t in taps])
+  assert _rel(hid, g["prefill_hidden_last"]) < REL_TOL
+  n = g["tokens"].shape[1]
+  got_tokens, worst = [], _rel(logits.cpu().numpy()[0], g["logits"][0])
+  for step in range(1, n):
+    got_tokens.append(int(st.sample(logits, temp=0.0).item()))
+    x = torch.tensor([int(g["tokens"][0, step - 1])], dtype=torch.int32, device="cuda")
+    if step == 1:
+      taps1 = [torch.empty((1, D), dtype=torch.bfloat16, device="cuda") for _ in range(nl)]
+      logits = st.forward([0], [1], [L + step - 1], tokens=x, taps=taps1)
+      assert _rel(np.stack([t[0].float().cpu().numpy() for t in taps1]), g["decode_hidden"]) < REL_TOL
+    else:
+      logits = st.forward([0], [1], [L + step - 1], tokens=x)
+    worst = max(worst, _rel(logits.cpu().numpy()[0], g["logits"][step]))
+  got_tokens.append(int(st.sample(logits, temp=0.0).item()))
+  assert worst < REL_TOL, worst
+  # greedy tokens: identical wherever the golden top-2 margin is above the numerical noise
+  srt = np.sort(g["logits"], axis=-1)
+  margin = srt[:, -1] - srt[:, -2]
+  noise = REL_TOL * np.abs(g["logits"]).max()
+  for i in range(n):
+    if margin[i] > 2 * noise:
+      assert got_tokens[i] == int(g["tokens"][0, i]), (i, got_tokens, g["tokens"][0].tolist())
+  st.close()

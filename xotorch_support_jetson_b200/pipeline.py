@@ -53,26 +53,41 @@ class PipelineRunner:
 
   def __init__(self, model_id: str, hf_cfg: dict, config: dict, rank: int, world: int, device: int, batch: int,
                micro_batches: int, max_ctx: int, max_batch_tokens: int = 8192, page_tokens: int = 64,
-               seed: int = 0, std: float = 0.02, dist=None, weights: Optional[tuple] = None):
+               seed: int = 0, std: float = 0.02, dist=None, weights: Optional[tuple] = None,
+               stage_factory: Optional[Callable] = None, ret_group=None):
+    """``stage_factory(shard) -> stage`` lets the host-side protocol (ordering of the
+    send/recv pairs, micro-batching, token return edge) be exercised without a GPU (the
+    world_size-2 gloo tests plug the CPU oracle in; the product never does)."""
     self.rank, self.world, self.dist = rank, world, dist
+    self.ret_group = ret_group   # separate communicator for the last->first token edge
     self.B, self.M = batch, micro_batches
+    self.tok_work = [None] * micro_batches
     n_layers = config["num_layers"]
     self.shard: Shard = pipeline_shards(model_id, n_layers, world)[rank]
     self.first, self.last = self.shard.is_first_layer(), self.shard.is_last_layer()
-    self.device = torch.device("cuda", device)
-    self.stage = StageRuntime(self.shard, config, device=device, max_batch_tokens=max_batch_tokens,
-                              max_seqs=batch * micro_batches, max_tokens_per_seq=max_ctx, page_tokens=page_tokens)
-    get, has = weights if weights is not None else gpu_random_getter(hf_cfg, seed, std, self.device)
-    self.stage.load_hf_tensors(get, has)
+    if stage_factory is not None:
+      self.stage = stage_factory(self.shard)
+      self.device = torch.device("cpu")
+      self.stream = None
+    else:
+      self.device = torch.device("cuda", device)
+      self.stage = StageRuntime(self.shard, config, device=device, max_batch_tokens=max_batch_tokens,
+                                max_seqs=batch * micro_batches, max_tokens_per_seq=max_ctx, page_tokens=page_tokens)
+      get, has = weights if weights is not None else gpu_random_getter(hf_cfg, seed, std, self.device)
+      self.stage.load_hf_tensors(get, has)
+      self.stream = torch.cuda.Stream(device=self.device)
     self.dim, self.vocab = config["embed_dim"], config["vocab_size"]
     self.max_batch_tokens = max_batch_tokens
-    self.stream = torch.cuda.Stream(device=self.device)
     B, M = batch, micro_batches
     self.tok = [torch.zeros(B, dtype=torch.int32, device=self.device) for _ in range(M)]
     self.h_in = torch.empty((max_batch_tokens, self.dim), dtype=torch.bfloat16, device=self.device)
     self.h_out = torch.empty((max_batch_tokens, self.dim), dtype=torch.bfloat16, device=self.device)
     self.logits = torch.empty((B, self.vocab), dtype=torch.float32, device=self.device) if self.last else None
     self.pos = [0] * M  # context length of each micro-batch (all its sequences share it)
+
+  def _on_stream(self):
+    import contextlib
+    return torch.cuda.stream(self.stream) if self.stream is not None else contextlib.nullcontext()
 
   def slots(self, m: int) -> List[int]:
     return list(range(m * self.B, (m + 1) * self.B))
@@ -83,11 +98,28 @@ class PipelineRunner:
     self.pos = [0] * self.M
 
   # ------------------------------------------------------------------ comms
+  # Forward edge (hidden states, stage i -> i+1): blocking send/recv in micro-batch order on the
+  # default group -- an acyclic chain.  Return edge (sampled ids, last -> first stage): async
+  # isend/irecv on its OWN group, posted ahead of use.  With both edges on one communicator the
+  # last stage's "send ids(m)" and the first stage's "send hidden(m+1)" wait on each other
+  # (p2p ops rendezvous), which deadlocks once more than one micro-batch is in flight.
   def _recv(self, t: torch.Tensor, src: int):
     self.dist.recv(t, src=src)
 
   def _send(self, t: torch.Tensor, dst: int):
     self.dist.send(t, dst=dst)
+
+  def _post_tok_recv(self, m: int):
+    self.tok_work[m] = self.dist.irecv(self.tok[m], src=self.world - 1, group=self.ret_group)
+
+  def _post_tok_send(self, m: int):
+    self.tok_work[m] = self.dist.isend(self.tok[m], dst=0, group=self.ret_group)
+
+  def _wait_tok(self, m: int):
+    w = self.tok_work[m]
+    if w is not None:
+      w.wait()
+      self.tok_work[m] = None
 
   # ------------------------------------------------------------------ prefill
   def prefill(self, prompts: List[torch.Tensor]):
@@ -96,10 +128,12 @@ class PipelineRunner:
     first sampled token of each sequence in ``self.tok[m]`` on rank 0 (sent back by the last
     stage like the reference's last->first ``send_tensor``)."""
     B = self.B
-    with torch.cuda.stream(self.stream):
+    with self._on_stream():
       for m in range(self.M):
         L = prompts[m].shape[1]
         per = max(1, self.max_batch_tokens // L)
+        if self.last and self.world > 1:
+          self._wait_tok(m)
         for c0 in range(0, B, per):
           c1 = min(B, c0 + per)
           n, T = c1 - c0, (c1 - c0) * L
@@ -121,9 +155,9 @@ class PipelineRunner:
         self.pos[m] = L
         if self.world > 1:
           if self.last:
-            self._send(self.tok[m], 0)
+            self._post_tok_send(m)
           elif self.first:
-            pass  # received at the top of the first decode step
+            self._post_tok_recv(m)
 
   # ------------------------------------------------------------------ decode
   def decode(self, steps: int, host_tokens: Optional[List[torch.Tensor]] = None, host_out: Optional[List[torch.Tensor]] = None):
@@ -133,19 +167,20 @@ class PipelineRunner:
     mode); otherwise ids stay on the devices."""
     B, M = self.B, self.M
     ones = [1] * B
-    with torch.cuda.stream(self.stream):
+    with self._on_stream():
       for k in range(steps):
         for m in range(M):
           pos = [self.pos[m]] * B
           slots = self.slots(m)
           if self.first:
             if self.world > 1:
-              self._recv(self.tok[m], self.world - 1)
+              self._wait_tok(m)            # ids sampled by the last stage for this micro-batch
             if host_tokens is not None:
               # the caller's ids live in (pinned) host memory: read back, then upload as this
               # step's input -- what a host-driven caller pays every step
               host_tokens[m].copy_(self.tok[m], non_blocking=True)
-              self.stream.synchronize()
+              if self.stream is not None:
+                self.stream.synchronize()
               self.tok[m].copy_(host_tokens[m], non_blocking=True)
           if self.first and self.last:
             lg = self.stage.forward(slots, ones, pos, tokens=self.tok[m], out=self.logits)
@@ -155,26 +190,28 @@ class PipelineRunner:
           elif self.first:
             out = self.stage.forward(slots, ones, pos, tokens=self.tok[m], out=self.h_out[:B])
             self._send(out, 1)
+            self._post_tok_recv(m)         # next step's ids, posted ahead
           else:
             hid = self.h_in[:B]
             self._recv(hid, self.rank - 1)
             if self.last:
               lg = self.stage.forward(slots, ones, pos, hidden=hid, out=self.logits)
+              self._wait_tok(m)            # previous send of this buffer has completed
               self.stage.sample(lg, temp=0.0, out=self.tok[m])
               if host_out is not None:
                 host_out[m].copy_(self.tok[m], non_blocking=True)
-              self._send(self.tok[m], 0)
+              self._post_tok_send(m)
             else:
               out = self.stage.forward(slots, ones, pos, hidden=hid, out=self.h_out[:B])
               self._send(out, self.rank + 1)
           self.pos[m] += 1
 
   def drain(self):
-    """Match the last stage's final token sends (rank 0 receives them as the next inputs)."""
-    if self.world > 1 and self.first:
-      with torch.cuda.stream(self.stream):
+    """Complete the outstanding return-edge transfers (rank 0 ends up holding the last ids)."""
+    if self.world > 1 and (self.first or self.last):
+      with self._on_stream():
         for m in range(self.M):
-          self._recv(self.tok[m], self.world - 1)
+          self._wait_tok(m)
 
   def close(self):
     self.stage.close()
