@@ -143,6 +143,19 @@ int xb_debug_linear(const void* x, const void* w, int T, int N, int K, float* y,
  * call with CUDA events; *n_launches receives the number of kernels enqueued. */
 int xb_bench_linears(xb_engine* e, int T, int iters, int* n_launches, void* stream);
 
+/* Allocation-free Linear (no counterpart in the reference, which never manages device memory
+ * itself): y[T,N] (fp32) = x[T,K] * w[N,K]^T on device buffers through the engine's split-K
+ * tcgen05 kernel, with the split-K workspace in an 8 MiB array built into the library instead
+ * of caller- or allocator-provided memory.  For callers that must not reach a GPU allocator:
+ * a decode loop that cannot afford the device-wide stall of cudaMalloc/cudaFree between steps,
+ * or a process whose HBM is already fully committed to weights and KV pages.  Performs no
+ * cudaMalloc/cudaFree and creates no framework tensor.  Limits: T <= 128 and
+ * splits*T*N <= 2Mi floats (rejected with the required size otherwise).  The first call on a
+ * device resolves the array's device address: make it before any stream capture.  All calls on
+ * a device share the array (its old contents are never read before being rewritten);
+ * calls that can overlap on the GPU race on it. */
+int xb_linear_noalloc(const void* x, const void* w, int T, int N, int K, float* y, int round_bf16, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

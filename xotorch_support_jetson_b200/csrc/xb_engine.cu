@@ -811,3 +811,62 @@ extern "C" int xb_debug_linear(const void* x, const void* w, int T, int N, int K
   XB_CUDA(cudaGetLastError());
   return 0;
 }
+
+// ----------------------------------------------------------------------------- allocation-free Linear
+// Built-in scratch for xb_linear_noalloc: lives in the library image, so every GPU that loads
+// libxb200 carries these 8 MiB for the life of the process.
+#define XB_NOALLOC_SCRATCH_FLOATS (2u * 1024u * 1024u)
+static __device__ __align__(256) float g_xb_noalloc_scratch[XB_NOALLOC_SCRATCH_FLOATS];
+// Per-device DEVICE address of the array above.  In host code `g_xb_noalloc_scratch` is only a
+// host-side handle for the symbol -- handing it to a kernel would make the kernel write through
+// a host address -- so the real address is looked up once per device and cached here.
+#define XB_NOALLOC_MAX_DEVICES 64
+static float* g_xb_noalloc_ptr[XB_NOALLOC_MAX_DEVICES] = {nullptr};
+
+// y[T,N] = x[T,K] * w[N,K]^T with the engine's split-K tcgen05 Linear, for callers that must
+// not allocate.  A serving loop that calls cudaMalloc/cudaFree (or lets a framework allocator do
+// it) between decode steps stalls every stream of the device on the allocator's implicit
+// synchronisation, and a process that has already handed all of its HBM to weights and KV pages
+// can be refused the few MiB of split-K workspace in the middle of a request.  Here the
+// workspace is the static array above: the call enqueues two kernels and touches no allocator
+// (no cudaMalloc, no cudaFree, no torch tensor is created).
+//
+// * T <= 128 (the weight-streaming "skinny" shape); splits*T*N floats of workspace must fit
+//   XB_NOALLOC_SCRATCH_FLOATS, otherwise the call fails with the required and available sizes.
+// * The first call on each device looks up the array's device address
+//   (cudaGetSymbolAddress, with that device current); make that first call outside any stream
+//   capture.
+// * All calls on a device share the one array and it keeps whatever the previous call left in
+//   it.  Nothing has to be cleared: every workspace element this call reads is written earlier in
+//   the same call (each (split, token, feature) partial is stored by exactly one work unit before
+//   the reduction kernel runs).  Two calls whose kernels can overlap on the GPU (different
+//   streams, or one stream per thread) race on the array -- serialise them.
+extern "C" int xb_linear_noalloc(const void* x, const void* w, int T, int N, int K, float* y, int round_bf16,
+                                 void* stream) {
+  XB_CHECK(x && w && y && T > 0 && N > 0 && K > 0, "bad argument");
+  XB_CHECK(T <= 128, "xb_linear_noalloc handles up to 128 token rows per call (got %d)", T);
+  cudaStream_t st = (cudaStream_t)stream;
+  int dev = 0, sms = 148;
+  XB_CUDA(cudaGetDevice(&dev));
+  XB_CHECK(dev >= 0 && dev < XB_NOALLOC_MAX_DEVICES, "device index %d not supported", dev);
+  if (g_xb_noalloc_ptr[dev] == nullptr) {
+    float* p = nullptr;
+    XB_CUDA(cudaGetSymbolAddress((void**)&p, g_xb_noalloc_scratch));
+    XB_CHECK(p != nullptr, "cudaGetSymbolAddress returned a null address for the built-in scratch");
+    g_xb_noalloc_ptr[dev] = p;
+  }
+  float* scratch = g_xb_noalloc_ptr[dev];
+  XB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  GemmPlan p;
+  XB_TRY(xb_gemm_plan(&p, (const bf16*)x, K, (const bf16*)w, 0, T, N, K, scratch, N, nullptr, 0, sms, 0));
+  const unsigned long long need = (unsigned long long)p.args.splits * T * N;
+  XB_CHECK(need <= XB_NOALLOC_SCRATCH_FLOATS,
+           "xb_linear_noalloc: this shape needs %llu floats of split-K workspace (splits=%d x T=%d x N=%d); the built-in "
+           "buffer holds %u floats (%u MiB)",
+           need, p.args.splits, T, N, XB_NOALLOC_SCRATCH_FLOATS, (unsigned)(XB_NOALLOC_SCRATCH_FLOATS * 4u >> 20));
+  XB_TRY(xb_gemm_run(p, st, 0));
+  const long long n = (long long)T * N;
+  xb_reduce_partials_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>(scratch, p.args.splits, n, y, round_bf16);
+  XB_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -227,3 +227,24 @@ def debug_linear(x: torch.Tensor, w: torch.Tensor, use_tensor_cores: bool = True
                                   C.c_void_p(scratch.data_ptr()), int(use_tensor_cores), int(force_splits), int(round_bf16),
                                   C.c_void_p(stream)))
   return y
+
+
+def linear_noalloc(x: torch.Tensor, w: torch.Tensor, y: torch.Tensor, round_bf16: bool = False) -> torch.Tensor:
+  """xb_linear_noalloc: fp32 ``y[T, N] = x[T, K] @ w[N, K]^T`` into the CALLER's ``y``.
+
+  For callers that must stay away from GPU allocators while they run: a decode loop where a
+  cudaMalloc/cudaFree (or a framework allocator growing its pool) would stall every stream of
+  the device, or a process whose HBM is already fully committed to weights and KV pages.  This
+  wrapper therefore creates no tensor either -- inputs and the output come from the caller and
+  the split-K workspace is an 8 MiB array inside libxb200.  T <= 128; shapes whose workspace
+  does not fit are rejected with a RuntimeError naming the required size.  Calls share that one
+  array: do not let two of them overlap on the GPU."""
+  lib = _cabi.load()
+  T, K = x.shape
+  N = w.shape[0]
+  assert x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and y.dtype == torch.float32
+  assert y.shape == (T, N) and x.is_contiguous() and w.is_contiguous() and y.is_contiguous()
+  stream = torch.cuda.current_stream(x.device).cuda_stream
+  _cabi.check(lib.xb_linear_noalloc(C.c_void_p(x.data_ptr()), C.c_void_p(w.data_ptr()), T, N, K, C.c_void_p(y.data_ptr()),
+                                    int(round_bf16), C.c_void_p(stream)))
+  return y
