@@ -197,3 +197,16 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
 __host__ __device__ constexpr uint32_t umma_idesc_bf16(int n) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
 }
+
+// How split-K partial sums of one output column are laid out: `slots` fp32 planes of [T][N].
+// Fixed split: every column has `splits` planes.  Stream-K: the planes of a 128-column tile are
+// the consecutive blocks whose item range touches the tile.
+struct SplitInfo {
+  int k_blocks, q, splits;
+};
+__host__ __device__ __forceinline__ int xb_n_segments(const SplitInfo& si, int col) {
+  if (si.q <= 0) return si.splits;
+  const int tile = col >> 7;
+  return ((tile + 1) * si.k_blocks - 1) / si.q - (tile * si.k_blocks) / si.q + 1;
+}
+

@@ -396,7 +396,7 @@ static int get_plan(xb_engine* e, int site, int layer, const bf16* x, long long 
     GemmPlan p;
     XB_TRY(xb_gemm_plan(&p, x, ldx, w, 1, T, N, K, out, ld_out, bias, round_bf16, e->num_sms, 0));
     if (out == e->gemm_out) {
-      const size_t need = p.args.mode == XB_GEMM_SKINNY ? (size_t)p.args.splits * T * N * 4 : (size_t)T * N * 2;
+      const size_t need = p.args.mode == XB_GEMM_SKINNY ? (size_t)p.split.splits * T * N * 4 : (size_t)T * N * 2;
       XB_CHECK(need <= e->gemm_out_bytes, "gemm workspace too small: need %zu have %zu", need, e->gemm_out_bytes);
     }
     it = e->plans.emplace(key, p).first;
@@ -463,7 +463,7 @@ template <int CL, int NT, int VPT>
 static int launch_resid_norm_cluster(xb_engine* e, const GemmPlan* gp, int T, const bf16* nw, cudaStream_t st) {
   const xb_model_desc& d = e->d;
   return launch_k(e, xb_resid_norm_cluster_kernel<CL, NT, VPT>, dim3(CL, T, 1), dim3(NT), 0, st, CL, (const float*)e->gemm_out,
-                  gp->args.splits, (long long)T * d.dim, e->h, nw, e->hn, d.dim, d.norm_eps, d.rmsnorm_two_round);
+                  gp->split, (long long)T * d.dim, e->h, nw, e->hn, d.dim, d.norm_eps, d.rmsnorm_two_round);
 }
 
 static int launch_resid_norm(xb_engine* e, const GemmPlan* gp, int T, const bf16* nw, cudaStream_t st) {
@@ -474,10 +474,10 @@ static int launch_resid_norm(xb_engine* e, const GemmPlan* gp, int T, const bf16
     if (d.dim % 32 == 0 && d.dim / 8 <= 128 * 4 * 2)
       return d.dim / 8 <= 128 * 4 ? launch_resid_norm_cluster<8, 128, 1>(e, gp, T, nw, st)
                                   : launch_resid_norm_cluster<8, 128, 2>(e, gp, T, nw, st);
-    XB_TRY(launch_k(e, xb_resid_norm_kernel<256, 0>, dim3(T), dim3(256), smem, st, 1, (const float*)e->gemm_out, gp->args.splits, (long long)T * d.dim,
+    XB_TRY(launch_k(e, xb_resid_norm_kernel<256, 0>, dim3(T), dim3(256), smem, st, 1, (const float*)e->gemm_out, gp->split, (long long)T * d.dim,
                                                         nullptr, e->h, nw, e->hn, d.dim, d.norm_eps, d.rmsnorm_two_round));
   } else {
-    XB_TRY(launch_k(e, xb_resid_norm_kernel<256, 1>, dim3(T), dim3(256), smem, st, 1, nullptr, 1, 0, (const bf16*)e->gemm_out, e->h, nw, e->hn, d.dim,
+    XB_TRY(launch_k(e, xb_resid_norm_kernel<256, 1>, dim3(T), dim3(256), smem, st, 1, nullptr, SplitInfo{1, 0, 1}, 0, (const bf16*)e->gemm_out, e->h, nw, e->hn, d.dim,
                                                         d.norm_eps, d.rmsnorm_two_round));
   }
   return 0;
@@ -506,7 +506,7 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
     XB_TRY(launch_k(e, xb_embed_norm_kernel<256>, dim3(T), dim3(256), 0, st, 1, e->in_tokens, e->embed, e->L[0].sa_norm, e->h, e->hn, D, d.vocab, d.norm_eps,
                                                   d.rmsnorm_two_round));
   } else {
-    XB_TRY(launch_k(e, xb_resid_norm_kernel<256, 2>, dim3(T), dim3(256), norm_smem, st, 1, nullptr, 0, 0, nullptr, e->h, e->L[0].sa_norm, e->hn, D,
+    XB_TRY(launch_k(e, xb_resid_norm_kernel<256, 2>, dim3(T), dim3(256), norm_smem, st, 1, nullptr, SplitInfo{1, 0, 1}, 0, nullptr, e->h, e->L[0].sa_norm, e->hn, D,
                                                              d.norm_eps, d.rmsnorm_two_round));
   }
 
@@ -520,12 +520,15 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
     {
       dim3 grid(T, d.n_heads + 2 * d.n_kv_heads);
       if (gp->args.mode == XB_GEMM_SKINNY)
-        XB_TRY(launch_k(e, xb_qkv_finalize_kernel<0>, dim3(grid), dim3(hd / 2), 0, st, 1, (const float*)e->gemm_out, gp->args.splits, (long long)T * e->NQKV,
+        XB_TRY(launch_k(e, xb_qkv_finalize_kernel<0>, dim3(grid), dim3(hd / 2), 0, st, 1, (const float*)e->gemm_out, gp->split, (long long)T * e->NQKV,
                                                             nullptr, w.bqkv, e->rope, e->q, w.k_pool, w.v_pool, m, d.n_heads,
                                                             d.n_kv_heads, hd, d.rope_kind));
-      else
-        XB_TRY(launch_k(e, xb_qkv_finalize_kernel<1>, dim3(grid), dim3(hd / 2), 0, st, 1, nullptr, 1, 0, (const bf16*)e->gemm_out, nullptr, e->rope, e->q,
-                                                            w.k_pool, w.v_pool, m, d.n_heads, d.n_kv_heads, hd, d.rope_kind));
+      else {
+        const long long items = (long long)T * (d.n_heads + 2 * d.n_kv_heads) * (d.rope_kind == 0 ? hd / 8 : hd / 16);
+        XB_TRY(launch_k(e, xb_qkv_finalize_wide_kernel, dim3((unsigned)((items + 255) / 256)), dim3(256), 0, st, 1,
+                        (const bf16*)e->gemm_out, e->rope, e->q, w.k_pool, w.v_pool, m, T, d.n_heads, d.n_kv_heads, hd,
+                        d.rope_kind));
+      }
     }
     if (hd == 128) XB_TRY(launch_attn<128>(e, w, m, T, n_splits, n_tiles, st));
     else XB_TRY(launch_attn<64>(e, w, m, T, n_splits, n_tiles, st));
@@ -542,10 +545,11 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
       const long long n = (long long)T * I;
       const int blocks = (int)((n + 255) / 256);
       if (gp->args.mode == XB_GEMM_SKINNY)
-        XB_TRY(launch_k(e, xb_silu_mul_kernel<0>, dim3(blocks), dim3(256), 0, st, 1, (const float*)e->gemm_out, gp->args.splits, (long long)T * 2 * I, nullptr,
+        XB_TRY(launch_k(e, xb_silu_mul_kernel<0>, dim3(blocks), dim3(256), 0, st, 1, (const float*)e->gemm_out, gp->split, (long long)T * 2 * I, nullptr,
                                                        e->act, T, I));
       else
-        XB_TRY(launch_k(e, xb_silu_mul_kernel<1>, dim3(blocks), dim3(256), 0, st, 1, nullptr, 1, 0, (const bf16*)e->gemm_out, e->act, T, I));
+        XB_TRY(launch_k(e, xb_silu_mul_wide_kernel, dim3((unsigned)(((long long)T * (I / 8) + 255) / 256)), dim3(256), 0, st, 1,
+                        (const bf16*)e->gemm_out, e->act, T, I));
     }
     XB_TRY(get_plan(e, SITE_DOWN, l, e->act, I, w.wdown, T, D, I, e->gemm_out, D, nullptr, 0, &gp));
     XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
@@ -773,11 +777,12 @@ extern "C" int xb_get_counters(xb_engine* e, xb_counters* out) {
 }
 
 // ----------------------------------------------------------------------------- kernel-level test hook
-__global__ void xb_reduce_partials_kernel(const float* __restrict__ part, int splits, long long n, float* __restrict__ y,
-                                          int round_bf16) {
+__global__ void xb_reduce_partials_kernel(const float* __restrict__ part, SplitInfo si, int N, long long n,
+                                          float* __restrict__ y, int round_bf16) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   float a = 0.f;
+  const int splits = xb_n_segments(si, (int)(i % N));
   for (int s = 0; s < splits; ++s) a += part[s * n + i];
   y[i] = round_bf16 ? rbf(a) : a;
 }
@@ -805,7 +810,7 @@ extern "C" int xb_debug_linear(const void* x, const void* w, int T, int N, int K
   const long long n = (long long)T * N;
   const int blocks = (int)((n + 255) / 256);
   if (p.args.mode == XB_GEMM_SKINNY)
-    xb_reduce_partials_kernel<<<blocks, 256, 0, st>>>(scratch, p.args.splits, n, y, round_bf16);
+    xb_reduce_partials_kernel<<<blocks, 256, 0, st>>>(scratch, p.split, N, n, y, round_bf16);
   else
     xb_bf16_to_f32_kernel<<<blocks, 256, 0, st>>>((const bf16*)scratch, n, y);
   XB_CUDA(cudaGetLastError());
@@ -859,14 +864,14 @@ extern "C" int xb_linear_noalloc(const void* x, const void* w, int T, int N, int
   XB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   GemmPlan p;
   XB_TRY(xb_gemm_plan(&p, (const bf16*)x, K, (const bf16*)w, 0, T, N, K, scratch, N, nullptr, 0, sms, 0));
-  const unsigned long long need = (unsigned long long)p.args.splits * T * N;
+  const unsigned long long need = (unsigned long long)p.split.splits * T * N;
   XB_CHECK(need <= XB_NOALLOC_SCRATCH_FLOATS,
            "xb_linear_noalloc: this shape needs %llu floats of split-K workspace (splits=%d x T=%d x N=%d); the built-in "
            "buffer holds %u floats (%u MiB)",
-           need, p.args.splits, T, N, XB_NOALLOC_SCRATCH_FLOATS, (unsigned)(XB_NOALLOC_SCRATCH_FLOATS * 4u >> 20));
+           need, p.split.splits, T, N, XB_NOALLOC_SCRATCH_FLOATS, (unsigned)(XB_NOALLOC_SCRATCH_FLOATS * 4u >> 20));
   XB_TRY(xb_gemm_run(p, st, 0));
   const long long n = (long long)T * N;
-  xb_reduce_partials_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>(scratch, p.args.splits, n, y, round_bf16);
+  xb_reduce_partials_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>(scratch, p.split, N, n, y, round_bf16);
   XB_CUDA(cudaGetLastError());
   return 0;
 }

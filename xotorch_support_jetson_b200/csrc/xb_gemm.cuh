@@ -37,6 +37,8 @@ struct GemmArgs {
   int mode;
   int round_bf16;          // SKINNY: round the fp32 result to bf16 precision (splits == 1 only)
   int w_tiled;             // weight operand is stored tile-major: [N/128][K/64][128][64]
+  int sk_q;                // > 0: stream-K -- block b owns items [b*sk_q, (b+1)*sk_q) of the
+  int sk_items;            //      a_tiles*k_blocks (tile-major, k-block-minor) item space
   void* out;
   long long ld_out;        // SKINNY: N (floats per token row); WIDE: elements per token row
   const bf16* bias;        // WIDE: per-feature bias or nullptr
@@ -47,6 +49,45 @@ __device__ __forceinline__ void gemm_w_coord(const GemmArgs& g, int wt, int kb, 
   if (g.w_tiled) { c0 = 0; c1 = (wt * g.k_blocks + kb) * 128; }
   else { c0 = kb * 64; c1 = wt * 128; }
 }
+
+struct GemmUnit {
+  int ta, tb, kb0, kb1, slot;
+};
+// Walks the work units of one block; all three warp roles walk the same sequence.
+struct UnitWalker {
+  int u, it, end;
+  __device__ __forceinline__ void init(const GemmArgs& g) {
+    if (g.sk_q > 0) {
+      it = blockIdx.x * g.sk_q;
+      end = it + g.sk_q < g.sk_items ? it + g.sk_q : g.sk_items;
+    } else {
+      u = blockIdx.x;
+    }
+  }
+  __device__ __forceinline__ bool next(const GemmArgs& g, GemmUnit& w) {
+    if (g.sk_q > 0) {
+      if (it >= end) return false;
+      w.ta = it / g.k_blocks;
+      w.tb = 0;
+      w.kb0 = it - w.ta * g.k_blocks;
+      const int left = end - it;
+      w.kb1 = w.kb0 + left < g.k_blocks ? w.kb0 + left : g.k_blocks;
+      w.slot = blockIdx.x - (w.ta * g.k_blocks) / g.sk_q;
+      it += w.kb1 - w.kb0;
+      return true;
+    }
+    if (u >= g.a_tiles * g.b_tiles * g.splits) return false;
+    const int s = u % g.splits;
+    const int tile = u / g.splits;
+    w.ta = tile % g.a_tiles;
+    w.tb = tile / g.a_tiles;
+    w.kb0 = (int)(((long long)s * g.k_blocks) / g.splits);
+    w.kb1 = (int)(((long long)(s + 1) * g.k_blocks) / g.splits);
+    w.slot = s;
+    u += gridDim.x;
+    return true;
+  }
+};
 
 template <int BN, int STAGES>
 struct GemmCfg {
@@ -100,7 +141,9 @@ xb_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   const uint32_t tmem_base = *tmem_slot;
   pdl_launch_dependents();   // the next kernel may start its prologue / weight prefetch now
 
-  const int total_units = g.a_tiles * g.b_tiles * g.splits;
+  UnitWalker walk;
+  walk.init(g);
+  GemmUnit wu;
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -109,13 +152,8 @@ xb_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       uint32_t phase = 0;
       bool waited = false;
       int pre = 0;   // stages whose weight box was issued ahead of the dependency wait
-      for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
-        const int s = u % g.splits;
-        const int tile = u / g.splits;
-        const int ta = tile % g.a_tiles;
-        const int tb = tile / g.a_tiles;
-        const int kb0 = (int)(((long long)s * g.k_blocks) / g.splits);
-        const int kb1 = (int)(((long long)(s + 1) * g.k_blocks) / g.splits);
+      while (walk.next(g, wu)) {
+        const int ta = wu.ta, tb = wu.tb, kb0 = wu.kb0, kb1 = wu.kb1;
         if (!waited) {
           // first unit: weight boxes of up to STAGES k-blocks go out before the upstream grid is done
           const int npre = (kb1 - kb0) < STAGES ? (kb1 - kb0) : STAGES;
@@ -181,10 +219,8 @@ xb_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       constexpr uint32_t idesc = umma_idesc_bf16(BN);
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
-      for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
-        const int s = u % g.splits;
-        const int kb0 = (int)(((long long)s * g.k_blocks) / g.splits);
-        const int kb1 = (int)(((long long)(s + 1) * g.k_blocks) / g.splits);
+      while (walk.next(g, wu)) {
+        const int kb0 = wu.kb0, kb1 = wu.kb1;
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);   // epilogue has drained this accumulator
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
@@ -212,11 +248,8 @@ xb_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     pdl_wait();                                       // `out` may still be read by the upstream grid
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int u = blockIdx.x; u < total_units; u += gridDim.x) {
-      const int s = u % g.splits;
-      const int tile = u / g.splits;
-      const int ta = tile % g.a_tiles;
-      const int tb = tile / g.a_tiles;
+    while (walk.next(g, wu)) {
+      const int s = wu.slot, ta = wu.ta, tb = wu.tb;
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN);
@@ -390,6 +423,7 @@ static int xb_gemm_launch_t(const CUtensorMap& tmA, const CUtensorMap& tmB, cons
 struct GemmPlan {
   CUtensorMap tmA, tmB;
   GemmArgs args;
+  SplitInfo split;   // how a consumer sums the fp32 partial planes (SKINNY)
   int bn;
   int grid;
 };
@@ -417,23 +451,20 @@ static int xb_gemm_plan(GemmPlan* p, const bf16* x, long long ldx, const bf16* w
     g.b_tiles = 1;
     g.a_rows = N;
     g.b_rows = T;
-    int splits = force_splits;
-    if (splits <= 0) {
-      // enough units that every SM streams weights, bounded so the fp32 partials stay a
-      // small fraction (<~6%) of the weight bytes and every unit keeps >= 4 k-blocks
-      splits = (2 * num_sms + g.a_tiles - 1) / g.a_tiles;
-      int cap_traffic = (int)((0.03 * K) / (T > 0 ? T : 1));
-      if (cap_traffic < 1) cap_traffic = 1;
-      int cap_k = g.k_blocks / 4;
-      if (cap_k < 1) cap_k = 1;
-      if (splits > cap_traffic) splits = cap_traffic;
-      if (splits > cap_k) splits = cap_k;
-      if (splits > 16) splits = 16;
-      if (splits < 1) splits = 1;
-    }
-    if (round_bf16) splits = 1;
+    g.sk_q = 0;
+    g.sk_items = g.a_tiles * g.k_blocks;
+    int splits = force_splits > 0 ? force_splits : 1;
+    if (round_bf16) splits = 1;          // the result is final: whole tiles, no partial planes
     if (splits > g.k_blocks) splits = g.k_blocks;
     g.splits = splits;
+    if (force_splits <= 0 && !round_bf16) {
+      // stream-K: one block per SM, each owning an equal contiguous range of (tile, k-block) items
+      int grid = num_sms;
+      if (g.sk_items < grid * 2) grid = (g.sk_items + 1) / 2;
+      if (grid < 1) grid = 1;
+      g.sk_q = (g.sk_items + grid - 1) / grid;
+      g.splits = (g.k_blocks + g.sk_q - 1) / g.sk_q + 1;   // most planes any tile can have
+    }
     if (w_tiled) XB_TRY(xb_make_tmap(&p->tmA, w, w_tiles * g.k_blocks * 128, 64, 64, 128));
     else XB_TRY(xb_make_tmap(&p->tmA, w, N, K, K, 128));
     XB_TRY(xb_make_tmap(&p->tmB, x, T, K, ldx, bn));
@@ -445,13 +476,23 @@ static int xb_gemm_plan(GemmPlan* p, const bf16* x, long long ldx, const bf16* w
     g.a_rows = T;
     g.b_rows = N;
     g.splits = 1;
+    g.sk_q = 0;
+    g.sk_items = 0;
     XB_TRY(xb_make_tmap(&p->tmA, x, T, K, ldx, 128));
     if (w_tiled) XB_TRY(xb_make_tmap(&p->tmB, w, w_tiles * g.k_blocks * 128, 64, 64, 128));
     else XB_TRY(xb_make_tmap(&p->tmB, w, N, K, K, 256));
   }
-  const int units = g.a_tiles * g.b_tiles * g.splits;
-  const int per_sm = (p->bn <= 64) ? 2 : 1;   // smem allows two resident CTAs for the small-BN configs
-  p->grid = units < num_sms * per_sm ? units : num_sms * per_sm;
+  // one block per SM: under programmatic dependent launch the NEXT kernel's block co-resides
+  // and prefetches its first weight stages while this one drains
+  if (g.mode == XB_GEMM_SKINNY && g.sk_q > 0) {
+    p->grid = (g.sk_items + g.sk_q - 1) / g.sk_q;
+  } else {
+    const int units = g.a_tiles * g.b_tiles * g.splits;
+    p->grid = units < num_sms ? units : num_sms;
+  }
+  p->split.k_blocks = g.k_blocks;
+  p->split.q = g.mode == XB_GEMM_SKINNY ? g.sk_q : 0;
+  p->split.splits = g.mode == XB_GEMM_SKINNY ? g.splits : 1;
   return 0;
 }
 
