@@ -54,7 +54,8 @@ class PipelineRunner:
   def __init__(self, model_id: str, hf_cfg: dict, config: dict, rank: int, world: int, device: int, batch: int,
                micro_batches: int, max_ctx: int, max_batch_tokens: int = 8192, page_tokens: int = 64,
                seed: int = 0, std: float = 0.02, dist=None, weights: Optional[tuple] = None,
-               stage_factory: Optional[Callable] = None, ret_group=None):
+               stage_factory: Optional[Callable] = None, ret_group=None,
+               balance_head: bool = True):
     """``stage_factory(shard) -> stage`` lets the host-side protocol (ordering of the
     send/recv pairs, micro-batching, token return edge) be exercised without a GPU (the
     world_size-2 gloo tests plug the CPU oracle in; the product never does)."""
@@ -63,7 +64,11 @@ class PipelineRunner:
     self.B, self.M = batch, micro_batches
     self.tok_work = [None] * micro_batches
     n_layers = config["num_layers"]
-    self.shard: Shard = pipeline_shards(model_id, n_layers, world)[rank]
+    # the last stage also streams the LM head every step: weigh it in layer units
+    D, I = config["embed_dim"], config["intermediate_dim"]
+    layer_params = 2 * D * config["num_heads"] * config["head_dim"] + 2 * D * config["num_kv_heads"] * config["head_dim"] + 3 * D * I
+    head_equiv = config["vocab_size"] * D / layer_params if balance_head else 0.0
+    self.shard: Shard = pipeline_shards(model_id, n_layers, world, head_equiv)[rank]
     self.first, self.last = self.shard.is_first_layer(), self.shard.is_last_layer()
     if stage_factory is not None:
       self.stage = stage_factory(self.shard)

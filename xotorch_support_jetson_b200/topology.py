@@ -116,16 +116,34 @@ def map_partitions_to_shards(partitions: List[Partition], num_layers: int, model
   return shards
 
 
-def box_topology(n_gpus: int, memory_mb: int = 183359) -> Topology:
-  """n equal B200 nodes named so that the ring order (memory desc, node id desc) is gpu0, gpu1, ..."""
+def box_topology(n_gpus: int, memory_mb: int = 183359, last_stage_reserved: float = 0.0) -> Topology:
+  """n B200 nodes named so that the ring order (memory desc, node id desc) is gpu0, gpu1, ...
+
+  ``last_stage_reserved`` (fraction of one node's share, 0..1) is the part of the LAST GPU's
+  capacity that is spoken for by the LM head, which the last shard holds and streams every
+  decode step on top of its layers.  The memory-weighted strategy then hands that GPU
+  proportionally fewer layers, so the stages of the pipeline stream equal bytes per step."""
   t = Topology()
   for i in range(n_gpus):
-    t.update_node(f"gpu{n_gpus - 1 - i:02d}-rank{i}", b200_device_capabilities(memory_mb))
+    mem = memory_mb
+    if i == n_gpus - 1 and n_gpus > 1 and last_stage_reserved > 0:
+      mem = max(1, int(round(memory_mb * (1.0 - last_stage_reserved))))
+    t.update_node(f"gpu{n_gpus - 1 - i:02d}-rank{i}", b200_device_capabilities(mem))
   return t
 
 
-def pipeline_shards(model_id: str, n_layers: int, n_gpus: int) -> List[Shard]:
-  """Layer ranges of an n_gpus pipeline, exactly what the reference's ring strategy +
-  map_partitions_to_shards assign to n equal-memory peers; entry i belongs to rank i."""
-  parts = RingMemoryWeightedPartitioningStrategy().partition(box_topology(n_gpus))
+def pipeline_shards(model_id: str, n_layers: int, n_gpus: int, head_layer_equiv: float = 0.0) -> List[Shard]:
+  """Layer ranges of an n_gpus pipeline: what the reference's ring strategy +
+  map_partitions_to_shards assign to the n per-GPU nodes; entry i belongs to rank i.
+
+  ``head_layer_equiv`` = bytes of the LM head / bytes of one decoder layer.  With 0 the nodes
+  are equal (the reference's view: 32 layers -> 8 x 4).  With the real value the last node's
+  capacity is reduced so that (its layers + head) matches the other stages' layers."""
+  reserved = 0.0
+  if head_layer_equiv > 0 and n_gpus > 1:
+    per_stage = (n_layers + head_layer_equiv) / n_gpus          # balanced cost per stage, in layers
+    last_layers = max(1.0, per_stage - head_layer_equiv)
+    other_layers = (n_layers - last_layers) / (n_gpus - 1)
+    reserved = max(0.0, 1.0 - last_layers / other_layers)
+  parts = RingMemoryWeightedPartitioningStrategy().partition(box_topology(n_gpus, last_stage_reserved=reserved))
   return map_partitions_to_shards(parts, n_layers, model_id)
