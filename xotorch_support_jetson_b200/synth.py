@@ -47,11 +47,13 @@ def hf_param_shapes(cfg: dict) -> Dict[str, tuple]:
 
 def random_hf_state(cfg: dict, seed: int = 0, std: float = 0.02, norm_jitter: float = 0.0,
                     dtype: torch.dtype = torch.bfloat16, only_layers: Optional[range] = None,
-                    peaked_head: float = 0.0) -> Dict[str, torch.Tensor]:
+                    peaked_head: float = 0.0, embed_std: Optional[float] = None) -> Dict[str, torch.Tensor]:
   """Seeded random-init state dict in HF naming.  Each tensor draws from its own
   generator (seed, name-hash) so a layer-range subset equals the same rows of the full
   model.  ``peaked_head`` > 0 plants ``lm_head = peaked_head * embed + noise`` so greedy
-  decoding has top-2 margins far above one bf16 ulp (hard parts)."""
+  decoding has top-2 margins far above one bf16 ulp (SURVEY.md section 7, hard parts);
+  ``embed_std`` scales the embedding table alone (with a tied head a larger table keeps the
+  last token's own embedding visible in the residual stream, which peaks the logits)."""
   out = {}
   names = sorted(hf_param_shapes(cfg).items())
   for idx, (name, shape) in enumerate(names):
@@ -64,6 +66,8 @@ def random_hf_state(cfg: dict, seed: int = 0, std: float = 0.02, norm_jitter: fl
       t = torch.ones(shape)
       if norm_jitter:
         t = t + norm_jitter * torch.randn(shape, generator=g)
+    elif name == "model.embed_tokens.weight" and embed_std is not None:
+      t = embed_std * torch.randn(shape, generator=g)
     else:
       t = std * torch.randn(shape, generator=g)
     out[name] = t.to(dtype)
