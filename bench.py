@@ -186,7 +186,10 @@ def run_b200(args):
   torch.cuda.set_device(local)
   ret_group = None
   if world > 1:
-    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    # lazy communicator init (no device_id): point-to-point ops then get per-peer communicators
+    # instead of being serialised as collectives on the default group
+    os.environ.setdefault("TORCH_NCCL_SHOW_EAGER_INIT_P2P_SERIALIZATION_WARNING", "false")
+    dist.init_process_group("nccl")
     ret_group = dist.new_group(ranks=list(range(world)))   # own communicator for the token return edge
   graft.build()
   from xotorch_support_jetson_b200.model_config import load_model_config  # noqa: F401

@@ -100,6 +100,18 @@ def test_llama32_1b_teacher_forced_64_steps_within_tolerance(built_lib):
         f"oracle margins: min {margin.min():.4f} ({(margin / ulp).min():.1f} ulps), {int(strict.sum())}/{N} steps above 4 ulps, "
         f"{n_strict_ok} of those identical; all-steps identical {int((mine == ref_toks[0]).sum())}/{N}; "
         f"free-running identical prefix {free_prefix}")
+  # accuracy against an fp32 evaluation of the same weights: the CUDA engine must be no further
+  # from the fp32 answer than the bf16 reference path itself is (prefill logits)
+  from xotorch_support_jetson_b200.models import model_cards
+  from xotorch_support_jetson_b200.synth import random_hf_state
+  state32 = random_hf_state(model_cards["llama-3.2-1b"]["hf_config"], seed=0, std=0.02)
+  ref32 = O.OracleShardModel(cfg, "llama-3.2-1b", 0, nl - 1, state32, O.OracleOptions(rope_table_dtype="fp32"), dtype=torch.float32)
+  _, l32, _ = O.greedy_generate([ref32], prompt, 1, collect_logits=True)
+  truth = l32[0][0]
+  e_gpu = float(np.abs(got[0] - truth).max() / np.abs(truth).max())
+  e_ref = float(np.abs(ref_l[0] - truth).max() / np.abs(truth).max())
+  print(f"[1B plain] prefill logits vs fp32 evaluation: CUDA engine rel err {e_gpu:.4f}, bf16 oracle rel err {e_ref:.4f}")
+  assert e_gpu < 1.5 * e_ref + 0.005
   assert hid_rel < REL_TOL and rel < REL_TOL
   assert n_strict_ok == int(strict.sum())
   for i in range(N):   # near-ties: the CUDA pick must be one of the oracle's near-top candidates
