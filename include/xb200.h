@@ -143,6 +143,12 @@ int xb_debug_linear(const void* x, const void* w, int T, int N, int K, float* y,
  * call with CUDA events; *n_launches receives the number of kernels enqueued. */
 int xb_bench_linears(xb_engine* e, int T, int iters, int* n_launches, void* stream);
 
+/* Measurement hook: the decode attention kernel(s) of this shard's first layer
+ * (torchtune MultiHeadAttention's SDPA over the KV cache, general_mha.py:78-106) for the batch of
+ * the last xb_forward call, `iters` times back to back, with `n_splits` kv splits (0 = the
+ * engine's choice, returned in *splits_used). */
+int xb_bench_attention(xb_engine* e, int n_seqs, int max_ctx, int n_splits, int iters, int* splits_used, void* stream);
+
 /* Allocation-free Linear (no counterpart in the reference, which never manages device memory
  * itself): y[T,N] (fp32) = x[T,K] * w[N,K]^T on device buffers through the engine's split-K
  * tcgen05 kernel, with the split-K workspace in an 8 MiB array built into the library instead

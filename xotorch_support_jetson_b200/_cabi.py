@@ -11,7 +11,7 @@ _LIB_NAME = "libxb200.so"
 SYMBOLS = (
   "xb_last_error", "xb_abi_version", "xb_engine_create", "xb_engine_destroy", "xb_load_weight",
   "xb_kv_reserve", "xb_kv_release_slot", "xb_kv_slot_len", "xb_forward", "xb_sample",
-  "xb_get_counters", "xb_debug_linear", "xb_bench_linears", "xb_linear_noalloc",
+  "xb_get_counters", "xb_debug_linear", "xb_bench_linears", "xb_bench_attention", "xb_linear_noalloc",
 )
 
 # weight kinds (enum in xb200.h)
@@ -80,6 +80,7 @@ def load():
   lib.xb_debug_linear.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
                                   C.c_int, C.c_int, C.c_void_p]
   lib.xb_linear_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p]
+  lib.xb_bench_attention.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_void_p]
   lib.xb_bench_linears.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_void_p]
   for name in SYMBOLS:
     fn = getattr(lib, name)

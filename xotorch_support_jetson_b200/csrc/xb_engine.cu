@@ -483,6 +483,23 @@ static int launch_resid_norm(xb_engine* e, const GemmPlan* gp, int T, const bf16
   return 0;
 }
 
+// kv splits of a decode batch.  Measured on B200 (profiles/attn_sweep.py, Llama-3.1-8B geometry,
+// ctx 2048): the kernel is fastest when the whole grid is ONE wave of about two blocks per SM --
+// 32 seqs x 8 kv heads unsplit (45 us, 5.96 TB/s) beats any split; 8 seqs want 4 splits, 1 seq 16.
+// More splits only add partial traffic and combine work.
+static int choose_kv_splits(xb_engine* e, int T, int max_ctx) {
+  const char* ov = getenv("XB_ATTN_SPLITS");
+  const int blocks = T * e->d.n_kv_heads;
+  const int tiles = (max_ctx + XB_ATT_TILE - 1) / XB_ATT_TILE;
+  int n = (2 * e->num_sms) / blocks;          // largest split count that still fits one wave
+  if (n > 16) n = 16;
+  if (ov != nullptr && atoi(ov) > 0) n = atoi(ov);
+  if (n > tiles) n = tiles;
+  if (n > e->max_attn_splits) n = e->max_attn_splits;
+  if (n < 1) n = 1;
+  return n;
+}
+
 // All kernel launches of one forward over T token rows.  Reads e->in_tokens (first shard) or
 // e->h (other shards); leaves the residual stream in e->h and, on a last shard, the logits
 // of each sequence's last position in e->logits.  Pure stream work on fixed addresses, so it
@@ -664,18 +681,12 @@ extern "C" int xb_forward(xb_engine* e, const xb_batch* b, void* out, void* cons
   if (first) XB_CUDA(cudaMemcpyAsync(e->in_tokens, b->tokens, (size_t)T * 4, cudaMemcpyDeviceToDevice, st));
   else XB_CUDA(cudaMemcpyAsync(e->h, b->hidden_in, (size_t)T * d.dim * 2, cudaMemcpyDeviceToDevice, st));
 
-  // decode: split each context so that a block streams ~8 key tiles and the grid holds at least
-  // two blocks per SM; prefill: one block per (query tile, kv head), no kv split
+  // decode: split every context across blocks (split-KV); prefill: one block per (query tile,
+  // kv head), no kv split
   int n_splits = 1;
   if (decode_only) {
     XB_CHECK(T <= 2 * e->num_sms, "decode batch of %d sequences exceeds the %d the split-KV workspace covers", T, 2 * e->num_sms);
-    const int blocks = T * d.n_kv_heads;
-    const int tiles = (max_ctx + XB_ATT_TILE - 1) / XB_ATT_TILE;
-    const int fill = (2 * e->num_sms + blocks - 1) / blocks;
-    n_splits = (tiles + 7) / 8 > fill ? (tiles + 7) / 8 : fill;
-    if (n_splits > tiles) n_splits = tiles;
-    if (n_splits > e->max_attn_splits) n_splits = e->max_attn_splits;
-    if (n_splits < 1) n_splits = 1;
+    n_splits = choose_kv_splits(e, T, max_ctx);
   }
 
   if (decode_only && e->use_graphs && taps == nullptr && st != nullptr && st != cudaStreamLegacy) {
@@ -751,6 +762,29 @@ extern "C" int xb_bench_linears(xb_engine* e, int T, int iters, int* n_launches,
   }
   e->c.launches += n;
   if (n_launches) *n_launches = n;
+  return 0;
+}
+
+// Measurement hook: the decode attention of local layer 0 for the batch of the LAST xb_forward
+// call (its metadata is still on the device), `iters` times back to back with the given kv-split
+// count (0 = the engine's own choice for that batch).  The caller brackets it with CUDA events.
+extern "C" int xb_bench_attention(xb_engine* e, int n_seqs, int max_ctx, int n_splits, int iters, int* splits_used,
+                                  void* stream) {
+  XB_CHECK(e != nullptr && n_seqs > 0 && n_seqs <= e->d.max_seqs && iters > 0, "bad argument");
+  const xb_model_desc& d = e->d;
+  cudaStream_t st = (cudaStream_t)stream;
+  XB_CUDA(cudaSetDevice(e->device));
+  BatchMeta m;
+  m.tok_seq = e->d_tok_seq; m.tok_pos = e->d_tok_pos; m.seq_slot = e->d_seq_slot; m.seq_last = e->d_seq_last;
+  m.page_table = e->d_page_table; m.tile_start = e->d_tile_start; m.tile_len = e->d_tile_len;
+  m.max_pages = e->max_pages; m.page_tokens = e->page_tokens;
+  if (n_splits <= 0) n_splits = choose_kv_splits(e, n_seqs, max_ctx);
+  XB_CHECK(n_splits <= e->max_attn_splits, "n_splits %d above the workspace limit %d", n_splits, e->max_attn_splits);
+  for (int it = 0; it < iters; ++it) {
+    if (d.head_dim == 128) XB_TRY(launch_attn<128>(e, e->L[0], m, n_seqs, n_splits, 0, st));
+    else XB_TRY(launch_attn<64>(e, e->L[0], m, n_seqs, n_splits, 0, st));
+  }
+  if (splits_used) *splits_used = n_splits;
   return 0;
 }
 

@@ -193,6 +193,14 @@ class StageRuntime:
     _cabi.check(self.lib.xb_bench_linears(self._h, int(T), int(iters), C.byref(n), C.c_void_p(stream)))
     return n.value
 
+  def bench_attention(self, n_seqs: int, max_ctx: int, n_splits: int, iters: int) -> int:
+    """Enqueue the decode attention of the first local layer `iters` times (xb_bench_attention)."""
+    used = C.c_int()
+    stream = torch.cuda.current_stream(self.device).cuda_stream
+    _cabi.check(self.lib.xb_bench_attention(self._h, int(n_seqs), int(max_ctx), int(n_splits), int(iters), C.byref(used),
+                                            C.c_void_p(stream)))
+    return used.value
+
   def release_slot(self, slot: int):
     _cabi.check(self.lib.xb_kv_release_slot(self._h, slot))
 
