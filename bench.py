@@ -411,8 +411,9 @@ def e2e_engine_api(runner, cfg, prompt, K, W):
   dt = asyncio.run(go())
   V = cfg["vocab_size"]
   eng.end_request("bench")
-  return {"value": B * K / dt, "unit": "tok/s", "h2d_bytes_per_step": B * 4 + B * V * 4, "d2h_bytes_per_step": B * V * 4 + B * 4,
-          "api": "B200ShardInferenceEngine.infer_tensor(np ids) -> np fp32 logits [B,V]; .sample(np logits) -> np ids (reference plugin API, host buffers)"}
+  return {"value": B * K / dt, "unit": "tok/s", "h2d_bytes_per_step": B * 4, "d2h_bytes_per_step": B * V * 4 + B * 4,
+          "api": "B200ShardInferenceEngine.infer_tensor(np ids) -> np fp32 logits [B,V] (pinned staging); .sample(that array) -> np ids "
+                 "(reference plugin API, host buffers; the logits array handed back to sample() is recognised and not re-uploaded)"}
 
 
 def main():
