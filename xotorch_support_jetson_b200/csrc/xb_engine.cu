@@ -123,7 +123,7 @@ static int alloc_tiled(bf16** p, size_t rows, size_t K) {
   return 0;
 }
 // copy `rows` x K row-major bf16 (host or device memory) into rows [row0, row0+rows) of a tiled matrix
-static int store_tiled(bf16* dst, const void* src, size_t row0, size_t rows, size_t K) {
+static int store_tiled(bf16* dst, const void* src, size_t row0, size_t rows, size_t K, int interleave = 0, int interleave_off = 0) {
   XB_CHECK(K % 8 == 0, "K=%zu must be a multiple of 8", K);
   cudaPointerAttributes pa;
   const bool on_device = cudaPointerGetAttributes(&pa, src) == cudaSuccess && pa.type == cudaMemoryTypeDevice;
@@ -137,7 +137,7 @@ static int store_tiled(bf16* dst, const void* src, size_t row0, size_t rows, siz
   }
   const long long n = (long long)rows * (K / 8);
   xb_tile_weight_kernel<<<(unsigned)((n + 255) / 256), 256>>>(dsrc, dst, (long long)row0, (long long)rows, (int)K,
-                                                              (int)((K + 63) / 64));
+                                                              (int)((K + 63) / 64), interleave, interleave_off);
   XB_CUDA(cudaGetLastError());
   XB_CUDA(cudaDeviceSynchronize());
   if (staging) cudaFree(staging);
@@ -164,7 +164,7 @@ extern "C" int xb_engine_create(const xb_model_desc* desc, int device, xb_engine
   XB_CHECK(d.head_dim == 64 || d.head_dim == 128, "head_dim %d not supported (64 or 128)", d.head_dim);
   XB_CHECK(d.n_heads % d.n_kv_heads == 0 && d.n_heads / d.n_kv_heads <= 8, "n_heads %d must be 1..8 x n_kv_heads %d",
            d.n_heads, d.n_kv_heads);
-  XB_CHECK(d.dim % 8 == 0 && d.inter_dim % 8 == 0, "dim/inter_dim must be multiples of 8");
+  XB_CHECK(d.dim % 8 == 0 && d.inter_dim % 16 == 0, "dim must be a multiple of 8 and inter_dim of 16");
   XB_CHECK(d.max_batch_tokens > 0 && d.max_seqs > 0 && d.max_positions > 0, "max_batch_tokens/max_seqs/max_positions must be > 0");
   xb_engine* e = new xb_engine();
   e->d = d;
@@ -277,6 +277,7 @@ extern "C" int xb_load_weight(xb_engine* e, int layer, int kind, const void* src
   void* dst = nullptr;          // plain copy target (vectors, embedding, RoPE table)
   bf16* tdst = nullptr;         // tiled matrix target
   size_t want = 0, row0 = 0, rows = 0, K = 0;
+  int il = 0, il_off = 0;       // gate/up rows are interleaved in 16-feature blocks
   if (layer >= 0) {
     XB_CHECK(layer >= d.start_layer && layer <= d.end_layer, "layer %d outside this shard [%d,%d]", layer, d.start_layer,
              d.end_layer);
@@ -286,8 +287,8 @@ extern "C" int xb_load_weight(xb_engine* e, int layer, int kind, const void* src
       case XB_W_K: tdst = w.wqkv; row0 = e->NQ; rows = e->NKV; K = D; break;
       case XB_W_V: tdst = w.wqkv; row0 = e->NQ + e->NKV; rows = e->NKV; K = D; break;
       case XB_W_O: tdst = w.wo; rows = D; K = e->NQ; break;
-      case XB_W_GATE: tdst = w.wgu; row0 = 0; rows = I; K = D; break;
-      case XB_W_UP: tdst = w.wgu; row0 = I; rows = I; K = D; break;
+      case XB_W_GATE: tdst = w.wgu; rows = I; K = D; il = 1; il_off = 0; break;
+      case XB_W_UP: tdst = w.wgu; rows = I; K = D; il = 1; il_off = 16; break;
       case XB_W_DOWN: tdst = w.wdown; rows = D; K = I; break;
       case XB_W_SA_NORM: dst = w.sa_norm; want = D * 2; break;
       case XB_W_MLP_NORM: dst = w.mlp_norm; want = D * 2; break;
@@ -318,7 +319,7 @@ extern "C" int xb_load_weight(xb_engine* e, int layer, int kind, const void* src
   if (tdst != nullptr) {
     want = rows * K * 2;
     XB_CHECK(nbytes == want, "weight kind %d layer %d: got %zu bytes, expected %zu", kind, layer, nbytes, want);
-    return store_tiled(tdst, src, row0, rows, K);
+    return store_tiled(tdst, src, row0, rows, K, il, il_off);
   }
   XB_CHECK(nbytes == want, "weight kind %d layer %d: got %zu bytes, expected %zu", kind, layer, nbytes, want);
   XB_CUDA(cudaMemcpy(dst, src, nbytes, cudaMemcpyDefault));
@@ -339,10 +340,11 @@ extern "C" int xb_kv_reserve(xb_engine* e, int n_slots, int max_tokens_per_slot,
   }
   cudaFree(e->d_page_table);
   e->d_page_table = nullptr;
-  // captured decode graphs hold the old pool / page-table addresses
+  // captured decode graphs and launch plans hold the old pool / page-table addresses
   for (auto& kv : e->graphs)
     if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
   e->graphs.clear();
+  e->plans.clear();
   e->n_slots = n_slots;
   e->page_tokens = page_tokens;
   e->max_pages = (max_tokens_per_slot + page_tokens - 1) / page_tokens;
@@ -395,7 +397,31 @@ static int get_plan(xb_engine* e, int site, int layer, const bf16* x, long long 
   if (it == e->plans.end()) {
     GemmPlan p;
     XB_TRY(xb_gemm_plan(&p, x, ldx, w, 1, T, N, K, out, ld_out, bias, round_bf16, e->num_sms, 0));
-    if (out == e->gemm_out) {
+    if (p.args.mode == XB_GEMM_WIDE && site == SITE_QKV) {
+      // prefill: bias + RoPE + q store + paged-KV append happen in the GEMM epilogue
+      const xb_model_desc& d = e->d;
+      GemmArgs& g = p.args;
+      g.epi = XB_EPI_QKV;
+      g.rope = e->rope;
+      g.q_out = e->q;
+      g.k_pool = e->L[layer].k_pool;
+      g.v_pool = e->L[layer].v_pool;
+      g.tok_seq = e->d_tok_seq;
+      g.tok_pos = e->d_tok_pos;
+      g.seq_slot = e->d_seq_slot;
+      g.page_table = e->d_page_table;
+      g.max_pages = e->max_pages;
+      g.page_tokens = e->page_tokens;
+      g.n_heads = d.n_heads;
+      g.n_kv_heads = d.n_kv_heads;
+      g.head_dim = d.head_dim;
+      g.rope_kind = d.rope_kind;
+    } else if (p.args.mode == XB_GEMM_WIDE && site == SITE_GU) {
+      // prefill: SiLU(gate) * up in the GEMM epilogue, straight into the down projection's input
+      p.args.epi = XB_EPI_SILU;
+      p.args.out = e->act;
+      p.args.ld_out = e->d.inter_dim;
+    } else if (out == e->gemm_out) {
       const size_t need = p.args.mode == XB_GEMM_SKINNY ? (size_t)p.split.splits * T * N * 4 : (size_t)T * N * 2;
       XB_CHECK(need <= e->gemm_out_bytes, "gemm workspace too small: need %zu have %zu", need, e->gemm_out_bytes);
     }
@@ -534,18 +560,11 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
     XB_TRY(get_plan(e, SITE_QKV, l, e->hn, D, w.wqkv, T, e->NQKV, D, e->gemm_out, e->NQKV, w.bqkv, 0, &gp));
     XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
     LAUNCH_COUNT(e);
-    {
+    if (gp->args.mode == XB_GEMM_SKINNY) {
       dim3 grid(T, d.n_heads + 2 * d.n_kv_heads);
-      if (gp->args.mode == XB_GEMM_SKINNY)
-        XB_TRY(launch_k(e, xb_qkv_finalize_kernel<0>, dim3(grid), dim3(hd / 2), 0, st, 1, (const float*)e->gemm_out, gp->split, (long long)T * e->NQKV,
-                                                            nullptr, w.bqkv, e->rope, e->q, w.k_pool, w.v_pool, m, d.n_heads,
-                                                            d.n_kv_heads, hd, d.rope_kind));
-      else {
-        const long long items = (long long)T * (d.n_heads + 2 * d.n_kv_heads) * (d.rope_kind == 0 ? hd / 8 : hd / 16);
-        XB_TRY(launch_k(e, xb_qkv_finalize_wide_kernel, dim3((unsigned)((items + 255) / 256)), dim3(256), 0, st, 1,
-                        (const bf16*)e->gemm_out, e->rope, e->q, w.k_pool, w.v_pool, m, T, d.n_heads, d.n_kv_heads, hd,
-                        d.rope_kind));
-      }
+      XB_TRY(launch_k(e, xb_qkv_finalize_kernel<0>, grid, dim3(hd / 2), 0, st, 1, (const float*)e->gemm_out, gp->split,
+                      (long long)T * e->NQKV, nullptr, w.bqkv, e->rope, e->q, w.k_pool, w.v_pool, m, d.n_heads, d.n_kv_heads, hd,
+                      d.rope_kind));
     }
     if (hd == 128) XB_TRY(launch_attn<128>(e, w, m, T, n_splits, n_tiles, st));
     else XB_TRY(launch_attn<64>(e, w, m, T, n_splits, n_tiles, st));
@@ -558,15 +577,10 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
     XB_TRY(get_plan(e, SITE_GU, l, e->hn, D, w.wgu, T, 2 * I, D, e->gemm_out, 2 * I, nullptr, 0, &gp));
     XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
     LAUNCH_COUNT(e);
-    {
+    if (gp->args.mode == XB_GEMM_SKINNY) {
       const long long n = (long long)T * I;
-      const int blocks = (int)((n + 255) / 256);
-      if (gp->args.mode == XB_GEMM_SKINNY)
-        XB_TRY(launch_k(e, xb_silu_mul_kernel<0>, dim3(blocks), dim3(256), 0, st, 1, (const float*)e->gemm_out, gp->split, (long long)T * 2 * I, nullptr,
-                                                       e->act, T, I));
-      else
-        XB_TRY(launch_k(e, xb_silu_mul_wide_kernel, dim3((unsigned)(((long long)T * (I / 8) + 255) / 256)), dim3(256), 0, st, 1,
-                        (const bf16*)e->gemm_out, e->act, T, I));
+      XB_TRY(launch_k(e, xb_silu_mul_kernel<0>, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, st, 1, (const float*)e->gemm_out,
+                      gp->split, (long long)T * 2 * I, nullptr, e->act, T, I));
     }
     XB_TRY(get_plan(e, SITE_DOWN, l, e->act, I, w.wdown, T, D, I, e->gemm_out, D, nullptr, 0, &gp));
     XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));

@@ -42,7 +42,15 @@ struct GemmArgs {
   void* out;
   long long ld_out;        // SKINNY: N (floats per token row); WIDE: elements per token row
   const bf16* bias;        // WIDE: per-feature bias or nullptr
+  // WIDE fused epilogues
+  int epi;                 // XB_EPI_*
+  // XB_EPI_QKV: bias + bf16 round + RoPE at the row's position + q store / paged-KV append
+  const float* rope;       // [pos][hd/2][cos,sin]
+  bf16 *q_out, *k_pool, *v_pool;
+  const int *tok_seq, *tok_pos, *seq_slot, *page_table;
+  int max_pages, page_tokens, n_heads, n_kv_heads, head_dim, rope_kind;
 };
+enum { XB_EPI_PLAIN = 0, XB_EPI_QKV = 1, XB_EPI_SILU = 2 };
 
 // TMA coordinates (innermost, row) of the [128 x 64] weight box holding rows 128*wt.. of k-block kb
 __device__ __forceinline__ void gemm_w_coord(const GemmArgs& g, int wt, int kb, int& c0, int& c1) {
@@ -98,6 +106,124 @@ struct GemmCfg {
   static constexpr int TM_COLS = TM_COLS_RAW <= 32 ? 32 : TM_COLS_RAW <= 64 ? 64 : TM_COLS_RAW <= 128 ? 128 : TM_COLS_RAW <= 256 ? 256 : 512;
   static constexpr int SMEM_BYTES = STAGES * (A_BYTES + B_BYTES) + 1024 /*align slack*/ + 256 /*barriers*/;
 };
+
+
+// ---- WIDE epilogues: one thread = one token row `t`, TMEM chunks of 16 consecutive columns ----
+__device__ __forceinline__ void epi_store16(bf16* dst, const float* x) {
+  uint4 p0, p1;
+  p0.x = f2_to_bf2(x[0], x[1]);   p0.y = f2_to_bf2(x[2], x[3]);
+  p0.z = f2_to_bf2(x[4], x[5]);   p0.w = f2_to_bf2(x[6], x[7]);
+  p1.x = f2_to_bf2(x[8], x[9]);   p1.y = f2_to_bf2(x[10], x[11]);
+  p1.z = f2_to_bf2(x[12], x[13]); p1.w = f2_to_bf2(x[14], x[15]);
+  reinterpret_cast<uint4*>(dst)[0] = p0;
+  reinterpret_cast<uint4*>(dst)[1] = p1;
+}
+// nn.Linear rounding point: bf16(acc + bias)
+__device__ __forceinline__ void epi_linear16(const GemmArgs& g, const uint32_t* v, int n0, float* x) {
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    float a = __uint_as_float(v[j]);
+    if (g.bias != nullptr) a += bf2f(g.bias[n0 + j]);
+    x[j] = rbf(a);
+  }
+}
+// where 16 elements [e, e+16) of fused-QKV head `head` of token row t go: q buffer or the paged cache
+__device__ __forceinline__ bf16* epi_qkv_dst(const GemmArgs& g, int t, int pos, int head, int e) {
+  const int H = g.n_heads, KV = g.n_kv_heads, hd = g.head_dim;
+  if (head < H) return g.q_out + ((long long)t * H + head) * hd + e;
+  const int slot = g.seq_slot[g.tok_seq[t]];
+  const int page = g.page_table[(long long)slot * g.max_pages + pos / g.page_tokens];
+  const int off = pos % g.page_tokens;
+  const int kvh = (head - H) % KV;
+  bf16* pool = head < H + KV ? g.k_pool : g.v_pool;
+  return pool + (((long long)page * KV + kvh) * g.page_tokens + off) * hd + e;
+}
+
+template <int BN>
+__device__ __forceinline__ void epi_wide_qkv(const GemmArgs& g, uint32_t t_addr, int t, int tb) {
+  const int hd = g.head_dim, half = hd >> 1, H = g.n_heads, KV = g.n_kv_heads;
+  const bool row_ok = t < g.a_rows;
+  const int pos = row_ok ? g.tok_pos[t] : 0;
+  const float* rope_row = g.rope + (long long)pos * half * 2;
+  if (g.rope_kind == 0) {
+    // interleaved pairs (2i, 2i+1): both members sit in one 16-column chunk
+#pragma unroll 1
+    for (int c = 0; c < BN; c += 16) {
+      uint32_t v[16];
+      tmem_ld16(t_addr + c, v);
+      tmem_ld_wait();
+      const int n0 = tb * BN + c;
+      if (!row_ok || n0 >= g.b_rows) continue;
+      const int head = n0 / hd, e = n0 % hd;
+      float x[16];
+      epi_linear16(g, v, n0, x);
+      if (head < H + KV) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float2 cs = *reinterpret_cast<const float2*>(rope_row + (e / 2 + j) * 2);
+          const float a = x[2 * j], b = x[2 * j + 1];
+          x[2 * j] = __fsub_rn(__fmul_rn(a, cs.x), __fmul_rn(b, cs.y));
+          x[2 * j + 1] = __fadd_rn(__fmul_rn(b, cs.x), __fmul_rn(a, cs.y));
+        }
+      }
+      epi_store16(epi_qkv_dst(g, t, pos, head, e), x);
+    }
+  } else {
+    // half-split pairs (i, i + hd/2): take the two chunks of a head together
+#pragma unroll 1
+    for (int hb = 0; hb < BN; hb += hd) {
+#pragma unroll 1
+      for (int c = 0; c < half; c += 16) {
+        uint32_t vl[16], vh[16];
+        tmem_ld16(t_addr + hb + c, vl);
+        tmem_ld16(t_addr + hb + half + c, vh);
+        tmem_ld_wait();
+        const int n0 = tb * BN + hb + c;
+        if (!row_ok || n0 >= g.b_rows) continue;
+        const int head = n0 / hd;
+        float lo[16], hi[16];
+        epi_linear16(g, vl, n0, lo);
+        epi_linear16(g, vh, n0 + half, hi);
+        if (head < H + KV) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const float2 cs = *reinterpret_cast<const float2*>(rope_row + (c + j) * 2);
+            const float cc = rbf(cs.x), ss = rbf(cs.y);
+            const float a = lo[j], b = hi[j];
+            lo[j] = __fadd_rn(rbf(__fmul_rn(a, cc)), rbf(__fmul_rn(-b, ss)));
+            hi[j] = __fadd_rn(rbf(__fmul_rn(b, cc)), rbf(__fmul_rn(a, ss)));
+          }
+        }
+        bf16* dst = epi_qkv_dst(g, t, pos, head, c);
+        epi_store16(dst, lo);
+        epi_store16(dst + half, hi);
+      }
+    }
+  }
+}
+
+// gate/up rows are interleaved in blocks of 16 features: columns [32b, 32b+16) = gate of features
+// [16b, 16b+16), columns [32b+16, 32b+32) = up of the same features.  act = bf16(bf16(silu(g)) * u).
+template <int BN>
+__device__ __forceinline__ void epi_wide_silu(const GemmArgs& g, uint32_t t_addr, int t, int tb) {
+  bf16* out = reinterpret_cast<bf16*>(g.out);
+#pragma unroll 1
+  for (int c = 0; c < BN; c += 32) {
+    uint32_t vg[16], vu[16];
+    tmem_ld16(t_addr + c, vg);
+    tmem_ld16(t_addr + c + 16, vu);
+    tmem_ld_wait();
+    const int n0 = tb * BN + c;
+    if (t >= g.a_rows || n0 >= g.b_rows) continue;
+    float x[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const float gg = rbf(__uint_as_float(vg[j])), uu = rbf(__uint_as_float(vu[j]));
+      x[j] = rbf(gg / (1.0f + expf(-gg))) * uu;
+    }
+    epi_store16(out + (long long)t * g.ld_out + (n0 >> 1), x);
+  }
+}
 
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(192, 1)
@@ -254,6 +380,11 @@ xb_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       tc_fence_after();
       const uint32_t t_addr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN);
       const int arow = ta * 128 + row_in_tile;
+      if (BN == 256 && g.mode == XB_GEMM_WIDE && g.epi == XB_EPI_QKV) {
+        epi_wide_qkv<BN>(g, t_addr, arow, tb);
+      } else if (BN == 256 && g.mode == XB_GEMM_WIDE && g.epi == XB_EPI_SILU) {
+        epi_wide_silu<BN>(g, t_addr, arow, tb);
+      } else
 #pragma unroll 1
       for (int c = 0; c < BN; c += 16) {
         uint32_t v[16];
@@ -349,12 +480,14 @@ __global__ void xb_linear_check_kernel(const bf16* __restrict__ x, const bf16* _
 
 // row-major rows [row0, row0+rows) x K of a weight matrix -> tile-major storage
 // dst[((r/128)*KB + k/64)*8192 + (r%128)*64 + k%64]; 16 bytes per thread
+// interleave > 0: source row j lands at fused row (j/16)*32 + interleave_off + j%16 (gate/up blocks)
 __global__ void xb_tile_weight_kernel(const bf16* __restrict__ src, bf16* __restrict__ dst, long long row0, long long rows,
-                                      int K, int KB) {
+                                      int K, int KB, int interleave, int interleave_off) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int k8 = K / 8;
   if (i >= rows * k8) return;
-  const long long r = row0 + i / k8;
+  const long long j = i / k8;
+  const long long r = interleave ? (j / 16) * 32 + interleave_off + (j % 16) : row0 + j;
   const int k = (int)(i % k8) * 8;
   const uint4 v = *reinterpret_cast<const uint4*>(src + (i / k8) * K + k);
   *reinterpret_cast<uint4*>(dst + ((r >> 7) * KB + (k >> 6)) * 8192 + (r & 127) * 64 + (k & 63)) = v;
@@ -442,6 +575,7 @@ static int xb_gemm_plan(GemmPlan* p, const bf16* x, long long ldx, const bf16* w
   g.bias = bias;
   g.round_bf16 = round_bf16;
   g.w_tiled = w_tiled;
+  g.epi = XB_EPI_PLAIN;
   const long long w_tiles = (N + 127) / 128;
   if (T <= 128) {
     const int bn = xb_pick_bn_skinny(T);

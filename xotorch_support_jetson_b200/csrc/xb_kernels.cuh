@@ -204,8 +204,8 @@ __global__ void __launch_bounds__(NT) xb_resid_norm_cluster_kernel(const float* 
 
 // ----------------------------------------------------------------------------- QKV finalize
 // One block per (token, head) over the fused [q | k | v] projection output.
-//   value = bf16(sum_splits(partial) + bias)        (nn.Linear rounding; SRC = 0)
-//         = already-rounded bf16                    (SRC = 1, bias added in the GEMM epilogue)
+//   value = bf16(sum_splits(partial) + bias)        (nn.Linear rounding)
+//   (decode path; the prefill GEMM does the same work in its epilogue, xb_gemm.cuh epi_wide_qkv)
 //   q,k heads: RoPE at the token's position, table = [pos][hd/2][cos,sin] fp32
 //     rope_kind 0: interleaved pairs (2i,2i+1), fp32 math, one rounding (Llama3ScaledRoPE /
 //                  RotaryPositionalEmbeddings as built at general_mha.py:35-40,58-63)
@@ -287,11 +287,13 @@ __global__ void xb_silu_mul_kernel(const float* __restrict__ part, SplitInfo si,
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (long long)T * I) return;
   const int t = (int)(idx / I), i = (int)(idx % I);
-  const long long og = (long long)t * 2 * I + i, ou = og + I;
+  // fused gate/up columns are interleaved in 16-feature blocks (see epi_wide_silu)
+  const int cg = (i >> 4) * 32 + (i & 15), cu = cg + 16;
+  const long long og = (long long)t * 2 * I + cg, ou = (long long)t * 2 * I + cu;
   float g, u;
   if (SRC == 0) {
     g = 0.f; u = 0.f;
-    const int sg_n = xb_n_segments(si, i), su_n = xb_n_segments(si, I + i);
+    const int sg_n = xb_n_segments(si, cg), su_n = xb_n_segments(si, cu);
     for (int s = 0; s < sg_n; ++s) g += part[s * split_stride + og];
     for (int s = 0; s < su_n; ++s) u += part[s * split_stride + ou];
     g = rbf(g);
@@ -302,99 +304,6 @@ __global__ void xb_silu_mul_kernel(const float* __restrict__ part, SplitInfo si,
   }
   const float sg = rbf(g / (1.0f + expf(-g)));
   act[idx] = f2bf(sg * u);
-}
-
-// ----------------------------------------------------------------------------- prefill (bf16 source) variants
-// Same arithmetic as xb_silu_mul_kernel<1> / xb_qkv_finalize_kernel<1>, 8 elements (128 bits) per
-// thread: the prefill tensors are hundreds of MB and these passes are pure HBM streaming.
-__global__ void __launch_bounds__(256) xb_silu_mul_wide_kernel(const bf16* __restrict__ y, bf16* __restrict__ act, int T, int I) {
-  pdl_launch_dependents();
-  pdl_wait();
-  const int i8 = I >> 3;
-  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= (long long)T * i8) return;
-  const int t = (int)(idx / i8), c = (int)(idx % i8) * 8;
-  const uint4 gu = *reinterpret_cast<const uint4*>(y + (long long)t * 2 * I + c);
-  const uint4 uu = *reinterpret_cast<const uint4*>(y + (long long)t * 2 * I + I + c);
-  const uint32_t gw[4] = {gu.x, gu.y, gu.z, gu.w}, uw[4] = {uu.x, uu.y, uu.z, uu.w};
-  uint32_t o[4];
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    const float2 g = bf2_to_f2(gw[j]), u = bf2_to_f2(uw[j]);
-    const float s0 = rbf(g.x / (1.0f + expf(-g.x))), s1 = rbf(g.y / (1.0f + expf(-g.y)));
-    o[j] = f2_to_bf2(s0 * u.x, s1 * u.y);
-  }
-  *reinterpret_cast<uint4*>(act + (long long)t * I + c) = make_uint4(o[0], o[1], o[2], o[3]);
-}
-
-// one thread per (token, head, 8-element chunk): chunk c covers elements [8c, 8c+8) of the head;
-// interleaved RoPE pairs sit inside the chunk, half-split pairs are chunk c and chunk c + hd/16.
-__global__ void __launch_bounds__(256) xb_qkv_finalize_wide_kernel(const bf16* __restrict__ y, const float* __restrict__ rope,
-                                                                   bf16* __restrict__ q_out, bf16* __restrict__ k_pool,
-                                                                   bf16* __restrict__ v_pool, BatchMeta m, int T, int H, int KV,
-                                                                   int hd, int rope_kind) {
-  pdl_launch_dependents();
-  pdl_wait();
-  const int heads = H + 2 * KV;
-  const int cph = rope_kind == 0 ? hd / 8 : hd / 16;     // work items per head
-  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= (long long)T * heads * cph) return;
-  const int c = (int)(idx % cph);
-  const int head = (int)((idx / cph) % heads);
-  const int t = (int)(idx / ((long long)cph * heads));
-  const int half = hd >> 1;
-  const long long base = (long long)t * heads * hd + (long long)head * hd;
-  const int pos = m.tok_pos[t];
-  const int nch = rope_kind == 0 ? 1 : 2;
-  uint32_t w[2][4];
-  {
-    const uint4 a = *reinterpret_cast<const uint4*>(y + base + c * 8);
-    w[0][0] = a.x; w[0][1] = a.y; w[0][2] = a.z; w[0][3] = a.w;
-    if (nch == 2) {
-      const uint4 b = *reinterpret_cast<const uint4*>(y + base + half + c * 8);
-      w[1][0] = b.x; w[1][1] = b.y; w[1][2] = b.z; w[1][3] = b.w;
-    }
-  }
-  if (head < H + KV) {
-    if (rope_kind == 0) {
-      // pairs (2i, 2i+1), i = 4c .. 4c+3
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float2 cs = *reinterpret_cast<const float2*>(rope + ((long long)pos * half + c * 4 + j) * 2);
-        const float2 x = bf2_to_f2(w[0][j]);
-        const float o0 = __fsub_rn(__fmul_rn(x.x, cs.x), __fmul_rn(x.y, cs.y));
-        const float o1 = __fadd_rn(__fmul_rn(x.y, cs.x), __fmul_rn(x.x, cs.y));
-        w[0][j] = f2_to_bf2(o0, o1);
-      }
-    } else {
-      // pairs (i, i + hd/2), i = 8c .. 8c+7
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float2 lo = bf2_to_f2(w[0][j]), hi = bf2_to_f2(w[1][j]);
-        const float4 cs = *reinterpret_cast<const float4*>(rope + ((long long)pos * half + c * 8 + j * 2) * 2);
-        const float c0 = rbf(cs.x), s0 = rbf(cs.y), c1 = rbf(cs.z), s1 = rbf(cs.w);
-        const float a0 = rbf(__fadd_rn(rbf(__fmul_rn(lo.x, c0)), rbf(__fmul_rn(-hi.x, s0))));
-        const float b0 = rbf(__fadd_rn(rbf(__fmul_rn(hi.x, c0)), rbf(__fmul_rn(lo.x, s0))));
-        const float a1 = rbf(__fadd_rn(rbf(__fmul_rn(lo.y, c1)), rbf(__fmul_rn(-hi.y, s1))));
-        const float b1 = rbf(__fadd_rn(rbf(__fmul_rn(hi.y, c1)), rbf(__fmul_rn(lo.y, s1))));
-        w[0][j] = f2_to_bf2(a0, a1);
-        w[1][j] = f2_to_bf2(b0, b1);
-      }
-    }
-  }
-  bf16* dst;
-  if (head < H) {
-    dst = q_out + (long long)t * H * hd + (long long)head * hd;
-  } else {
-    const int slot = m.seq_slot[m.tok_seq[t]];
-    const int page = m.page_table[(long long)slot * m.max_pages + pos / m.page_tokens];
-    const int off = pos % m.page_tokens;
-    const int kvh = (head - H) % KV;
-    bf16* pool = (head < H + KV) ? k_pool : v_pool;
-    dst = pool + (((long long)page * KV + kvh) * m.page_tokens + off) * hd;
-  }
-  *reinterpret_cast<uint4*>(dst + c * 8) = make_uint4(w[0][0], w[0][1], w[0][2], w[0][3]);
-  if (nch == 2) *reinterpret_cast<uint4*>(dst + half + c * 8) = make_uint4(w[1][0], w[1][1], w[1][2], w[1][3]);
 }
 
 // ----------------------------------------------------------------------------- misc
