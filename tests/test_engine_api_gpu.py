@@ -71,7 +71,9 @@ def test_plugin_api_full_shard_and_two_shard_ring(built_lib, tmp_path):
   for a, b, r in zip(logits_full, logits_ring, ref_logits):
     assert np.array_equal(a, b)                     # sharded == unsharded, exactly (the reference's assertion)
     assert np.abs(a - r).max() / np.abs(r).max() < REL_TOL
-  assert first_tok == int(ref_toks[0, 0])
+  # greedy token: identical unless the oracle's own top-2 logits are within the numerical noise
+  r0 = ref_logits[0][0]
+  assert r0[first_tok] >= r0.max() - REL_TOL * np.abs(r0).max()
 
 
 def test_sample_reference_semantics_and_noise_stream(built_lib, tmp_path):

@@ -216,3 +216,36 @@ def test_cuda_path_against_committed_golden(built_lib, mid):
     if margin[i] > 2 * noise:
       assert got_tokens[i] == int(g["tokens"][0, i]), (i, got_tokens, g["tokens"][0].tolist())
   st.close()
+
+
+@pytest.mark.parametrize("mid,L", [("llama-3.1-tiny", 333), ("llama-3.2-tiny", 200), ("qwen-2.5-tiny", 150)])
+def test_long_prompt_prefill_multi_tile_attention(built_lib, mid, L):
+  """Prompts spanning several 64-key attention tiles and several query tiles (causal masking
+  across tiles, online-softmax rescaling, KV ring reuse), plus a chunked continuation."""
+  from xotorch_support_jetson_b200.shard import Shard
+  from xotorch_support_jetson_b200.stage import StageRuntime
+  O, cfg, state = _setup(mid)
+  nl, D = cfg["num_layers"], cfg["embed_dim"]
+  g = torch.Generator().manual_seed(99)
+  prompt = torch.randint(1, cfg["vocab_size"], (1, L), generator=g)
+  ref = O.OracleShardModel(cfg, mid, 0, nl - 1, state, O.OracleOptions(max_generated_tokens=8))
+  ref_toks, ref_logits, ref_taps = O.greedy_generate([ref], prompt, 2, collect_logits=True, taps_at=(0,))
+  st = StageRuntime(Shard(mid, 0, nl - 1, nl), cfg, device=0, max_batch_tokens=512, max_seqs=2, max_tokens_per_seq=512, page_tokens=64)
+  st.load_state(state)
+  toks = prompt.to(torch.int32).cuda().reshape(-1)
+  taps = [torch.empty((L, D), dtype=torch.bfloat16, device="cuda") for _ in range(nl)]
+  lg = st.forward([0], [L], [0], tokens=toks, taps=taps)
+  # same prompt in two chunks (second chunk attends to the cached first one)
+  cut = 64 + 37
+  st.forward([1], [cut], [0], tokens=toks[:cut])
+  lg2 = st.forward([1], [L - cut], [cut], tokens=toks[cut:])
+  nxt = torch.tensor([int(ref_toks[0, 0])], dtype=torch.int32, device="cuda")
+  lg3 = st.forward([0], [1], [L], tokens=nxt)
+  torch.cuda.synchronize()
+  worst_h = max(_rel(taps[l].float().cpu().numpy(), ref_taps[0][l].reshape(L, D)) for l in range(nl))
+  e1 = _rel(lg.cpu().numpy(), ref_logits[0])
+  e2 = _rel(lg2.cpu().numpy(), ref_logits[0])
+  e3 = _rel(lg3.cpu().numpy(), ref_logits[1])
+  print(f"{mid} L={L}: hidden {worst_h:.4f} logits {e1:.4f} chunked {e2:.4f} decode {e3:.4f}")
+  assert worst_h < REL_TOL and e1 < REL_TOL and e2 < REL_TOL and e3 < REL_TOL
+  st.close()

@@ -9,8 +9,9 @@
 //   * decode kernel: the G heads of one token form one 16-row tile (zero padded); the 4
 //     compute warps split the KEYS of each tile; blocks split the context (split-KV) and a
 //     combine kernel merges the partial (max, sum, acc).
-//   * prefill kernel: 128 rows = (128/G) consecutive tokens x G heads; the 8 compute warps
-//     split the ROWS; causal masking by each row's absolute position.
+//   * prefill kernel (tcgen05, further down): 128 rows = (128/G) consecutive tokens x G heads of
+//     ONE sequence (tile table built on the host: tile_start[i] = first token row, tile_len[i] =
+//     #tokens); S and O live in TMEM; causal masking by each row's absolute position.
 #pragma once
 #include "xb_common.cuh"
 #include "xb_kernels.cuh"
@@ -331,27 +332,76 @@ __global__ void __launch_bounds__(128) xb_attn_combine2_kernel(const float* __re
     *reinterpret_cast<uint32_t*>(dst + j) = f2_to_bf2(acc[j] * invL, acc[j + 1] * invL);
 }
 
-// ----------------------------------------------------------------------------- prefill
-// Work item = (query tile, kv head).  A query tile is up to 128/G consecutive tokens of ONE
-// sequence (tile table built on the host): tile_start[i] = first token row, tile_len[i] = #tokens.
-template <int HD, int NST>
-struct AttPreCfg {
-  static constexpr int TILE_BYTES = XB_ATT_TILE * HD * 2;
-  static constexpr int STAGE_BYTES = 2 * TILE_BYTES;
-  static constexpr int SMEM_BYTES = NST * STAGE_BYTES + 1024 + 128;
+// ============================================================================= tcgen05 prefill attention
+// Work item = (query tile, kv head): 128 rows = tokens x group heads of one kv head.  Both GEMMs
+// run on the 5th-gen tensor cores:
+//   S[128 x 64]  = Q[128 x hd] K_tile[64 x hd]^T        tcgen05.mma, A/B K-major from smem -> TMEM
+//   O[128 x hd] += P[128 x 64] V_tile[64 x hd]          A = P (bf16, written to swizzled smem by the
+//                                                       softmax threads), B = V as an MN-major operand
+// One TMEM lane = one query row, so the softmax is thread-private (no shuffles): pass 1 row max,
+// pass 2 p = exp2(s - m) -> bf16 -> smem.  O is only rescaled (TMEM ld/st) when some row's max moved
+// by more than 2^8 (lazy rescale).  Two blocks per SM: one block's softmax overlaps the other's MMAs.
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* v) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+      ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]),
+        "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// MN-major, 128B-swizzled operand: 64-element (128 B) atoms along MN every `lbo` bytes, 8-row groups
+// along K every 1024 B
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t smem_addr, uint32_t lbo_bytes) {
+  return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16) | (64ull << 32) |
+         (1ull << 46) | (2ull << 61);
+}
+
+#define XB_ATT_PG_CACHE 128   // page ids prefetched per block (8k keys at 64-token pages; beyond: on demand)
+
+template <int HD>
+struct AttTcCfg {
+  static constexpr int Q_BYTES = 128 * HD * 2;
+  static constexpr int TILE_BYTES = XB_ATT_TILE * HD * 2;   // one K or V tile
+  static constexpr int P_BYTES = 128 * XB_ATT_TILE * 2;
+  static constexpr int NST = 2;                             // K and V ring depth
+  // TWO blocks per SM (measured: 240 us vs 328 us for one block with double-buffered P and 4-deep
+  // rings at 4 x 2048 tokens -- the four softmax warps of a block are latency bound, a second
+  // block doubles the warps per scheduler).  No alignment slack: 2 x (112.75 KB + 1 KB reserved)
+  // must fit 228 KB; the kernel traps if the dynamic shared memory base is not 1024-byte aligned.
+  static constexpr int SMEM_BYTES = Q_BYTES + NST * 2 * TILE_BYTES + P_BYTES + 256 + XB_ATT_PG_CACHE * 4;
+  static constexpr int TM_COLS = 256;                       // S: 64 columns, O: HD columns
 };
 
-template <int HD, int G, int NST>
-__global__ void __launch_bounds__(288) xb_attn_prefill_mma_kernel(
+template <int HD, int G>
+__global__ void __launch_bounds__(192, 2) xb_attn_prefill_tc_kernel(
     const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, const bf16* __restrict__ q,
     BatchMeta m, const int* __restrict__ tile_start, const int* __restrict__ tile_len, bf16* __restrict__ out, int H,
     int KV, float scale_log2) {
-  using Cfg = AttPreCfg<HD, NST>;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* stages = smem;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + NST * Cfg::STAGE_BYTES);
-  uint64_t* empty_bar = full_bar + NST;
+  using Cfg = AttTcCfg<HD>;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if ((smem_u32(smem) & 1023u) != 0u) {
+    if (threadIdx.x == 0) printf("xb200: attention smem base not 1024-aligned\n");
+    __trap();
+  }
+  uint8_t* sQ = smem;
+  uint8_t* sKV = sQ + Cfg::Q_BYTES;
+  uint8_t* sP = sKV + Cfg::NST * 2 * Cfg::TILE_BYTES;
+  // K and V have separate rings: a K slot is free as soon as QK^T of its tile retires, a V slot
+  // after PV -- the next K load starts a whole tile earlier than with a shared ring
+  uint64_t* k_full = reinterpret_cast<uint64_t*>(sP + Cfg::P_BYTES);
+  uint64_t* k_empty = k_full + Cfg::NST;
+  uint64_t* v_full = k_empty + Cfg::NST;
+  uint64_t* v_empty = v_full + Cfg::NST;
+  // the per-tile barriers come in pairs indexed by (tile & 1): each completes every other tile, so a
+  // parity wait can never be overrun by the next completion
+  uint64_t* s_full = v_empty + Cfg::NST;      // [2] S buffer written (QK^T retired)
+  uint64_t* p_full = s_full + 2;              // [2] P buffer written by the softmax warps
+  uint64_t* o_done = p_full + 2;              // [2] PV of the tile retired (P buffer free, O updated)
+  uint64_t* q_ready = o_done + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(q_ready + 1);
+  int* s_pages = reinterpret_cast<int*>(tmem_slot + 2);   // [XB_ATT_PG_CACHE] prefetched page ids
 
   const int tile = blockIdx.x, kvh = blockIdx.y;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -359,101 +409,243 @@ __global__ void __launch_bounds__(288) xb_attn_prefill_mma_kernel(
   pdl_wait();
   const int t0 = tile_start[tile];
   const int nt = tile_len[tile];
-  const int pos0 = m.tok_pos[t0];                       // tokens of a tile have consecutive positions
+  const int pos0 = m.tok_pos[t0];
   const int slot = m.seq_slot[m.tok_seq[t0]];
   const int* pt = m.page_table + (long long)slot * m.max_pages;
-  const int last_pos = pos0 + nt - 1;
-  const int n_tiles = last_pos / XB_ATT_TILE + 1;
+  const int n_kt = (pos0 + nt - 1) / XB_ATT_TILE + 1;
 
-  if (threadIdx.x == 0) {
-    for (int i = 0; i < NST; ++i) {
-      mbar_init(&full_bar[i], 1);
-      mbar_init(&empty_bar[i], 8);
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int i = 0; i < Cfg::NST; ++i) {
+        mbar_init(&k_full[i], 1);
+        mbar_init(&k_empty[i], 1);
+        mbar_init(&v_full[i], 1);
+        mbar_init(&v_empty[i], 1);
+      }
+      mbar_init(&s_full[0], 1);
+      mbar_init(&s_full[1], 1);
+      mbar_init(&p_full[0], 4);
+      mbar_init(&p_full[1], 4);
+      mbar_init(&o_done[0], 1);
+      mbar_init(&o_done[1], 1);
+      mbar_init(q_ready, 4);
+      fence_mbar_init();
     }
-    fence_mbar_init();
+    __syncwarp();
+    tmem_alloc(tmem_slot, Cfg::TM_COLS);
   }
+  tc_fence_before();
   __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  // S is double buffered (columns 0..63 and 64..127): QK^T of tile j+1 overlaps the softmax of tile j
+  const uint32_t tm_S = tmem_base, tm_O = tmem_base + 2 * XB_ATT_TILE;
 
-  if (warp == 8) {
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    // page ids of the block's key tiles are fetched up front by the whole warp, so the TMA
+    // issue loop carries no dependent global load
+    const int P = m.page_tokens;
+    const int BR = P < XB_ATT_TILE ? P : XB_ATT_TILE;       // rows per TMA box
+    const int rgs = XB_ATT_TILE / BR;                        // boxes (row groups) per tile
+    const int n_rg = n_kt * rgs;
+    for (int i = lane; i < n_rg && i < XB_ATT_PG_CACHE; i += 32) {
+      const int pi = (i * BR) / P;
+      s_pages[i] = pt[pi < m.max_pages ? pi : m.max_pages - 1];
+    }
+    __syncwarp();
     if (lane == 0) {
       tma_prefetch_desc(&tmK);
       tma_prefetch_desc(&tmV);
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int kt = 0; kt < n_tiles; ++kt) {
-        mbar_wait(&empty_bar[stage], phase ^ 1);
-        uint8_t* sK = stages + stage * Cfg::STAGE_BYTES;
-        att_issue_tile<HD>(&tmK, &tmV, sK, sK + Cfg::TILE_BYTES, &full_bar[stage], pt, m.max_pages, kt, kvh, KV, m.page_tokens);
-        if (++stage == NST) { stage = 0; phase ^= 1; }
+      auto issue = [&](const CUtensorMap* tm, uint8_t* dst, uint64_t* bar, int kt) {
+        mbar_expect_tx(bar, Cfg::TILE_BYTES);
+        for (int rg = 0; rg < rgs; ++rg) {
+          const int i = kt * rgs + rg;
+          const int key = kt * XB_ATT_TILE + rg * BR;
+          int page;
+          if (i < XB_ATT_PG_CACHE) page = s_pages[i];
+          else { const int pi = key / P; page = pt[pi < m.max_pages ? pi : m.max_pages - 1]; }
+          const int row = (page * KV + kvh) * P + (key % P);
+#pragma unroll
+          for (int db = 0; db < HD / 64; ++db) tma_load_2d(dst + db * (XB_ATT_TILE * 128) + rg * BR * 128, tm, bar, db * 64, row);
+        }
+      };
+      for (int kt = 0; kt < n_kt; ++kt) {
+        const int stage = kt % Cfg::NST;
+        const uint32_t ph = (kt / Cfg::NST) & 1;
+        uint8_t* sK = sKV + stage * 2 * Cfg::TILE_BYTES;
+        mbar_wait(&k_empty[stage], ph ^ 1);
+        issue(&tmK, sK, &k_full[stage], kt);
+        mbar_wait(&v_empty[stage], ph ^ 1);
+        issue(&tmV, sK + Cfg::TILE_BYTES, &v_full[stage], kt);
       }
     }
-    return;
-  }
-
-  // ===================== 8 compute warps: 16 query rows each; row = (token, head-in-group) ====
-  constexpr int KS = HD / 16, DT = HD / 8;
-  const int ra = warp * 16 + (lane >> 2), rb = ra + 8;
-  const int ta = ra / G, ga = ra % G, tb = rb / G, gb = rb % G;
-  const bool va = ta < nt, vb = tb < nt;
-  uint32_t qf[KS][4];
-  {
-    const bf16* qa = q + ((long long)(t0 + (va ? ta : 0)) * H + (kvh * G + ga)) * HD + ((lane & 3) << 1);
-    const bf16* qb = q + ((long long)(t0 + (vb ? tb : 0)) * H + (kvh * G + gb)) * HD + ((lane & 3) << 1);
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc_s = umma_idesc_bf16(XB_ATT_TILE);            // M=128, N=64, A/B K-major
+      constexpr uint32_t idesc_o = umma_idesc_bf16(HD) | (1u << 16);        // M=128, N=HD, B MN-major
+      mbar_wait(q_ready, 0);
+      tc_fence_after();
+      const uint32_t q_addr = smem_u32(sQ), p_addr = smem_u32(sP);
+      auto issue_qk = [&](int kt) {
+        const int stage = kt % Cfg::NST;
+        mbar_wait(&k_full[stage], (kt / Cfg::NST) & 1);
+        tc_fence_after();
+        const uint32_t k_addr = smem_u32(sKV + stage * 2 * Cfg::TILE_BYTES);
+        const uint32_t d = tm_S + (uint32_t)((kt & 1) * XB_ATT_TILE);
+        // S = Q K^T over hd in steps of 16; dims 64.. live in the second 128-byte-wide region
 #pragma unroll
-    for (int ks = 0; ks < KS; ++ks) {
-      uint32_t a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-      if (va) {
-        a0 = *reinterpret_cast<const uint32_t*>(qa + ks * 16);
-        a2 = *reinterpret_cast<const uint32_t*>(qa + ks * 16 + 8);
+        for (int ks = 0; ks < HD / 16; ++ks) {
+          const uint32_t a = q_addr + (ks >> 2) * (128 * 128) + (ks & 3) * 32;
+          const uint32_t b = k_addr + (ks >> 2) * (XB_ATT_TILE * 128) + (ks & 3) * 32;
+          tc_mma_bf16(d, umma_desc_sw128(a), umma_desc_sw128(b), idesc_s, ks > 0 ? 1u : 0u);
+        }
+        tc_commit(&k_empty[stage]);      // the K slot may be refilled as soon as these MMAs retire
+        tc_commit(&s_full[kt & 1]);
+      };
+      issue_qk(0);
+      for (int kt = 0; kt < n_kt; ++kt) {
+        // S buffer (kt+1)&1 was last read by the softmax of tile kt-1, which finished before p_full(kt-1)
+        if (kt + 1 < n_kt) issue_qk(kt + 1);
+        const int stage = kt % Cfg::NST;
+        const uint32_t v_addr = smem_u32(sKV + stage * 2 * Cfg::TILE_BYTES) + Cfg::TILE_BYTES;
+        // O += P V over the 64 keys in steps of 16
+        mbar_wait(&v_full[stage], (kt / Cfg::NST) & 1);
+        mbar_wait(&p_full[kt & 1], (kt >> 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int ks = 0; ks < XB_ATT_TILE / 16; ++ks) {
+          const uint32_t a = p_addr + ks * 32;
+          const uint32_t b = v_addr + ks * 2048;
+          tc_mma_bf16(tm_O, umma_desc_sw128(a), umma_desc_mn_sw128(b, XB_ATT_TILE * 128), idesc_o, (kt > 0 || ks > 0) ? 1u : 0u);
+        }
+        tc_commit(&v_empty[stage]);
+        tc_commit(&o_done[kt & 1]);
       }
-      if (vb) {
-        a1 = *reinterpret_cast<const uint32_t*>(qb + ks * 16);
-        a3 = *reinterpret_cast<const uint32_t*>(qb + ks * 16 + 8);
-      }
-      qf[ks][0] = a0; qf[ks][1] = a1; qf[ks][2] = a2; qf[ks][3] = a3;
     }
-  }
-  const int lim0 = va ? pos0 + ta : -1, lim1 = vb ? pos0 + tb : -1;
-  // last key any row of this WARP may see (warp-uniform): rows of the warp are consecutive
-  const int wt_last = (warp * 16 + 15) / G;
-  const int warp_lim = pos0 + (wt_last < nt ? wt_last : nt - 1);
-  const bool warp_active = (warp * 16) / G < nt;
-  float mrow[2] = {-INFINITY, -INFINITY}, lrow[2] = {0.f, 0.f};
-  float o[DT][4];
+  } else {
+    // ===================== softmax / correction / epilogue: warps 2..5, one row per thread =====
+    const int quad = warp & 3;
+    const int r = quad * 32 + lane;                 // query row = TMEM lane
+    const int tq = r / G, gq = r % G;
+    const bool valid = tq < nt;
+    const int lim = valid ? pos0 + tq : -1;
+    const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
+    // ---- stage Q into swizzled smem (K-major A operand), zero rows beyond the tile
+    {
+      const bf16* qrow = q + ((long long)(t0 + (valid ? tq : 0)) * H + (kvh * G + gq)) * HD;
 #pragma unroll
-  for (int d = 0; d < DT; ++d) o[d][0] = o[d][1] = o[d][2] = o[d][3] = 0.f;
-
-  int stage = 0;
-  uint32_t phase = 0;
-  for (int kt = 0; kt < n_tiles; ++kt) {
-    mbar_wait(&full_bar[stage], phase);
-    const int key_abs0 = kt * XB_ATT_TILE;
-    if (warp_active && key_abs0 <= warp_lim) {
-      const uint32_t sK = smem_u32(stages + stage * Cfg::STAGE_BYTES);
+      for (int c = 0; c < HD / 8; ++c) {
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (valid) v = *reinterpret_cast<const uint4*>(qrow + c * 8);
+        *reinterpret_cast<uint4*>(sQ + (c >> 3) * (128 * 128) + r * 128 + (((c & 7) ^ (r & 7)) << 4)) = v;
+      }
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(q_ready);
+    }
+    float m_used = -INFINITY;     // reference max (scaled, log2 units) that O and l are expressed against
+    float l_sum = 0.f;
+    for (int kt = 0; kt < n_kt; ++kt) {
+      mbar_wait(&s_full[kt & 1], (kt >> 1) & 1);
+      tc_fence_after();
+      const int key0 = kt * XB_ATT_TILE;
+      const uint32_t tm_Sk = tm_S + (uint32_t)((kt & 1) * XB_ATT_TILE);
+      // ---- the 64 scores of this row: ONE TMEM read, kept in registers for both steps below
+      uint32_t v[XB_ATT_TILE];
+#pragma unroll
+      for (int c = 0; c < XB_ATT_TILE; c += 16) tmem_ld16(tm_Sk + lane_base + c, v + c);
+      tmem_ld_wait();
+      // only tiles that reach past the first row's position need per-element causal masks
+      const bool masked = key0 + XB_ATT_TILE - 1 > pos0;
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // independent chains (ILP)
+      if (masked) {
+#pragma unroll
+        for (int j = 0; j < XB_ATT_TILE; ++j)
+          if (key0 + j <= lim) mx4[j & 3] = fmaxf(mx4[j & 3], __uint_as_float(v[j]));
+      } else {
+#pragma unroll
+        for (int j = 0; j < XB_ATT_TILE; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], __uint_as_float(v[j]));
+      }
+      const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * scale_log2;   // scale > 0
+      // ---- the (single) P buffer was last read by PV of tile kt-1
+      if (kt > 0) {
+        mbar_wait(&o_done[(kt - 1) & 1], ((kt - 1) >> 1) & 1);
+        tc_fence_after();
+      }
+      // ---- lazy rescale: only when some row of the warp moved by more than 2^8
+      const bool need = mx > m_used + 8.0f;
+      if (__any_sync(0xffffffffu, need)) {
+        const float m_new = need ? mx : m_used;
+        const float corr = (m_used == -INFINITY) ? 0.f : exp2f(m_used - m_new);
+        l_sum *= corr;
+        if (kt > 0) {   // O is quiescent: PV of tile kt-1 retired (waited above)
 #pragma unroll 1
-      for (int kb = 0; kb < XB_ATT_TILE / 32; ++kb) {
-        if (key_abs0 + kb * 32 <= warp_lim)
-          att_warp_block<HD, 2>(qf, sK, sK + Cfg::TILE_BYTES, kb * 32, key_abs0, lim0, lim1, scale_log2, mrow, lrow, o);
+          for (int c = 0; c < HD; c += 16) {
+            uint32_t o[16];
+            tmem_ld16(tm_O + lane_base + c, o);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 16; ++j) o[j] = __float_as_uint(__uint_as_float(o[j]) * corr);
+            tmem_st16(tm_O + lane_base + c, o);
+          }
+          tmem_st_wait();
+        }
+        m_used = m_new;
+      }
+      // ---- p = 2^(s*scale - m_used) -> bf16 -> swizzled smem (A operand of the PV MMA)
+      const float nmref = (m_used == -INFINITY) ? 0.f : -m_used;
+      float ps[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int c = 0; c < XB_ATT_TILE; c += 8) {
+        float p[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(p[j]) : "f"(fmaf(__uint_as_float(v[c + j]), scale_log2, nmref)));
+        if (masked) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            if (key0 + c + j > lim) p[j] = 0.f;
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) ps[j & 3] += p[j];
+        uint4 w;
+        w.x = f2_to_bf2(p[0], p[1]); w.y = f2_to_bf2(p[2], p[3]); w.z = f2_to_bf2(p[4], p[5]); w.w = f2_to_bf2(p[6], p[7]);
+        *reinterpret_cast<uint4*>(sP + r * 128 + ((((c >> 3)) ^ (r & 7)) << 4)) = w;
+      }
+      l_sum += (ps[0] + ps[1]) + (ps[2] + ps[3]);
+      fence_proxy_async();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&p_full[kt & 1]);
+    }
+    // ---- epilogue: O / l -> bf16 -> attention output row
+    mbar_wait(&o_done[(n_kt - 1) & 1], ((n_kt - 1) >> 1) & 1);
+    tc_fence_after();
+    const float inv = l_sum > 0.f ? 1.0f / l_sum : 0.f;
+    bf16* dst = out + ((long long)(t0 + (valid ? tq : 0)) * H + (kvh * G + gq)) * HD;
+#pragma unroll 1
+    for (int c = 0; c < HD; c += 16) {
+      uint32_t v[16];
+      tmem_ld16(tm_O + lane_base + c, v);
+      tmem_ld_wait();
+      if (valid) {
+        float x[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) x[j] = __uint_as_float(v[j]) * inv;
+        uint4 w0, w1;
+        w0.x = f2_to_bf2(x[0], x[1]);   w0.y = f2_to_bf2(x[2], x[3]);   w0.z = f2_to_bf2(x[4], x[5]);   w0.w = f2_to_bf2(x[6], x[7]);
+        w1.x = f2_to_bf2(x[8], x[9]);   w1.y = f2_to_bf2(x[10], x[11]); w1.z = f2_to_bf2(x[12], x[13]); w1.w = f2_to_bf2(x[14], x[15]);
+        reinterpret_cast<uint4*>(dst + c)[0] = w0;
+        reinterpret_cast<uint4*>(dst + c)[1] = w1;
       }
     }
-    __syncwarp();
-    if (lane == 0) mbar_arrive(&empty_bar[stage]);
-    if (++stage == NST) { stage = 0; phase ^= 1; }
   }
-
-  lrow[0] += __shfl_xor_sync(0xffffffffu, lrow[0], 1);
-  lrow[0] += __shfl_xor_sync(0xffffffffu, lrow[0], 2);
-  lrow[1] += __shfl_xor_sync(0xffffffffu, lrow[1], 1);
-  lrow[1] += __shfl_xor_sync(0xffffffffu, lrow[1], 2);
-  const float i0 = lrow[0] > 0.f ? 1.0f / lrow[0] : 0.f, i1 = lrow[1] > 0.f ? 1.0f / lrow[1] : 0.f;
-  if (va) {
-    bf16* dst = out + ((long long)(t0 + ta) * H + (kvh * G + ga)) * HD + ((lane & 3) << 1);
-#pragma unroll
-    for (int d = 0; d < DT; ++d) *reinterpret_cast<uint32_t*>(dst + d * 8) = f2_to_bf2(o[d][0] * i0, o[d][1] * i0);
-  }
-  if (vb) {
-    bf16* dst = out + ((long long)(t0 + tb) * H + (kvh * G + gb)) * HD + ((lane & 3) << 1);
-#pragma unroll
-    for (int d = 0; d < DT; ++d) *reinterpret_cast<uint32_t*>(dst + d * 8) = f2_to_bf2(o[d][2] * i1, o[d][3] * i1);
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, Cfg::TM_COLS);
   }
 }

@@ -455,17 +455,16 @@ static int launch_attn_g(xb_engine* e, const LayerW& w, const BatchMeta& m, int 
       XB_TRY(launch_k(e, xb_attn_combine2_kernel<HD>, dim3((rows + 3) / 4), dim3(128), 0, st, 1, e->o_part, e->ml_part, e->attn, n_splits, rows));
     }
   } else {
-    // prefill: one block per (query tile, kv head)
-    using Cfg = AttPreCfg<HD, NST>;
+    // prefill: one block per (query tile, kv head), tcgen05 flash attention
+    using Cfg = AttTcCfg<HD>;
     static bool attr_set = false;
     if (!attr_set) {
-      XB_CUDA(cudaFuncSetAttribute(xb_attn_prefill_mma_kernel<HD, G, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+      XB_CUDA(cudaFuncSetAttribute(xb_attn_prefill_tc_kernel<HD, G>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    Cfg::SMEM_BYTES));
       attr_set = true;
     }
-    dim3 grid(n_tiles, d.n_kv_heads);
-    XB_TRY(launch_k(e, xb_attn_prefill_mma_kernel<HD, G, NST>, dim3(grid), dim3(288), Cfg::SMEM_BYTES, st, 1, w.tmK, w.tmV, e->q, m, m.tile_start, m.tile_len,
-                                                                               e->attn, d.n_heads, d.n_kv_heads, scale_log2));
+    XB_TRY(launch_k(e, xb_attn_prefill_tc_kernel<HD, G>, dim3(n_tiles, d.n_kv_heads), dim3(192), Cfg::SMEM_BYTES, st, 1, w.tmK,
+                    w.tmV, e->q, m, m.tile_start, m.tile_len, e->attn, d.n_heads, d.n_kv_heads, scale_log2));
   }
   return 0;
 }
