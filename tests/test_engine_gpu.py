@@ -249,3 +249,35 @@ def test_long_prompt_prefill_multi_tile_attention(built_lib, mid, L):
   print(f"{mid} L={L}: hidden {worst_h:.4f} logits {e1:.4f} chunked {e2:.4f} decode {e3:.4f}")
   assert worst_h < REL_TOL and e1 < REL_TOL and e2 < REL_TOL and e3 < REL_TOL
   st.close()
+
+
+def test_long_context_chunked_prefill_beyond_page_cache(built_lib):
+  """8.5k-token context on a tiny model, prefilled in 2048-token chunks (BASELINE config 3 runs
+  8k contexts): more than 128 pages per sequence, so the attention producer's on-demand page
+  lookups and many-tile softmax rescaling are exercised; then cached decode steps."""
+  from xotorch_support_jetson_b200.shard import Shard
+  from xotorch_support_jetson_b200.stage import StageRuntime
+  mid = "llama-3.2-tiny"
+  O, cfg, state = _setup(mid)
+  nl = cfg["num_layers"]
+  L, CH = 8500, 2048
+  g = torch.Generator().manual_seed(5)
+  prompt = torch.randint(1, cfg["vocab_size"], (1, L), generator=g)
+  ref = O.OracleShardModel(cfg, mid, 0, nl - 1, state, O.OracleOptions(max_generated_tokens=8))
+  ref_toks, ref_logits, _ = O.greedy_generate([ref], prompt, 3, collect_logits=True)
+  st = StageRuntime(Shard(mid, 0, nl - 1, nl), cfg, device=0, max_batch_tokens=CH, max_seqs=1, max_tokens_per_seq=L + 64, page_tokens=64)
+  st.load_state(state)
+  toks = prompt.to(torch.int32).cuda().reshape(-1)
+  with torch.cuda.stream(torch.cuda.Stream()):
+    for c0 in range(0, L, CH):
+      c1 = min(L, c0 + CH)
+      lg = st.forward([0], [c1 - c0], [c0], tokens=toks[c0:c1])
+    errs = [_rel(lg.cpu().numpy(), ref_logits[0])]
+    for i in range(2):
+      x = torch.tensor([int(ref_toks[0, i])], dtype=torch.int32, device="cuda")
+      lg = st.forward([0], [1], [L + i], tokens=x)
+      errs.append(_rel(lg.cpu().numpy(), ref_logits[i + 1]))
+  torch.cuda.synchronize()
+  print(f"8.5k context: logits rel err prefill {errs[0]:.4f}, decode {errs[1]:.4f} {errs[2]:.4f}")
+  assert max(errs) < REL_TOL
+  st.close()

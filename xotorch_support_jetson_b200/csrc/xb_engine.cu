@@ -698,8 +698,7 @@ extern "C" int xb_forward(xb_engine* e, const xb_batch* b, void* out, void* cons
   // kv head), no kv split
   int n_splits = 1;
   if (decode_only) {
-    XB_CHECK(T <= 2 * e->num_sms, "decode batch of %d sequences exceeds the %d the split-KV workspace covers", T, 2 * e->num_sms);
-    n_splits = choose_kv_splits(e, T, max_ctx);
+    n_splits = choose_kv_splits(e, T, max_ctx);   // 1 once T * kv heads exceeds one wave (no split workspace needed)
   }
 
   if (decode_only && e->use_graphs && taps == nullptr && st != nullptr && st != cudaStreamLegacy) {
