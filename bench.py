@@ -92,41 +92,53 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------- reference / CPU baseline
-def cpu_decode_sample(hf_cfg, sample_batch: int, ctx: int, steps: int, warmup: int, weights_cpu=None, seed: int = 0):
-  """Times the oracle (reference-exact eager PyTorch: per-op bf16 modules, contiguous
-  [B, KV, prompt+1024, hd] cache, GQA expand, full-cache masked SDPA, top-k-35 sampler) on
-  the host cores: `steps` decode steps of `sample_batch` sequences at context `ctx`.  The
-  cache is filled with synthetic K/V instead of running the 2048-token prefill on the CPU
-  (the decode cost does not depend on the cached values)."""
-  import torch
-  from oracle import torch_oracle as O
-  torch.set_num_threads(os.cpu_count() or 1)
-  cfg = O.model_config_from_hf(hf_cfg)
-  nl = cfg["num_layers"]
-  if weights_cpu is None:
+class CpuDecodeSample:
+  """The oracle (reference-exact eager PyTorch: per-op bf16 modules, contiguous
+  [B, KV, prompt+1024, hd] cache, GQA expand, full-cache masked SDPA, top-k-35 sampler) on the
+  host cores: decode steps of `sample_batch` sequences at context `ctx`.  The cache is filled
+  with synthetic K/V instead of running the 2048-token prefill on the CPU (the decode cost does
+  not depend on the cached values)."""
+
+  def __init__(self, hf_cfg, model_id: str, sample_batch: int, ctx: int, seed: int = 0):
+    import numpy as np
+    import torch
+    from oracle import torch_oracle as O
     from xotorch_support_jetson_b200.synth import random_hf_state
+    torch.set_num_threads(os.cpu_count() or 1)
+    cfg = O.model_config_from_hf(hf_cfg)
+    nl = cfg["num_layers"]
     weights_cpu = random_hf_state(hf_cfg, seed=seed)
-  model = O.OracleShardModel(cfg, MODEL, 0, nl - 1, weights_cpu, O.OracleOptions())
-  eng = O.OracleEngine(model)
-  B = sample_batch
-  g = torch.Generator().manual_seed(1234)
-  prompt = torch.randint(1, cfg["vocab_size"], (B, ctx), generator=g)
-  eng.start_request(prompt)          # allocates the [B, KV, ctx+1024, hd] caches, mask and input_pos
-  for l in model.k_cache:
-    model.k_cache[l][:, :, :ctx].normal_(0, 0.5, generator=g)
-    model.v_cache[l][:, :, :ctx].normal_(0, 0.5, generator=g)
-  model.cache_pos = ctx
-  eng.curr_pos = ctx
-  import numpy as np
-  tok = np.ones((B, 1), dtype=np.int64)
-  times = []
-  for i in range(warmup + steps):
-    t0 = time.perf_counter()
-    logits = eng.infer_tensor(tok)
-    tok = eng.sample(logits, temp=0.0, top_k=35).astype(np.int64).reshape(B, 1)
-    times.append(time.perf_counter() - t0)
-  t = sum(times[warmup:])
-  return B * steps / t, t / steps
+    self.model = O.OracleShardModel(cfg, model_id, 0, nl - 1, weights_cpu, O.OracleOptions())
+    del weights_cpu
+    self.eng = O.OracleEngine(self.model)
+    self.B = sample_batch
+    g = torch.Generator().manual_seed(1234)
+    prompt = torch.randint(1, cfg["vocab_size"], (self.B, ctx), generator=g)
+    self.eng.start_request(prompt)   # allocates the [B, KV, ctx+1024, hd] caches, mask and input_pos
+    for l in self.model.k_cache:
+      self.model.k_cache[l][:, :, :ctx].normal_(0, 0.5, generator=g)
+      self.model.v_cache[l][:, :, :ctx].normal_(0, 0.5, generator=g)
+    self.model.cache_pos = ctx
+    self.eng.curr_pos = ctx
+    self.tok = np.ones((self.B, 1), dtype=np.int64)
+
+  def steps(self, n: int):
+    """Runs n decode steps (infer_tensor + sample), returns the list of per-step seconds."""
+    import numpy as np
+    times = []
+    for _ in range(n):
+      t0 = time.perf_counter()
+      logits = self.eng.infer_tensor(self.tok)
+      self.tok = self.eng.sample(logits, temp=0.0, top_k=35).astype(np.int64).reshape(self.B, 1)
+      times.append(time.perf_counter() - t0)
+    return times
+
+
+def cpu_decode_sample(hf_cfg, model_id, sample_batch: int, ctx: int, steps: int, warmup: int):
+  s = CpuDecodeSample(hf_cfg, model_id, sample_batch, ctx)
+  s.steps(warmup)
+  t = sum(s.steps(steps))
+  return sample_batch * steps / t, t / steps
 
 
 def run_reference(args):
@@ -140,15 +152,17 @@ def run_reference(args):
   cores = os.cpu_count() or 1
   sb = args.ref_batch
   steps, warm = args.steps, min(args.warmup, 2)
-  # keep the whole run within a few minutes: calibrate on one step
+  # keep the whole run within a few minutes: one model, calibrate on the warm-up steps
   import torch  # noqa: F401
   t0 = time.perf_counter()
-  val, per_step = cpu_decode_sample(hf_cfg, sb, args.prompt_len, 1, 1)
+  smp = CpuDecodeSample(hf_cfg, args.model, sb, args.prompt_len)
   setup_s = time.perf_counter() - t0
+  per_step = max(smp.steps(max(1, warm)))
   budget = 150.0
-  if per_step * (steps + warm) > budget:
-    steps = max(2, int(budget / per_step) - warm)
-  val, per_step = cpu_decode_sample(hf_cfg, sb, args.prompt_len, steps, warm)
+  if per_step * steps > budget:
+    steps = max(2, int(budget / per_step))
+  times = smp.steps(steps)
+  val, per_step = sb * steps / sum(times), sum(times) / steps
   sample = (f"{steps} decode steps of {sb} of the {args.batch * args.gpus} sequences at context {args.prompt_len} "
             f"(synthetic KV cache, no CPU prefill), oracle port in reference-exact mode")
   line = {
@@ -321,7 +335,7 @@ def run_b200(args):
     e2e = e2e_engine_api(runner, cfg, prompts[0], K, W)
     if rank == 0 and not args.no_cpu_baseline:
       t0 = time.perf_counter()
-      val, per_step = cpu_decode_sample(hf_cfg, args.ref_batch, L, args.cpu_steps, 1)
+      val, per_step = cpu_decode_sample(hf_cfg, args.model, args.ref_batch, L, args.cpu_steps, 1)
       cpu_base = {"value": val, "unit": "tok/s", "cores": os.cpu_count() or 1, "kind": "port",
                   "sample": f"{args.cpu_steps} decode steps of {args.ref_batch} sequences at context {L} (synthetic KV cache), "
                             f"oracle port in reference-exact mode, {time.perf_counter() - t0:.0f}s incl. weight init"}

@@ -561,8 +561,8 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
     LAUNCH_COUNT(e);
     if (gp->args.mode == XB_GEMM_SKINNY) {
       dim3 grid(T, d.n_heads + 2 * d.n_kv_heads);
-      XB_TRY(launch_k(e, xb_qkv_finalize_kernel<0>, grid, dim3(hd / 2), 0, st, 1, (const float*)e->gemm_out, gp->split,
-                      (long long)T * e->NQKV, nullptr, w.bqkv, e->rope, e->q, w.k_pool, w.v_pool, m, d.n_heads, d.n_kv_heads, hd,
+      XB_TRY(launch_k(e, xb_qkv_finalize_kernel, grid, dim3(hd / 2), 0, st, 1, (const float*)e->gemm_out, gp->split,
+                      (long long)T * e->NQKV, w.bqkv, e->rope, e->q, w.k_pool, w.v_pool, m, d.n_heads, d.n_kv_heads, hd,
                       d.rope_kind));
     }
     if (hd == 128) XB_TRY(launch_attn<128>(e, w, m, T, n_splits, n_tiles, st));
@@ -578,8 +578,8 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
     LAUNCH_COUNT(e);
     if (gp->args.mode == XB_GEMM_SKINNY) {
       const long long n = (long long)T * I;
-      XB_TRY(launch_k(e, xb_silu_mul_kernel<0>, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, st, 1, (const float*)e->gemm_out,
-                      gp->split, (long long)T * 2 * I, nullptr, e->act, T, I));
+      XB_TRY(launch_k(e, xb_silu_mul_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, st, 1, (const float*)e->gemm_out,
+                      gp->split, (long long)T * 2 * I, e->act, T, I));
     }
     XB_TRY(get_plan(e, SITE_DOWN, l, e->act, I, w.wdown, T, D, I, e->gemm_out, D, nullptr, 0, &gp));
     XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));

@@ -212,9 +212,8 @@ __global__ void __launch_bounds__(NT) xb_resid_norm_cluster_kernel(const float* 
 //     rope_kind 1: half-split pairs (i,i+hd/2), every product and the sum rounded to bf16
 //                  (Qwen2RotaryPositionalEmbeddings, general_mha.py:47-51)
 //   q -> q_out[t][h*hd..]; k,v -> the paged cache (KVCache.update, llm_utils.py:320-345)
-template <int SRC>
 __global__ void xb_qkv_finalize_kernel(const float* __restrict__ part, SplitInfo si, long long split_stride,
-                                       const bf16* __restrict__ y, const bf16* __restrict__ bias,
+                                       const bf16* __restrict__ bias,
                                        const float* __restrict__ rope, bf16* __restrict__ q_out, bf16* __restrict__ k_pool,
                                        bf16* __restrict__ v_pool, BatchMeta m, int H, int KV, int hd, int rope_kind) {
   pdl_launch_dependents();
@@ -228,7 +227,7 @@ __global__ void xb_qkv_finalize_kernel(const float* __restrict__ part, SplitInfo
   if (rope_kind == 0) { e0 = 2 * i; e1 = 2 * i + 1; } else { e0 = i; e1 = i + half; }
   const long long base = (long long)t * NQKV + (long long)head * hd;
   float x0, x1;
-  if (SRC == 0) {
+  {
     float a = 0.f, b = 0.f;
     const int splits = xb_n_segments(si, head * hd + e0);   // e0 and e1 lie in the same 128-column tile
     for (int s = 0; s < splits; ++s) {
@@ -241,9 +240,6 @@ __global__ void xb_qkv_finalize_kernel(const float* __restrict__ part, SplitInfo
     }
     x0 = rbf(a);
     x1 = rbf(b);
-  } else {
-    x0 = bf2f(y[base + e0]);
-    x1 = bf2f(y[base + e1]);
   }
   const int pos = m.tok_pos[t];
   if (head < H + KV) {
@@ -278,10 +274,10 @@ __global__ void xb_qkv_finalize_kernel(const float* __restrict__ part, SplitInfo
 
 // ----------------------------------------------------------------------------- SiLU(gate) * up
 // FeedForward (llm_utils.py:513-522): w2(silu(w1 x) * w3 x); silu output and the product
-// are separate bf16 ops in the reference.  Input = fused [gate | up] projection.
-template <int SRC>
+// are separate bf16 ops in the reference.  Input = split-K partial planes of the fused gate/up
+// projection (decode path; the prefill GEMM does this in its epilogue, xb_gemm.cuh epi_wide_silu).
 __global__ void xb_silu_mul_kernel(const float* __restrict__ part, SplitInfo si, long long split_stride,
-                                   const bf16* __restrict__ y, bf16* __restrict__ act, int T, int I) {
+                                   bf16* __restrict__ act, int T, int I) {
   pdl_launch_dependents();
   pdl_wait();
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -291,16 +287,13 @@ __global__ void xb_silu_mul_kernel(const float* __restrict__ part, SplitInfo si,
   const int cg = (i >> 4) * 32 + (i & 15), cu = cg + 16;
   const long long og = (long long)t * 2 * I + cg, ou = (long long)t * 2 * I + cu;
   float g, u;
-  if (SRC == 0) {
+  {
     g = 0.f; u = 0.f;
     const int sg_n = xb_n_segments(si, cg), su_n = xb_n_segments(si, cu);
     for (int s = 0; s < sg_n; ++s) g += part[s * split_stride + og];
     for (int s = 0; s < su_n; ++s) u += part[s * split_stride + ou];
     g = rbf(g);
     u = rbf(u);
-  } else {
-    g = bf2f(y[og]);
-    u = bf2f(y[ou]);
   }
   const float sg = rbf(g / (1.0f + expf(-g)));
   act[idx] = f2bf(sg * u);
