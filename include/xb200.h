@@ -118,6 +118,25 @@ int xb_kv_slot_len(xb_engine* e, int slot, int* len);
  * receive the residual stream after each layer (parity instrumentation). */
 int xb_forward(xb_engine* e, const xb_batch* batch, void* out, void* const* taps, void* stream);
 
+/* Intra-box hand-off between pipeline stages over NVLink peer memory, replacing the per-token gRPC
+ * SendTensor hop of the reference (Node.forward_tensor, xotorch/orchestration/node.py:424-443;
+ * GRPCPeerHandle.send_tensor, xotorch/networking/grpc/grpc_peer_handle.py:117-136) for decode steps.
+ * Every stage calls xb_handoff_create (n_slots landing buffers of `rows` x dim bf16 + one flag
+ * each; the two 64-byte CUDA IPC handles are exchanged by the host, e.g. all_gather) and every
+ * non-last stage xb_handoff_connect with the handles of the NEXT stage.  xb_forward_handoff is
+ * xb_forward for a decode-only batch where
+ *   slot_in  >= 0: the hidden rows are taken from this stage's landing[slot_in] once its flag has
+ *                  reached wait_value (the stage's first kernel spins on the flag; batch->hidden_in
+ *                  is ignored);
+ *   slot_out >= 0: the stage's last kernel stores the hidden rows into the next stage's
+ *                  landing[slot_out] and then sets that flag to signal_value (`out` is ignored).
+ * Flags only grow; use a per-slot step counter.  A slot may be rewritten once its consumer has run
+ * (in a ring of stages this follows from the token that travels back to the first stage). */
+int xb_handoff_create(xb_engine* e, int n_slots, int rows, void* landing_handle, void* flag_handle);
+int xb_handoff_connect(xb_engine* e, const void* next_landing_handle, const void* next_flag_handle);
+int xb_forward_handoff(xb_engine* e, const xb_batch* batch, int slot_in, int wait_value, int slot_out, int signal_value,
+                       void* out, void* stream);
+
 /* Replaces TorchDynamicShardInferenceEngine.sample + torchtune.generation.sample
  * (sharded_inference_engine.py:208-228).  logits: device fp32 [n, vocab].
  * temp <= 0 selects first-index argmax.  top_k <= 0 and top_p <= 0 (or >= 1) disable

@@ -42,6 +42,7 @@ def main():
   for k in range(K):
     r.decode(1)
     r.drain()
+    torch.cuda.synchronize()   # the runner works on its own stream; read the ids only when it is done
     if rank == world - 1:
       hist.append(torch.stack([t.clone() for t in r.tok]).cpu())
   torch.cuda.synchronize()

@@ -8,6 +8,7 @@
 
 #include <stdarg.h>
 #include <stdlib.h>
+#include <string.h>
 #include <map>
 #include <vector>
 
@@ -67,6 +68,15 @@ struct xb_engine {
   std::map<long long, StepGraph> graphs;
   int use_graphs = 1;
   int use_pdl = 1;
+  // peer hand-off (pipeline decode): landing buffers of THIS stage (written by the previous GPU) and
+  // the peer-mapped landing buffers of the NEXT stage
+  bf16* landing = nullptr;
+  uint32_t* flags = nullptr;
+  unsigned int* done_cnt = nullptr;
+  bf16* peer_landing = nullptr;
+  uint32_t* peer_flags = nullptr;
+  int ho_slots = 0, ho_rows = 0;
+  HandoffCtl* d_ctl = nullptr;
   // workspaces
   bf16 *h = nullptr, *hn = nullptr, *q = nullptr, *attn = nullptr, *act = nullptr, *last_rows = nullptr;
   void* gemm_out = nullptr;
@@ -223,7 +233,7 @@ extern "C" int xb_engine_create(const xb_model_desc* desc, int device, xb_engine
   XB_TRY(dmalloc((void**)&e->ml_part, Tsplit * d.n_heads * e->max_attn_splits * 2 * sizeof(float)));
   e->tile_tokens = 128 / (d.n_heads / d.n_kv_heads);
   e->max_tiles = (int)(T / e->tile_tokens) + d.max_seqs + 1;
-  e->meta_ints = 2 * T + 2 * (size_t)d.max_seqs + 2 * (size_t)e->max_tiles;
+  e->meta_ints = 2 * T + 2 * (size_t)d.max_seqs + 2 * (size_t)e->max_tiles + 4;
   XB_TRY(dmalloc((void**)&e->d_meta, e->meta_ints * 4));
   e->d_tok_seq = e->d_meta;
   e->d_tok_pos = e->d_meta + T;
@@ -231,6 +241,7 @@ extern "C" int xb_engine_create(const xb_model_desc* desc, int device, xb_engine
   e->d_seq_last = e->d_meta + 2 * T + d.max_seqs;
   e->d_tile_start = e->d_meta + 2 * T + 2 * d.max_seqs;
   e->d_tile_len = e->d_tile_start + e->max_tiles;
+  e->d_ctl = reinterpret_cast<HandoffCtl*>(e->d_tile_len + e->max_tiles);
   for (int i = 0; i < xb_engine::META_RING; ++i) {
     XB_CUDA(cudaMallocHost((void**)&e->h_meta_ring[i], e->meta_ints * 4));
     XB_CUDA(cudaEventCreateWithFlags(&e->meta_ev[i], cudaEventDisableTiming));
@@ -257,6 +268,9 @@ extern "C" int xb_engine_destroy(xb_engine* e) {
   }
   cudaFree(e->embed); cudaFree(e->final_norm); cudaFree(e->lm_head); cudaFree(e->rope);
   cudaFree(e->d_page_table); cudaFree(e->d_meta); cudaFree(e->in_tokens); cudaFree(e->logits);
+  if (e->peer_landing) cudaIpcCloseMemHandle(e->peer_landing);
+  if (e->peer_flags) cudaIpcCloseMemHandle(e->peer_flags);
+  cudaFree(e->landing); cudaFree(e->flags); cudaFree(e->done_cnt);
   for (int i = 0; i < xb_engine::META_RING; ++i) {
     if (e->h_meta_ring[i]) cudaFreeHost(e->h_meta_ring[i]);
     if (e->meta_ev[i]) cudaEventDestroy(e->meta_ev[i]);
@@ -529,7 +543,8 @@ static int choose_kv_splits(xb_engine* e, int T, int max_ctx) {
 // e->h (other shards); leaves the residual stream in e->h and, on a last shard, the logits
 // of each sequence's last position in e->logits.  Pure stream work on fixed addresses, so it
 // can be captured into a CUDA graph.
-static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, void* const* taps, cudaStream_t st) {
+static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, void* const* taps, cudaStream_t st,
+                    int ho_in = 0, int ho_out = 0) {
   const xb_model_desc& d = e->d;
   const bool first = d.start_layer == 0, last = d.end_layer == d.n_layers - 1;
   BatchMeta m;
@@ -547,6 +562,11 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
   if (first) {
     XB_TRY(launch_k(e, xb_embed_norm_kernel<256>, dim3(T), dim3(256), 0, st, 1, e->in_tokens, e->embed, e->L[0].sa_norm, e->h, e->hn, D, d.vocab, d.norm_eps,
                                                   d.rmsnorm_two_round));
+  } else if (ho_in) {
+    // stage input arrives in the landing buffer, stored there by the previous GPU's last kernel
+    XB_TRY(launch_k(e, xb_recv_norm_kernel<256>, dim3(T), dim3(256), norm_smem, st, 1, (const bf16*)e->landing,
+                    (const uint32_t*)e->flags, (const HandoffCtl*)e->d_ctl, (long long)e->ho_rows * D, e->h, e->L[0].sa_norm, e->hn, D,
+                    d.norm_eps, d.rmsnorm_two_round));
   } else {
     XB_TRY(launch_k(e, xb_resid_norm_kernel<256, 2>, dim3(T), dim3(256), norm_smem, st, 1, nullptr, SplitInfo{1, 0, 1}, 0, nullptr, e->h, e->L[0].sa_norm, e->hn, D,
                                                              d.norm_eps, d.rmsnorm_two_round));
@@ -585,7 +605,14 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
     XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
     LAUNCH_COUNT(e);
     const bf16* next_norm = (l + 1 < e->nl) ? e->L[l + 1].sa_norm : (last ? e->final_norm : nullptr);
-    XB_TRY(launch_resid_norm(e, gp, T, next_norm, st));
+    if (ho_out && l + 1 == e->nl && gp->args.mode == XB_GEMM_SKINNY) {
+      // stage output: reduce + residual, stored straight into the next GPU's landing buffer
+      XB_TRY(launch_k(e, xb_resid_send_kernel<256>, dim3(T), dim3(256), 0, st, 1, (const float*)e->gemm_out, gp->split,
+                      (long long)T * D, e->h, e->peer_landing, e->peer_flags, e->done_cnt, (const HandoffCtl*)e->d_ctl,
+                      (long long)e->ho_rows * D, D));
+    } else {
+      XB_TRY(launch_resid_norm(e, gp, T, next_norm, st));
+    }
     if (taps != nullptr && taps[l] != nullptr)
       XB_CUDA(cudaMemcpyAsync(taps[l], e->h, (size_t)T * D * 2, cudaMemcpyDeviceToDevice, st));
   }
@@ -602,15 +629,16 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
   return 0;
 }
 
-extern "C" int xb_forward(xb_engine* e, const xb_batch* b, void* out, void* const* taps, void* stream) {
+static int forward_impl(xb_engine* e, const xb_batch* b, void* out, void* const* taps, void* stream, const int* ctl) {
   XB_CHECK(e != nullptr && b != nullptr, "null argument");
+  const int ho_in = ctl != nullptr && ctl[0] >= 0, ho_out = ctl != nullptr && ctl[2] >= 0;
   const xb_model_desc& d = e->d;
   cudaStream_t st = (cudaStream_t)stream;
   XB_CUDA(cudaSetDevice(e->device));
   XB_CHECK(e->n_slots > 0, "xb_kv_reserve must be called before xb_forward");
   XB_CHECK(b->n_seqs > 0 && b->n_seqs <= d.max_seqs, "n_seqs %d out of range (max %d)", b->n_seqs, d.max_seqs);
   const bool first = d.start_layer == 0, last = d.end_layer == d.n_layers - 1;
-  XB_CHECK(first ? (b->tokens != nullptr) : (b->hidden_in != nullptr),
+  XB_CHECK(first ? (b->tokens != nullptr) : (ho_in || b->hidden_in != nullptr),
            first ? "first shard needs token ids" : "non-first shard needs a hidden state");
   XB_CHECK(!last || b->n_seqs <= 128, "LM head path supports up to 128 sequences per call");
   // ---- host-side batch bookkeeping
@@ -688,11 +716,21 @@ extern "C" int xb_forward(xb_engine* e, const xb_batch* b, void* out, void* cons
   } else {
     XB_CUDA(cudaMemcpyAsync(e->d_meta, hm, e->meta_ints * 4, cudaMemcpyHostToDevice, st));
   }
+  if (ctl != nullptr) {
+    XB_CHECK(decode_only, "the peer hand-off carries decode steps only");
+    XB_CHECK(!ho_in || (!first && e->landing != nullptr && ctl[0] < e->ho_slots && T <= e->ho_rows),
+             "hand-off input: needs a non-first shard with xb_handoff_create done, slot < %d, rows <= %d", e->ho_slots, e->ho_rows);
+    XB_CHECK(!ho_out || (!last && e->peer_landing != nullptr && ctl[2] < e->ho_slots && T <= e->ho_rows),
+             "hand-off output: needs a non-last shard with xb_handoff_connect done, slot < %d, rows <= %d", e->ho_slots, e->ho_rows);
+    int* hc = hm + e->meta_ints - 4;
+    hc[0] = ctl[0]; hc[1] = ctl[1]; hc[2] = ctl[2]; hc[3] = ctl[3];
+    XB_CUDA(cudaMemcpyAsync(e->d_ctl, hc, 16, cudaMemcpyHostToDevice, st));
+  }
   XB_CUDA(cudaEventRecord(e->meta_ev[ring], st));
 
   // ---- inputs to fixed addresses
   if (first) XB_CUDA(cudaMemcpyAsync(e->in_tokens, b->tokens, (size_t)T * 4, cudaMemcpyDeviceToDevice, st));
-  else XB_CUDA(cudaMemcpyAsync(e->h, b->hidden_in, (size_t)T * d.dim * 2, cudaMemcpyDeviceToDevice, st));
+  else if (!ho_in) XB_CUDA(cudaMemcpyAsync(e->h, b->hidden_in, (size_t)T * d.dim * 2, cudaMemcpyDeviceToDevice, st));
 
   // decode: split every context across blocks (split-KV); prefill: one block per (query tile,
   // kv head), no kv split
@@ -704,13 +742,13 @@ extern "C" int xb_forward(xb_engine* e, const xb_batch* b, void* out, void* cons
   if (decode_only && e->use_graphs && taps == nullptr && st != nullptr && st != cudaStreamLegacy) {
     // decode step: replay a captured graph (first call of a shape runs eagerly to build the
     // launch plans and set kernel attributes, second call captures)
-    const long long key = ((long long)b->n_seqs << 16) | n_splits;
+    const long long key = ((long long)b->n_seqs << 16) | (n_splits << 2) | (ho_in << 1) | ho_out;
     xb_engine::StepGraph& sg = e->graphs[key];
     if (sg.exec == nullptr && sg.warmed) {
       cudaGraph_t graph = nullptr;
       const uint64_t before = e->c.launches;
       XB_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-      const int rc = run_body(e, T, b->n_seqs, n_splits, 0, nullptr, st);
+      const int rc = run_body(e, T, b->n_seqs, n_splits, 0, nullptr, st, ho_in, ho_out);
       cudaError_t ce = cudaStreamEndCapture(st, &graph);
       if (rc != 0) { if (graph) cudaGraphDestroy(graph); return rc; }
       XB_CUDA(ce);
@@ -723,18 +761,62 @@ extern "C" int xb_forward(xb_engine* e, const xb_batch* b, void* out, void* cons
       XB_CUDA(cudaGraphLaunch(sg.exec, st));
       e->c.launches += sg.launches;
     } else {
-      XB_TRY(run_body(e, T, b->n_seqs, n_splits, 0, nullptr, st));
+      XB_TRY(run_body(e, T, b->n_seqs, n_splits, 0, nullptr, st, ho_in, ho_out));
       sg.warmed = 1;
     }
   } else {
-    XB_TRY(run_body(e, T, b->n_seqs, n_splits, n_tiles, taps, st));
+    XB_TRY(run_body(e, T, b->n_seqs, n_splits, n_tiles, taps, st, ho_in, ho_out));
   }
 
-  if (out != nullptr) {
+  if (out != nullptr && !(ho_out && !last)) {
     if (last) XB_CUDA(cudaMemcpyAsync(out, e->logits, (size_t)b->n_seqs * d.vocab * sizeof(float), cudaMemcpyDeviceToDevice, st));
     else XB_CUDA(cudaMemcpyAsync(out, e->h, (size_t)T * d.dim * 2, cudaMemcpyDeviceToDevice, st));
   }
   e->c.forwards++;
+  return 0;
+}
+
+extern "C" int xb_forward(xb_engine* e, const xb_batch* b, void* out, void* const* taps, void* stream) {
+  return forward_impl(e, b, out, taps, stream, nullptr);
+}
+
+extern "C" int xb_forward_handoff(xb_engine* e, const xb_batch* b, int slot_in, int wait_value, int slot_out, int signal_value,
+                                  void* out, void* stream) {
+  const int ctl[4] = {slot_in, wait_value, slot_out, signal_value};
+  return forward_impl(e, b, out, nullptr, stream, ctl);
+}
+
+extern "C" int xb_handoff_create(xb_engine* e, int n_slots, int rows, void* landing_handle, void* flag_handle) {
+  XB_CHECK(e != nullptr && n_slots > 0 && rows > 0 && rows <= 128 && landing_handle && flag_handle, "bad argument");
+  XB_CUDA(cudaSetDevice(e->device));
+  XB_CHECK(e->landing == nullptr, "hand-off buffers already created");
+  const size_t bytes = (size_t)n_slots * rows * e->d.dim * 2;
+  XB_TRY(dmalloc((void**)&e->landing, bytes));
+  XB_TRY(dmalloc((void**)&e->flags, (size_t)n_slots * 4));
+  XB_TRY(dmalloc((void**)&e->done_cnt, (size_t)n_slots * 4));
+  XB_CUDA(cudaMemset(e->landing, 0, bytes));
+  XB_CUDA(cudaMemset(e->flags, 0, (size_t)n_slots * 4));
+  XB_CUDA(cudaMemset(e->done_cnt, 0, (size_t)n_slots * 4));
+  e->ho_slots = n_slots;
+  e->ho_rows = rows;
+  XB_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(landing_handle), e->landing));
+  XB_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(flag_handle), e->flags));
+  XB_CUDA(cudaDeviceSynchronize());
+  return 0;
+}
+
+extern "C" int xb_handoff_connect(xb_engine* e, const void* next_landing_handle, const void* next_flag_handle) {
+  XB_CHECK(e != nullptr && next_landing_handle && next_flag_handle, "bad argument");
+  XB_CHECK(e->ho_slots > 0, "call xb_handoff_create first (slot geometry is shared by all stages)");
+  XB_CUDA(cudaSetDevice(e->device));
+  cudaIpcMemHandle_t hl, hf;
+  memcpy(&hl, next_landing_handle, sizeof(hl));
+  memcpy(&hf, next_flag_handle, sizeof(hf));
+  void *pl = nullptr, *pf = nullptr;
+  XB_CUDA(cudaIpcOpenMemHandle(&pl, hl, cudaIpcMemLazyEnablePeerAccess));
+  XB_CUDA(cudaIpcOpenMemHandle(&pf, hf, cudaIpcMemLazyEnablePeerAccess));
+  e->peer_landing = (bf16*)pl;
+  e->peer_flags = (uint32_t*)pf;
   return 0;
 }
 

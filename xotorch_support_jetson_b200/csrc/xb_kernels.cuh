@@ -202,6 +202,108 @@ __global__ void __launch_bounds__(NT) xb_resid_norm_cluster_kernel(const float* 
   }
 }
 
+// ----------------------------------------------------------------------------- peer hand-off (pipeline, decode)
+// Replaces the gRPC SendTensor hop of the reference (Node.forward_tensor, orchestration/node.py:
+// 424-443; GRPCPeerHandle.send_tensor, networking/grpc/grpc_peer_handle.py:117-136) inside one box:
+// the producing stage's LAST kernel stores its hidden rows straight into the next GPU's landing
+// buffer through an NVLink peer mapping and then releases a flag; the consuming stage's FIRST
+// kernel acquires the flag and fuses the read with its RMSNorm.  No copy kernel, no NCCL launch.
+struct HandoffCtl {      // lives in device memory next to the batch metadata (graph replays re-read it)
+  int slot_in, wait_value, slot_out, signal_value;
+};
+
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// consumer head: wait for landing[slot_in] (flag >= wait_value), h = landing row, hn = RMSNorm(h)
+template <int NT>
+__global__ void __launch_bounds__(NT) xb_recv_norm_kernel(const bf16* __restrict__ landing, const uint32_t* __restrict__ flags,
+                                                          const HandoffCtl* __restrict__ ctl, long long slot_elems,
+                                                          bf16* __restrict__ h, const bf16* __restrict__ nw,
+                                                          bf16* __restrict__ hn, int D, float eps, int two_round) {
+  pdl_launch_dependents();
+  pdl_wait();
+  __shared__ float red[32];
+  extern __shared__ float row[];
+  const int t = blockIdx.x;
+  const int slot = ctl->slot_in;
+  const uint32_t want = (uint32_t)ctl->wait_value;
+  if (threadIdx.x == 0) {
+    long long t0 = clock64();
+    while ((int32_t)(ld_acquire_sys(flags + slot) - want) < 0) {
+      if (clock64() - t0 > 4000000000LL) {
+        printf("xb200: hand-off flag wait timed out (slot %d want %u)\n", slot, want);
+        __trap();
+      }
+    }
+  }
+  __syncthreads();
+  const bf16* src = landing + (long long)slot * slot_elems + (long long)t * D;
+  float ss = 0.f;
+  for (int i = threadIdx.x * 2; i < D; i += NT * 2) {
+    uint32_t u;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(u) : "l"(src + i) : "memory");   // written by a peer GPU
+    *reinterpret_cast<uint32_t*>(h + (long long)t * D + i) = u;
+    const float2 f = bf2_to_f2(u);
+    row[i] = f.x;
+    row[i + 1] = f.y;
+    ss += f.x * f.x + f.y * f.y;
+  }
+  ss = block_sum<NT>(ss, red);
+  const float inv = 1.0f / sqrtf(ss / (float)D + eps);
+  for (int i = threadIdx.x * 2; i < D; i += NT * 2) {
+    const float2 w = bf2_to_f2(*reinterpret_cast<const uint32_t*>(nw + i));
+    *reinterpret_cast<uint32_t*>(hn + (long long)t * D + i) =
+        f2_to_bf2(rms_apply(row[i], inv, w.x, two_round), rms_apply(row[i + 1], inv, w.y, two_round));
+  }
+}
+
+// producer tail: split-K reduce + Linear rounding + residual add (the stage's final hidden rows),
+// stored locally AND into the next GPU's landing[slot_out]; the last block to finish releases the flag.
+template <int NT>
+__global__ void __launch_bounds__(NT) xb_resid_send_kernel(const float* __restrict__ part, SplitInfo si, long long split_stride,
+                                                           bf16* __restrict__ h, bf16* __restrict__ peer_landing,
+                                                           uint32_t* __restrict__ peer_flags, unsigned int* __restrict__ done_cnt,
+                                                           const HandoffCtl* __restrict__ ctl, long long slot_elems, int D) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int t = blockIdx.x;
+  const int slot = ctl->slot_out;
+  bf16* dst = peer_landing + (long long)slot * slot_elems + (long long)t * D;
+  for (int i = threadIdx.x * 4; i < D; i += NT * 4) {
+    const long long o = (long long)t * D + i;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    const int splits = xb_n_segments(si, i);
+    for (int s = 0; s < splits; ++s) {
+      const float4 p = *reinterpret_cast<const float4*>(part + s * split_stride + o);
+      a.x += p.x; a.y += p.y; a.z += p.z; a.w += p.w;
+    }
+    const uint2 hu = *reinterpret_cast<const uint2*>(h + o);
+    const float2 h0 = bf2_to_f2(hu.x), h1 = bf2_to_f2(hu.y);
+    uint2 r;
+    r.x = f2_to_bf2(h0.x + rbf(a.x), h0.y + rbf(a.y));
+    r.y = f2_to_bf2(h1.x + rbf(a.z), h1.y + rbf(a.w));
+    *reinterpret_cast<uint2*>(h + o) = r;
+    *reinterpret_cast<uint2*>(dst + i) = r;          // NVLink peer store
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int prev = atomicAdd(done_cnt + slot, 1u);
+    if (prev == gridDim.x - 1) {
+      done_cnt[slot] = 0;
+      __threadfence_system();
+      st_release_sys(peer_flags + slot, (uint32_t)ctl->signal_value);
+    }
+  }
+}
+
 // ----------------------------------------------------------------------------- QKV finalize
 // One block per (token, head) over the fused [q | k | v] projection output.
 //   value = bf16(sum_splits(partial) + bias)        (nn.Linear rounding)

@@ -12,6 +12,7 @@ equal peers (``topology.pipeline_shards``); the hand-off is a bf16 ``[B, dim]`` 
 and N micro-batches are kept in flight so every stage is busy in steady state.  Each
 stage reads its weight slice once per micro-batch.
 """
+import os
 import zlib
 from typing import Callable, Dict, List, Optional
 
@@ -83,6 +84,17 @@ class PipelineRunner:
       self.stream = torch.cuda.Stream(device=self.device)
     self.dim, self.vocab = config["embed_dim"], config["vocab_size"]
     self.max_batch_tokens = max_batch_tokens
+    # decode hand-off over NVLink peer memory (fused into the stages' last / first kernels);
+    # prefill chunks and the token return edge stay on NCCL.  XB_PEER_HANDOFF=0 forces NCCL.
+    self.peer = False
+    self.ho_step = [0] * micro_batches      # per-slot flag value of the last hand-off
+    if world > 1 and stage_factory is None and batch <= 128 and os.environ.get("XB_PEER_HANDOFF", "1") != "0":
+      handles = self.stage.handoff_create(micro_batches, batch)
+      gathered = [None] * world
+      dist.all_gather_object(gathered, handles)
+      if rank + 1 < world:
+        self.stage.handoff_connect(*gathered[rank + 1])
+      self.peer = True
     B, M = batch, micro_batches
     self.tok = [torch.zeros(B, dtype=torch.int32, device=self.device) for _ in range(M)]
     self.h_in = torch.empty((max_batch_tokens, self.dim), dtype=torch.bfloat16, device=self.device)
@@ -192,6 +204,22 @@ class PipelineRunner:
             self.stage.sample(lg, temp=0.0, out=self.tok[m])
             if host_out is not None:
               host_out[m].copy_(self.tok[m], non_blocking=True)
+          elif self.peer:
+            # hidden rows travel GPU -> GPU inside the stages' own kernels (no send/recv launch)
+            self.ho_step[m] += 1
+            v = self.ho_step[m]
+            ho = (-1 if self.first else m, v, -1 if self.last else m, v)
+            if self.last:
+              lg = self.stage.forward(slots, ones, pos, out=self.logits, handoff=ho)
+              self._wait_tok(m)            # previous send of this buffer has completed
+              self.stage.sample(lg, temp=0.0, out=self.tok[m])
+              if host_out is not None:
+                host_out[m].copy_(self.tok[m], non_blocking=True)
+              self._post_tok_send(m)
+            else:
+              self.stage.forward(slots, ones, pos, tokens=self.tok[m] if self.first else None, handoff=ho)
+              if self.first:
+                self._post_tok_recv(m)     # next step's ids, posted ahead
           elif self.first:
             out = self.stage.forward(slots, ones, pos, tokens=self.tok[m], out=self.h_out[:B])
             self._send(out, 1)

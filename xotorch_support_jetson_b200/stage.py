@@ -148,7 +148,8 @@ class StageRuntime:
   # -- compute
   def forward(self, slot_ids: Sequence[int], q_lens: Sequence[int], positions: Sequence[int],
               tokens: Optional[torch.Tensor] = None, hidden: Optional[torch.Tensor] = None,
-              out: Optional[torch.Tensor] = None, taps: Optional[List[torch.Tensor]] = None) -> torch.Tensor:
+              out: Optional[torch.Tensor] = None, taps: Optional[List[torch.Tensor]] = None,
+              handoff: Optional[tuple] = None) -> Optional[torch.Tensor]:
     """tokens: int32 [T] (first shard) / hidden: bf16 [T, D].  Returns bf16 [T, D] hidden
     or fp32 [n_seqs, V] logits (last shard).  Enqueued on the current torch stream."""
     n = len(slot_ids)
@@ -162,7 +163,8 @@ class StageRuntime:
     if hidden is not None:
       assert hidden.dtype == torch.bfloat16 and hidden.is_cuda and hidden.numel() == T * self.dim and hidden.is_contiguous()
       b.hidden_in = hidden.data_ptr()
-    if out is None:
+    sends = handoff is not None and handoff[2] >= 0
+    if out is None and not sends:
       if self.shard.is_last_layer():
         out = torch.empty((n, self.vocab), dtype=torch.float32, device=self.device)
       else:
@@ -171,8 +173,25 @@ class StageRuntime:
     if taps is not None:
       tap_ptrs = (C.c_void_p * len(taps))(*[t.data_ptr() for t in taps])
     stream = torch.cuda.current_stream(self.device).cuda_stream
-    _cabi.check(self.lib.xb_forward(self._h, C.byref(b), C.c_void_p(out.data_ptr()), tap_ptrs, C.c_void_p(stream)))
+    optr = C.c_void_p(out.data_ptr()) if out is not None else None
+    if handoff is not None:
+      # (slot_in, wait_value, slot_out, signal_value): input from / output to the NVLink landing buffers
+      _cabi.check(self.lib.xb_forward_handoff(self._h, C.byref(b), int(handoff[0]), int(handoff[1]), int(handoff[2]),
+                                              int(handoff[3]), optr, C.c_void_p(stream)))
+      return None if sends else out
+    _cabi.check(self.lib.xb_forward(self._h, C.byref(b), optr, tap_ptrs, C.c_void_p(stream)))
     return out
+
+  def handoff_create(self, n_slots: int, rows: int) -> tuple:
+    """Allocate this stage's landing buffers; returns the two CUDA IPC handles (bytes)."""
+    hl, hf = C.create_string_buffer(64), C.create_string_buffer(64)
+    _cabi.check(self.lib.xb_handoff_create(self._h, int(n_slots), int(rows), hl, hf))
+    return bytes(hl.raw), bytes(hf.raw)
+
+  def handoff_connect(self, landing_handle: bytes, flag_handle: bytes):
+    """Map the NEXT stage's landing buffers (handles from its handoff_create)."""
+    hl, hf = C.create_string_buffer(landing_handle, 64), C.create_string_buffer(flag_handle, 64)
+    _cabi.check(self.lib.xb_handoff_connect(self._h, hl, hf))
 
   def sample(self, logits: torch.Tensor, temp: float = 0.0, top_k: int = 0, top_p: float = 0.0,
              q: Optional[torch.Tensor] = None, seed: int = 0, out: Optional[torch.Tensor] = None) -> torch.Tensor:
