@@ -139,11 +139,20 @@ def pipeline_shards(model_id: str, n_layers: int, n_gpus: int, head_layer_equiv:
   ``head_layer_equiv`` = bytes of the LM head / bytes of one decoder layer.  With 0 the nodes
   are equal (the reference's view: 32 layers -> 8 x 4).  With the real value the last node's
   capacity is reduced so that (its layers + head) matches the other stages' layers."""
-  reserved = 0.0
-  if head_layer_equiv > 0 and n_gpus > 1:
-    per_stage = (n_layers + head_layer_equiv) / n_gpus          # balanced cost per stage, in layers
-    last_layers = max(1.0, per_stage - head_layer_equiv)
-    other_layers = (n_layers - last_layers) / (n_gpus - 1)
-    reserved = max(0.0, 1.0 - last_layers / other_layers)
-  parts = RingMemoryWeightedPartitioningStrategy().partition(box_topology(n_gpus, last_stage_reserved=reserved))
-  return map_partitions_to_shards(parts, n_layers, model_id)
+  def shards_for(reserved: float) -> List[Shard]:
+    parts = RingMemoryWeightedPartitioningStrategy().partition(box_topology(n_gpus, last_stage_reserved=reserved))
+    return map_partitions_to_shards(parts, n_layers, model_id)
+
+  if head_layer_equiv <= 0 or n_gpus <= 1:
+    return shards_for(0.0)
+  # the strategy rounds fractions to whole layers, so scan the last GPU's reserved share and keep
+  # the assignment whose slowest stage (layers + head on the last one) is cheapest
+  best, best_cost = None, None
+  for step in range(0, 91):
+    sh = shards_for(step / 100.0)
+    if len(sh) != n_gpus:
+      continue
+    cost = max(s.get_layer_count() + (head_layer_equiv if i == n_gpus - 1 else 0.0) for i, s in enumerate(sh))
+    if best_cost is None or cost < best_cost - 1e-9:
+      best, best_cost = sh, cost
+  return best if best is not None else shards_for(0.0)
