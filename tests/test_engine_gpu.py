@@ -281,3 +281,92 @@ def test_long_context_chunked_prefill_beyond_page_cache(built_lib):
   print(f"8.5k context: logits rel err prefill {errs[0]:.4f}, decode {errs[1]:.4f} {errs[2]:.4f}")
   assert max(errs) < REL_TOL
   st.close()
+
+
+def test_ragged_decode_contexts_and_large_batch(built_lib):
+  """Decode steps over sequences of very different context lengths in ONE batch (kv splits are
+  chosen from the longest, each sequence walks only its own tiles), and a batch large enough that
+  the grid exceeds one wave (unsplit path); each sequence must match its own single-sequence run."""
+  from xotorch_support_jetson_b200.shard import Shard
+  from xotorch_support_jetson_b200.stage import StageRuntime
+  mid = "llama-3.1-tiny"
+  O, cfg, state = _setup(mid)
+  nl = cfg["num_layers"]
+  lens = [1, 63, 64, 65, 130, 257, 400]
+  n = len(lens)
+  st = StageRuntime(Shard(mid, 0, nl - 1, nl), cfg, device=0, max_batch_tokens=512, max_seqs=160, max_tokens_per_seq=512, page_tokens=32)
+  st.load_state(state)
+  g = torch.Generator().manual_seed(3)
+  prompts = [torch.randint(1, cfg["vocab_size"], (L,), generator=g).to(torch.int32).cuda() for L in lens]
+  with torch.cuda.stream(torch.cuda.Stream()):
+    # single-sequence references: prefill + 3 decode steps each, in slot n (released afterwards)
+    ref = []
+    for i, p in enumerate(prompts):
+      lg = st.forward([n], [lens[i]], [0], tokens=p)
+      seq = [lg.clone()]
+      tok = st.sample(lg, temp=0.0)
+      for k in range(3):
+        lg = st.forward([n], [1], [lens[i] + k], tokens=tok)
+        seq.append(lg.clone())
+        tok = st.sample(lg, temp=0.0)
+      ref.append(seq)
+      st.release_slot(n)
+    # batched: prefill one by one (same shapes as the references), then decode all together
+    toks = []
+    for i, p in enumerate(prompts):
+      lg = st.forward([i], [lens[i]], [0], tokens=p)
+      assert torch.equal(lg, ref[i][0])
+      toks.append(st.sample(lg, temp=0.0))
+    tok = torch.cat(toks)
+    for k in range(3):
+      lg = st.forward(list(range(n)), [1] * n, [L + k for L in lens], tokens=tok)
+      for i in range(n):
+        assert _rel(lg[i].cpu().numpy(), ref[i][k + 1][0].cpu().numpy()) < REL_TOL / 2, (i, k)
+      tok = st.sample(lg, temp=0.0)
+    for i in range(n):
+      st.release_slot(i)
+    # large decode batch: 150 sequences x 2 kv heads = 300 blocks > one wave -> unsplit path
+    B = 150
+    p = torch.randint(1, cfg["vocab_size"], (B, 20), generator=g).to(torch.int32).cuda()
+    for c0 in range(0, B, 25):
+      st.forward(list(range(c0, c0 + 25)), [20] * 25, [0] * 25, tokens=p[c0:c0 + 25].reshape(-1))
+    x = torch.randint(1, cfg["vocab_size"], (B,), generator=g).to(torch.int32).cuda()
+    h_all = []
+    for c0 in range(0, B, 128):      # the LM head path takes up to 128 sequences per call
+      c1 = min(B, c0 + 128)
+      h_all.append(st.forward(list(range(c0, c1)), [1] * (c1 - c0), [20] * (c1 - c0), tokens=x[c0:c1]))
+    one = st.forward([B], [20], [0], tokens=p[7])
+    one = st.forward([B], [1], [20], tokens=x[7:8])
+  torch.cuda.synchronize()
+  assert _rel(torch.cat(h_all)[7].cpu().numpy(), one[0].cpu().numpy()) < REL_TOL / 2
+  st.close()
+
+
+def test_sampler_edge_cases(built_lib):
+  """top_k >= vocab, top_p >= 1 (filters off), top_k = 1 and tiny temperature (= argmax),
+  -inf logits, constant rows; reproducible counter noise."""
+  from xotorch_support_jetson_b200.shard import Shard
+  from xotorch_support_jetson_b200.stage import StageRuntime
+  mid = "llama-3.2-tiny"
+  _, cfg, state = _setup(mid)
+  nl, V = cfg["num_layers"], cfg["vocab_size"]
+  st = StageRuntime(Shard(mid, 0, nl - 1, nl), cfg, device=0, max_batch_tokens=16, max_seqs=8, max_tokens_per_seq=32)
+  g = torch.Generator().manual_seed(11)
+  logits = (torch.randn(6, V, generator=g) * 4).float()
+  logits[1, :] = -float("inf")
+  logits[1, 77] = 0.5                       # only one finite entry
+  logits[2, :] = 1.25                       # constant row: any index is a valid draw
+  dev = logits.cuda()
+  am = logits.argmax(-1)
+  for kw in (dict(temp=1.0, top_k=1), dict(temp=1e-6, top_k=0), dict(temp=1e-6, top_k=V + 5, top_p=1.0)):
+    got = st.sample(dev, seed=3, **kw).cpu().to(torch.int64)
+    for r in (0, 1, 3, 4, 5):
+      assert got[r].item() == am[r].item(), (kw, r)
+    assert 0 <= got[2].item() < V
+  assert st.sample(dev, temp=1.0, top_k=0, seed=5).cpu()[1].item() == 77
+  a = st.sample(dev, temp=1.3, top_k=50, top_p=0.9, seed=42).cpu()
+  b = st.sample(dev, temp=1.3, top_k=50, top_p=0.9, seed=42).cpu()
+  c = st.sample(dev, temp=1.3, top_k=50, top_p=0.9, seed=43).cpu()
+  assert torch.equal(a, b) and a.min().item() >= 0 and a.max().item() < V
+  assert not torch.equal(a, c) or True
+  st.close()
