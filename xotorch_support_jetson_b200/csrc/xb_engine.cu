@@ -580,8 +580,8 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
     XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
     LAUNCH_COUNT(e);
     if (gp->args.mode == XB_GEMM_SKINNY) {
-      dim3 grid(T, d.n_heads + 2 * d.n_kv_heads);
-      XB_TRY(launch_k(e, xb_qkv_finalize_kernel, grid, dim3(hd / 2), 0, st, 1, (const float*)e->gemm_out, gp->split,
+      const int qkv_items = (d.n_heads + 2 * d.n_kv_heads) * (d.rope_kind == 0 ? hd / 4 : hd / 8);
+      XB_TRY(launch_k(e, xb_qkv_finalize_kernel, dim3(T, (qkv_items + 255) / 256), dim3(256), 0, st, 1, (const float*)e->gemm_out, gp->split,
                       (long long)T * e->NQKV, w.bqkv, e->rope, e->q, w.k_pool, w.v_pool, m, d.n_heads, d.n_kv_heads, hd,
                       d.rope_kind));
     }
@@ -597,7 +597,7 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
     XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
     LAUNCH_COUNT(e);
     if (gp->args.mode == XB_GEMM_SKINNY) {
-      const long long n = (long long)T * I;
+      const long long n = (long long)T * (I / 4);
       XB_TRY(launch_k(e, xb_silu_mul_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, st, 1, (const float*)e->gemm_out,
                       gp->split, (long long)T * 2 * I, e->act, T, I));
     }

@@ -305,72 +305,99 @@ __global__ void __launch_bounds__(NT) xb_resid_send_kernel(const float* __restri
 }
 
 // ----------------------------------------------------------------------------- QKV finalize
-// One block per (token, head) over the fused [q | k | v] projection output.
-//   value = bf16(sum_splits(partial) + bias)        (nn.Linear rounding)
-//   (decode path; the prefill GEMM does the same work in its epilogue, xb_gemm.cuh epi_wide_qkv)
+// Decode path (the prefill GEMM does the same work in its epilogue, xb_gemm.cuh epi_wide_qkv).
+// One block per token over the fused [q | k | v] projection output, 4 consecutive elements per
+// work item (float4 reads of the split-K planes):
+//   value = bf16(sum_planes(partial) + bias)        (nn.Linear rounding)
 //   q,k heads: RoPE at the token's position, table = [pos][hd/2][cos,sin] fp32
 //     rope_kind 0: interleaved pairs (2i,2i+1), fp32 math, one rounding (Llama3ScaledRoPE /
 //                  RotaryPositionalEmbeddings as built at general_mha.py:35-40,58-63)
 //     rope_kind 1: half-split pairs (i,i+hd/2), every product and the sum rounded to bf16
 //                  (Qwen2RotaryPositionalEmbeddings, general_mha.py:47-51)
 //   q -> q_out[t][h*hd..]; k,v -> the paged cache (KVCache.update, llm_utils.py:320-345)
-__global__ void xb_qkv_finalize_kernel(const float* __restrict__ part, SplitInfo si, long long split_stride,
-                                       const bf16* __restrict__ bias,
-                                       const float* __restrict__ rope, bf16* __restrict__ q_out, bf16* __restrict__ k_pool,
-                                       bf16* __restrict__ v_pool, BatchMeta m, int H, int KV, int hd, int rope_kind) {
+__device__ __forceinline__ void qkv_load4(const float* __restrict__ part, const SplitInfo& si, long long split_stride,
+                                          long long base, int col, const bf16* __restrict__ bias, float* x) {
+  float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+  const int planes = xb_n_segments(si, col);
+  for (int s = 0; s < planes; ++s) {
+    const float4 p = *reinterpret_cast<const float4*>(part + s * split_stride + base + col);
+    a.x += p.x; a.y += p.y; a.z += p.z; a.w += p.w;
+  }
+  if (bias != nullptr) {
+    const uint2 bu = *reinterpret_cast<const uint2*>(bias + col);
+    const float2 b0 = bf2_to_f2(bu.x), b1 = bf2_to_f2(bu.y);
+    a.x += b0.x; a.y += b0.y; a.z += b1.x; a.w += b1.y;
+  }
+  x[0] = rbf(a.x); x[1] = rbf(a.y); x[2] = rbf(a.z); x[3] = rbf(a.w);
+}
+
+__global__ void __launch_bounds__(256) xb_qkv_finalize_kernel(const float* __restrict__ part, SplitInfo si, long long split_stride,
+                                                              const bf16* __restrict__ bias, const float* __restrict__ rope,
+                                                              bf16* __restrict__ q_out, bf16* __restrict__ k_pool,
+                                                              bf16* __restrict__ v_pool, BatchMeta m, int H, int KV, int hd,
+                                                              int rope_kind) {
   pdl_launch_dependents();
   pdl_wait();
   const int t = blockIdx.x;
-  const int head = blockIdx.y;              // [0,H) q heads, [H,H+KV) k heads, [H+KV,H+2KV) v heads
-  const int i = threadIdx.x;                // pair index, hd/2 threads
-  const int NQKV = (H + 2 * KV) * hd;
+  const int heads = H + 2 * KV;
   const int half = hd >> 1;
-  int e0, e1;
-  if (rope_kind == 0) { e0 = 2 * i; e1 = 2 * i + 1; } else { e0 = i; e1 = i + half; }
-  const long long base = (long long)t * NQKV + (long long)head * hd;
-  float x0, x1;
-  {
-    float a = 0.f, b = 0.f;
-    const int splits = xb_n_segments(si, head * hd + e0);   // e0 and e1 lie in the same 128-column tile
-    for (int s = 0; s < splits; ++s) {
-      a += part[s * split_stride + base + e0];
-      b += part[s * split_stride + base + e1];
-    }
-    if (bias != nullptr) {
-      a += bf2f(bias[head * hd + e0]);
-      b += bf2f(bias[head * hd + e1]);
-    }
-    x0 = rbf(a);
-    x1 = rbf(b);
-  }
+  const long long base = (long long)t * heads * hd;
   const int pos = m.tok_pos[t];
-  if (head < H + KV) {
-    const float2 cs = *reinterpret_cast<const float2*>(rope + ((long long)pos * half + i) * 2);
-    float o0, o1;
-    if (rope_kind == 0) {
-      o0 = rbf(__fsub_rn(__fmul_rn(x0, cs.x), __fmul_rn(x1, cs.y)));
-      o1 = rbf(__fadd_rn(__fmul_rn(x1, cs.x), __fmul_rn(x0, cs.y)));
+  const int slot = m.seq_slot[m.tok_seq[t]];
+  const int page = m.page_table[(long long)slot * m.max_pages + pos / m.page_tokens];
+  const int off = pos % m.page_tokens;
+  const float* rope_row = rope + (long long)pos * half * 2;
+  // work items per head: hd/4 (interleaved: 4 consecutive elements = 2 pairs) or hd/8 (half-split:
+  // 4 elements of the low half + their 4 partners of the high half)
+  const int iph = rope_kind == 0 ? hd / 4 : hd / 8;
+  // grid = (tokens, ceil(items / 256)): one work item per thread, so a 1-token decode step still spreads out
+  const int it = blockIdx.y * blockDim.x + threadIdx.x;
+  if (it < heads * iph) {
+    const int head = it / iph, c = (it % iph) * 4;
+    bf16* dst;
+    if (head < H) {
+      dst = q_out + (long long)t * H * hd + (long long)head * hd;
     } else {
-      const float c = rbf(cs.x), s = rbf(cs.y);
-      o0 = rbf(__fadd_rn(rbf(__fmul_rn(x0, c)), rbf(__fmul_rn(-x1, s))));
-      o1 = rbf(__fadd_rn(rbf(__fmul_rn(x1, c)), rbf(__fmul_rn(x0, s))));
+      const int kvh = (head - H) % KV;
+      bf16* pool = (head < H + KV) ? k_pool : v_pool;
+      dst = pool + (((long long)page * KV + kvh) * m.page_tokens + off) * hd;
     }
-    x0 = o0;
-    x1 = o1;
-  }
-  if (head < H) {
-    bf16* dst = q_out + (long long)t * H * hd + (long long)head * hd;
-    dst[e0] = f2bf(x0);
-    dst[e1] = f2bf(x1);
-  } else {
-    const int slot = m.seq_slot[m.tok_seq[t]];
-    const int page = m.page_table[(long long)slot * m.max_pages + pos / m.page_tokens];
-    const int off = pos % m.page_tokens;
-    const int kvh = (head - H) % KV;
-    bf16* pool = (head < H + KV) ? k_pool : v_pool;
-    bf16* dst = pool + (((long long)page * KV + kvh) * m.page_tokens + off) * hd;
-    dst[e0] = f2bf(x0);
-    dst[e1] = f2bf(x1);
+    float x[4];
+    qkv_load4(part, si, split_stride, base, head * hd + c, bias, x);
+    if (rope_kind == 0) {
+      if (head < H + KV) {
+        const float4 cs = *reinterpret_cast<const float4*>(rope_row + c);   // (cos,sin) of pairs c/2, c/2+1
+        const float a0 = x[0], b0 = x[1], a1 = x[2], b1 = x[3];
+        x[0] = __fsub_rn(__fmul_rn(a0, cs.x), __fmul_rn(b0, cs.y));
+        x[1] = __fadd_rn(__fmul_rn(b0, cs.x), __fmul_rn(a0, cs.y));
+        x[2] = __fsub_rn(__fmul_rn(a1, cs.z), __fmul_rn(b1, cs.w));
+        x[3] = __fadd_rn(__fmul_rn(b1, cs.z), __fmul_rn(a1, cs.w));
+      }
+      uint2 o;
+      o.x = f2_to_bf2(x[0], x[1]);
+      o.y = f2_to_bf2(x[2], x[3]);
+      *reinterpret_cast<uint2*>(dst + c) = o;
+    } else {
+      float y[4];
+      qkv_load4(part, si, split_stride, base, head * hd + half + c, bias, y);
+      if (head < H + KV) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 cs = *reinterpret_cast<const float2*>(rope_row + (c + j) * 2);
+          const float cc = rbf(cs.x), ss = rbf(cs.y);
+          const float a = x[j], b = y[j];
+          x[j] = __fadd_rn(rbf(__fmul_rn(a, cc)), rbf(__fmul_rn(-b, ss)));
+          y[j] = __fadd_rn(rbf(__fmul_rn(b, cc)), rbf(__fmul_rn(a, ss)));
+        }
+      }
+      uint2 o;
+      o.x = f2_to_bf2(x[0], x[1]);
+      o.y = f2_to_bf2(x[2], x[3]);
+      *reinterpret_cast<uint2*>(dst + c) = o;
+      o.x = f2_to_bf2(y[0], y[1]);
+      o.y = f2_to_bf2(y[2], y[3]);
+      *reinterpret_cast<uint2*>(dst + half + c) = o;
+    }
   }
 }
 
@@ -378,27 +405,34 @@ __global__ void xb_qkv_finalize_kernel(const float* __restrict__ part, SplitInfo
 // FeedForward (llm_utils.py:513-522): w2(silu(w1 x) * w3 x); silu output and the product
 // are separate bf16 ops in the reference.  Input = split-K partial planes of the fused gate/up
 // projection (decode path; the prefill GEMM does this in its epilogue, xb_gemm.cuh epi_wide_silu).
-__global__ void xb_silu_mul_kernel(const float* __restrict__ part, SplitInfo si, long long split_stride,
-                                   bf16* __restrict__ act, int T, int I) {
+// Fused gate/up columns are interleaved in 16-feature blocks; 4 consecutive features per thread.
+__global__ void __launch_bounds__(256) xb_silu_mul_kernel(const float* __restrict__ part, SplitInfo si, long long split_stride,
+                                                          bf16* __restrict__ act, int T, int I) {
   pdl_launch_dependents();
   pdl_wait();
+  const int i4 = I >> 2;
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= (long long)T * I) return;
-  const int t = (int)(idx / I), i = (int)(idx % I);
-  // fused gate/up columns are interleaved in 16-feature blocks (see epi_wide_silu)
-  const int cg = (i >> 4) * 32 + (i & 15), cu = cg + 16;
-  const long long og = (long long)t * 2 * I + cg, ou = (long long)t * 2 * I + cu;
-  float g, u;
-  {
-    g = 0.f; u = 0.f;
-    const int sg_n = xb_n_segments(si, cg), su_n = xb_n_segments(si, cu);
-    for (int s = 0; s < sg_n; ++s) g += part[s * split_stride + og];
-    for (int s = 0; s < su_n; ++s) u += part[s * split_stride + ou];
-    g = rbf(g);
-    u = rbf(u);
+  if (idx >= (long long)T * i4) return;
+  const int t = (int)(idx / i4), i = (int)(idx % i4) * 4;
+  const int cg = (i >> 4) * 32 + (i & 15), cu = cg + 16;     // same 128-column tile: (i>>4)*32 is a multiple of 32
+  const long long row = (long long)t * 2 * I;
+  const int planes = xb_n_segments(si, cg);                  // cg and cu lie in one 128-column tile
+  float4 g = make_float4(0.f, 0.f, 0.f, 0.f), u = g;
+  for (int s = 0; s < planes; ++s) {
+    const float4 pg = *reinterpret_cast<const float4*>(part + s * split_stride + row + cg);
+    const float4 pu = *reinterpret_cast<const float4*>(part + s * split_stride + row + cu);
+    g.x += pg.x; g.y += pg.y; g.z += pg.z; g.w += pg.w;
+    u.x += pu.x; u.y += pu.y; u.z += pu.z; u.w += pu.w;
   }
-  const float sg = rbf(g / (1.0f + expf(-g)));
-  act[idx] = f2bf(sg * u);
+  const float gv[4] = {rbf(g.x), rbf(g.y), rbf(g.z), rbf(g.w)};
+  const float uv[4] = {rbf(u.x), rbf(u.y), rbf(u.z), rbf(u.w)};
+  float o[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) o[j] = rbf(gv[j] / (1.0f + expf(-gv[j]))) * uv[j];
+  uint2 w;
+  w.x = f2_to_bf2(o[0], o[1]);
+  w.y = f2_to_bf2(o[2], o[3]);
+  *reinterpret_cast<uint2*>(act + (long long)t * I + i) = w;
 }
 
 // ----------------------------------------------------------------------------- misc
