@@ -18,32 +18,32 @@ HF_PRECISION_STR_TO_DTYPE = {
 }
 
 
+# HF config.json key -> engine key, for the fields that are copied as they are
+_DIRECT_FIELDS = (
+  ("hidden_size", "embed_dim"), ("num_attention_heads", "num_heads"), ("num_key_value_heads", "num_kv_heads"),
+  ("max_position_embeddings", "max_seq_len"), ("intermediate_size", "intermediate_dim"), ("rms_norm_eps", "norm_eps"),
+  ("rope_theta", "rope_base"), ("vocab_size", "vocab_size"), ("num_hidden_layers", "num_layers"),
+)
+# optional HF keys with the defaults the reference applies
+_OPTIONAL_FIELDS = (("attention_dropout", "attn_dropout", 0.0), ("attention_bias", "attn_bias", False), ("hidden_act", "hidden_act", "silu"))
+
+
 def load_model_config(model_config_path: Path) -> dict:
-  with open(model_config_path, "r") as f:
-    base_config = json.load(f)
-  model_config = {
-    "rope_scaling": base_config.get("rope_scaling"),
-    "embed_dim": base_config["hidden_size"],
-    "num_heads": base_config["num_attention_heads"],
-    "head_dim": base_config.get("head_dim", base_config["hidden_size"] // base_config["num_attention_heads"]),
-    "num_kv_heads": base_config["num_key_value_heads"],
-    "max_seq_len": base_config["max_position_embeddings"],
-    "intermediate_dim": base_config["intermediate_size"],
-    "attn_dropout": base_config.get("attention_dropout", 0.0),
-    "norm_eps": base_config["rms_norm_eps"],
-    "rope_base": base_config["rope_theta"],
-    "vocab_size": base_config["vocab_size"],
-    "num_layers": base_config["num_hidden_layers"],
-    "attn_bias": base_config.get("attention_bias", False),
-    "hidden_act": base_config.get("hidden_act", "silu"),
-    "torch_dtype": HF_PRECISION_STR_TO_DTYPE.get(base_config.get("torch_dtype", "bfloat16"), torch.bfloat16),
-  }
-  if model_config.get("rope_scaling", None) is not None:
-    model_config["rope_scaling_factor"] = model_config["rope_scaling"].get("rope_factor", 32)
-  use_org_seq = bool(os.getenv("TORCH_USE_ORG_SEQ", "False").lower() == "true")
-  if use_org_seq and model_config.get("rope_scaling", None) is not None:
-    model_config["max_seq_len"] = model_config["rope_scaling"]["original_max_position_embeddings"]
-  return model_config
+  """Read an HF ``config.json`` into the flat dict the engine works with."""
+  hf = json.loads(Path(model_config_path).read_text())
+  cfg = {ours: hf[theirs] for theirs, ours in _DIRECT_FIELDS}
+  cfg.update({ours: hf.get(theirs, default) for theirs, ours, default in _OPTIONAL_FIELDS})
+  cfg["head_dim"] = hf.get("head_dim", hf["hidden_size"] // hf["num_attention_heads"])
+  cfg["torch_dtype"] = HF_PRECISION_STR_TO_DTYPE.get(hf.get("torch_dtype", "bfloat16"), torch.bfloat16)
+  scaling = hf.get("rope_scaling")
+  cfg["rope_scaling"] = scaling
+  if scaling is not None:
+    # reference quirk kept on purpose: the factor is looked up under "rope_factor", a key HF configs
+    # do not carry, so Llama-3.x always runs with 32 (llm_utils.py:68-69; SURVEY 8a defect 2)
+    cfg["rope_scaling_factor"] = scaling.get("rope_factor", 32)
+    if os.getenv("TORCH_USE_ORG_SEQ", "False").lower() == "true":
+      cfg["max_seq_len"] = scaling["original_max_position_embeddings"]
+  return cfg
 
 
 def model_family(model_id: str) -> str:

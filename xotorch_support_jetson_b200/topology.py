@@ -89,30 +89,39 @@ class Partition:
 
 
 class RingMemoryWeightedPartitioningStrategy:
+  """Same rule as the reference's strategy
+  (``xotorch/topology/ring_memory_weighted_partitioning_strategy.py:7-18``): order the nodes by
+  (memory, node id) descending and give each a slice of [0, 1) proportional to its memory, the
+  running boundary rounded to 5 decimals."""
+
   def partition(self, topology: Topology) -> List[Partition]:
-    nodes = list(topology.all_nodes())
-    nodes.sort(key=lambda x: (x[1].memory, x[0]), reverse=True)
-    total_memory = sum(node[1].memory for node in nodes)
-    partitions = []
-    start = 0
-    for node in nodes:
-      end = round(start + (node[1].memory / total_memory), 5)
-      partitions.append(Partition(node[0], start, end))
-      start = end
-    return partitions
+    ring = sorted(topology.all_nodes(), key=lambda kv: (kv[1].memory, kv[0]), reverse=True)
+    total = float(sum(caps.memory for _, caps in ring))
+    out: List[Partition] = []
+    lo = 0
+    for node_id, caps in ring:
+      hi = round(lo + caps.memory / total, 5)
+      out.append(Partition(node_id, lo, hi))
+      lo = hi
+    return out
 
 
 def map_partitions_to_shards(partitions: List[Partition], num_layers: int, model_id: str) -> List[Shard]:
-  shards = []
-  for i, partition in enumerate(partitions):
-    start_layer = int(partition.start * num_layers)
-    end_layer = int(partition.end * num_layers) - 1
-    if i == len(partitions) - 1:
-      end_layer = num_layers - 1
-    if start_layer <= end_layer:
-      shards.append(Shard(model_id, start_layer, end_layer, num_layers))
-  if shards and shards[-1].end_layer < num_layers - 1:
-    shards[-1] = Shard(model_id, shards[-1].start_layer, num_layers - 1, num_layers)
+  """Fractions of [0, 1) -> inclusive layer ranges, with the reference's conventions
+  (``xotorch/topology/partitioning_strategy.py:23-42``): boundaries are truncated
+  (``int(x * L)``), the last partition always runs to the final layer, partitions that end up
+  empty are dropped, and whatever comes last is stretched to cover the model."""
+  n_parts = len(partitions)
+  shards: List[Shard] = []
+  for idx, part in enumerate(partitions):
+    first = int(part.start * num_layers)
+    last = num_layers - 1 if idx == n_parts - 1 else int(part.end * num_layers) - 1
+    if last >= first:
+      shards.append(Shard(model_id, first, last, num_layers))
+  if shards and shards[-1].end_layer != num_layers - 1:
+    tail = shards[-1]
+    if tail.end_layer < num_layers - 1:
+      shards[-1] = Shard(model_id, tail.start_layer, num_layers - 1, num_layers)
   return shards
 
 
