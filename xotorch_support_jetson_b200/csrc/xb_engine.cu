@@ -498,21 +498,18 @@ static int launch_attn(xb_engine* e, const LayerW& w, const BatchMeta& m, int T,
   return xb_fail(1, "GQA group size %d not supported (1..8)", e->d.n_heads / e->d.n_kv_heads);
 }
 
-template <int CL, int NT, int VPT>
-static int launch_resid_norm_cluster(xb_engine* e, const GemmPlan* gp, int T, const bf16* nw, cudaStream_t st) {
-  const xb_model_desc& d = e->d;
-  return launch_k(e, xb_resid_norm_cluster_kernel<CL, NT, VPT>, dim3(CL, T, 1), dim3(NT), 0, st, CL, (const float*)e->gemm_out,
-                  gp->split, (long long)T * d.dim, e->h, nw, e->hn, d.dim, d.norm_eps, d.rmsnorm_two_round);
-}
-
 static int launch_resid_norm(xb_engine* e, const GemmPlan* gp, int T, const bf16* nw, cudaStream_t st) {
   const xb_model_desc& d = e->d;
   const size_t smem = (size_t)d.dim * sizeof(float);
   if (gp->args.mode == XB_GEMM_SKINNY) {
-    // decode-sized batches: one 8-block cluster per row (columns split over 8 SMs)
-    if (d.dim % 32 == 0 && d.dim / 8 <= 128 * 4 * 2)
-      return d.dim / 8 <= 128 * 4 ? launch_resid_norm_cluster<8, 128, 1>(e, gp, T, nw, st)
-                                  : launch_resid_norm_cluster<8, 128, 2>(e, gp, T, nw, st);
+    // decode-sized batches: one 1024-thread block per row
+    if (d.dim % 4 == 0 && d.dim <= 1024 * 4 * 2) {
+      if (d.dim <= 1024 * 4)
+        return launch_k(e, xb_resid_norm_row_kernel<1024, 1>, dim3(T), dim3(1024), 0, st, 1, (const float*)e->gemm_out, gp->split,
+                        (long long)T * d.dim, e->h, nw, e->hn, d.dim, d.norm_eps, d.rmsnorm_two_round);
+      return launch_k(e, xb_resid_norm_row_kernel<1024, 2>, dim3(T), dim3(1024), 0, st, 1, (const float*)e->gemm_out, gp->split,
+                      (long long)T * d.dim, e->h, nw, e->hn, d.dim, d.norm_eps, d.rmsnorm_two_round);
+    }
     XB_TRY(launch_k(e, xb_resid_norm_kernel<256, 0>, dim3(T), dim3(256), smem, st, 1, (const float*)e->gemm_out, gp->split, (long long)T * d.dim,
                                                         nullptr, e->h, nw, e->hn, d.dim, d.norm_eps, d.rmsnorm_two_round));
   } else {
@@ -831,22 +828,36 @@ extern "C" int xb_bench_linears(xb_engine* e, int T, int iters, int* n_launches,
   XB_CUDA(cudaSetDevice(e->device));
   const bool last = d.end_layer == d.n_layers - 1;
   const int D = d.dim, I = d.inter_dim;
+  // XB_BENCH_SITE=0..4 restricts the pass to one site (qkv, o, gate/up, down, head) for per-site numbers
+  const char* sv = getenv("XB_BENCH_SITE");
+  const int only = sv != nullptr ? atoi(sv) : -1;
   int n = 0;
   for (int it = 0; it < iters; ++it) {
     for (int l = 0; l < e->nl; ++l) {
       const LayerW& w = e->L[l];
       const GemmPlan* gp;
-      XB_TRY(get_plan(e, SITE_QKV, l, e->hn, D, w.wqkv, T, e->NQKV, D, e->gemm_out, e->NQKV, w.bqkv, 0, &gp));
-      XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
-      XB_TRY(get_plan(e, SITE_O, l, e->attn, e->NQ, w.wo, T, D, e->NQ, e->gemm_out, D, nullptr, 0, &gp));
-      XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
-      XB_TRY(get_plan(e, SITE_GU, l, e->hn, D, w.wgu, T, 2 * I, D, e->gemm_out, 2 * I, nullptr, 0, &gp));
-      XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
-      XB_TRY(get_plan(e, SITE_DOWN, l, e->act, I, w.wdown, T, D, I, e->gemm_out, D, nullptr, 0, &gp));
-      XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
-      n += 4;
+      if (only < 0 || only == SITE_QKV) {
+        XB_TRY(get_plan(e, SITE_QKV, l, e->hn, D, w.wqkv, T, e->NQKV, D, e->gemm_out, e->NQKV, w.bqkv, 0, &gp));
+        XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
+        ++n;
+      }
+      if (only < 0 || only == SITE_O) {
+        XB_TRY(get_plan(e, SITE_O, l, e->attn, e->NQ, w.wo, T, D, e->NQ, e->gemm_out, D, nullptr, 0, &gp));
+        XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
+        ++n;
+      }
+      if (only < 0 || only == SITE_GU) {
+        XB_TRY(get_plan(e, SITE_GU, l, e->hn, D, w.wgu, T, 2 * I, D, e->gemm_out, 2 * I, nullptr, 0, &gp));
+        XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
+        ++n;
+      }
+      if (only < 0 || only == SITE_DOWN) {
+        XB_TRY(get_plan(e, SITE_DOWN, l, e->act, I, w.wdown, T, D, I, e->gemm_out, D, nullptr, 0, &gp));
+        XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
+        ++n;
+      }
     }
-    if (last && T <= d.max_seqs && T <= 128) {
+    if ((only < 0 || only == SITE_HEAD) && last && T <= d.max_seqs && T <= 128) {
       const bf16* head = e->lm_head;
       const GemmPlan* gp;
       XB_TRY(get_plan(e, SITE_HEAD, 0, e->last_rows, D, head, T, d.vocab, D, e->logits, d.vocab, nullptr, 1, &gp));

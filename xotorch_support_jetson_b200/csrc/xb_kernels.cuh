@@ -127,37 +127,39 @@ __global__ void __launch_bounds__(NT) xb_resid_norm_kernel(const float* __restri
   }
 }
 
-// Small-T variant: one CLUSTER of CL blocks per token row, each block owning D/CL columns, so
-// a decode step (T = 1..128 rows) spreads over CL*T SMs instead of T.  The row's sum of
-// squares is exchanged through distributed shared memory.  Same arithmetic and rounding
-// points as xb_resid_norm_kernel<., 0>; the split partials are summed in split order.
-template <int CL, int NT, int VPT>
-__global__ void __launch_bounds__(NT) xb_resid_norm_cluster_kernel(const float* __restrict__ part, SplitInfo si,
-                                                                   long long split_stride, bf16* __restrict__ h,
-                                                                   const bf16* __restrict__ nw, bf16* __restrict__ hn,
-                                                                   int D, float eps, int two_round) {
+// Decode variant: one 1024-thread block per token row, 4 consecutive columns per thread (float4
+// reads of the split-K planes, all planes' loads issued before the adds), row sum of squares by
+// shuffle + one shared-memory round.  Same arithmetic and rounding points as
+// xb_resid_norm_kernel<., 0>; planes are summed in plane order.  (An 8-block cluster per row with a
+// DSMEM exchange measured 5.7-6.0 us per launch at T <= 32: cluster scheduling and the cluster
+// barrier cost more than the extra SMs bring for 100 KB of input.)
+template <int NT, int VPT>
+__global__ void __launch_bounds__(NT) xb_resid_norm_row_kernel(const float* __restrict__ part, SplitInfo si,
+                                                               long long split_stride, bf16* __restrict__ h,
+                                                               const bf16* __restrict__ nw, bf16* __restrict__ hn, int D,
+                                                               float eps, int two_round) {
   pdl_launch_dependents();
   pdl_wait();
   __shared__ float red[32];
-  __shared__ float cl_part[CL];
-  const int t = blockIdx.y;
-  uint32_t rank;
-  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
-  const int cols = D / CL;                      // columns of this block (multiple of 4)
-  const int c0 = rank * cols;
+  const int t = blockIdx.x;
   float v[VPT][4];
   float ss = 0.f;
 #pragma unroll
   for (int it = 0; it < VPT; ++it) {
     const int c = (it * NT + threadIdx.x) * 4;
     v[it][0] = v[it][1] = v[it][2] = v[it][3] = 0.f;
-    if (c < cols) {
-      const long long o = (long long)t * D + c0 + c;
+    if (c < D) {
+      const long long o = (long long)t * D + c;
+      const int planes = xb_n_segments(si, c);
       float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-      const int splits = xb_n_segments(si, c0 + c);
-      for (int s = 0; s < splits; ++s) {
-        const float4 p = *reinterpret_cast<const float4*>(part + s * split_stride + o);
-        a.x += p.x; a.y += p.y; a.z += p.z; a.w += p.w;
+      for (int s0 = 0; s0 < planes; s0 += 4) {
+        float4 p[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          p[u] = (s0 + u < planes) ? *reinterpret_cast<const float4*>(part + (s0 + u) * split_stride + o)
+                                   : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { a.x += p[u].x; a.y += p[u].y; a.z += p[u].z; a.w += p[u].w; }
       }
       const uint2 hu = *reinterpret_cast<const uint2*>(h + o);
       const float2 h0 = bf2_to_f2(hu.x), h1 = bf2_to_f2(hu.y);
@@ -172,32 +174,19 @@ __global__ void __launch_bounds__(NT) xb_resid_norm_cluster_kernel(const float* 
       ss += v[it][0] * v[it][0] + v[it][1] * v[it][1] + v[it][2] * v[it][2] + v[it][3] * v[it][3];
     }
   }
-  if (nw == nullptr) return;   // uniform across the cluster
+  if (nw == nullptr) return;
   ss = block_sum<NT>(ss, red);
-  // publish this block's partial to every block of the cluster (DSMEM store), then cluster barrier
-  if (threadIdx.x < CL) {
-    uint32_t local = smem_u32(&cl_part[rank]);
-    uint32_t remote;
-    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"((uint32_t)threadIdx.x));
-    asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote), "f"(ss) : "memory");
-  }
-  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-  float tot = 0.f;
-#pragma unroll
-  for (int i = 0; i < CL; ++i) tot += cl_part[i];
-  const float inv = 1.0f / sqrtf(tot / (float)D + eps);
+  const float inv = 1.0f / sqrtf(ss / (float)D + eps);
 #pragma unroll
   for (int it = 0; it < VPT; ++it) {
     const int c = (it * NT + threadIdx.x) * 4;
-    if (c < cols) {
-      const long long o = (long long)t * D + c0 + c;
-      const uint2 wu = *reinterpret_cast<const uint2*>(nw + c0 + c);
+    if (c < D) {
+      const uint2 wu = *reinterpret_cast<const uint2*>(nw + c);
       const float2 w0 = bf2_to_f2(wu.x), w1 = bf2_to_f2(wu.y);
       uint2 r;
       r.x = f2_to_bf2(rms_apply(v[it][0], inv, w0.x, two_round), rms_apply(v[it][1], inv, w0.y, two_round));
       r.y = f2_to_bf2(rms_apply(v[it][2], inv, w1.x, two_round), rms_apply(v[it][3], inv, w1.y, two_round));
-      *reinterpret_cast<uint2*>(hn + o) = r;
+      *reinterpret_cast<uint2*>(hn + (long long)t * D + c) = r;
     }
   }
 }
