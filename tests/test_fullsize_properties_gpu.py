@@ -1,0 +1,118 @@
+"""Size-independent properties at BASELINE.json's full size (Llama-3.1-8B bf16, 2048-token prompt),
+where the CPU oracle is too slow to be the checker:
+  * a 2-shard split (layers 0-15 | 16-31, hidden state handed over in bf16) gives EXACTLY the
+    full-shard logits and greedy tokens (the reference's contract,
+    xotorch/inference/test_inference_engine.py:11,43-44);
+  * chunked prefill (2 x 1024) equals the one-shot prefill within the stated tolerance;
+  * a cached decode step and the last position of a prefill over the extended prompt are both as
+    close to an fp32 evaluation of the same weights as the bf16 oracle is (the oracle, in fp32 and
+    in bf16, is run on the GPU through torch here purely as the checker: on the CPU a 2048-token
+    8B prefill takes tens of minutes)."""
+import json
+import tempfile
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+REL_TOL = 0.04
+
+
+def _rel(a, b):
+  return float((a.float() - b.float()).abs().max() / b.float().abs().max())
+
+
+def test_llama31_8b_properties(built_lib):
+  from xotorch_support_jetson_b200 import model_config as mc
+  from xotorch_support_jetson_b200.models import model_cards
+  from xotorch_support_jetson_b200.pipeline import gpu_random_getter
+  from xotorch_support_jetson_b200.shard import Shard
+  from xotorch_support_jetson_b200.stage import StageRuntime
+  if torch.cuda.get_device_properties(0).total_memory < 60e9:
+    pytest.skip("needs ~40 GB of HBM")
+  mid = "llama-3.1-8b"
+  hf = model_cards[mid]["hf_config"]
+  with tempfile.TemporaryDirectory() as td:
+    (Path(td) / "config.json").write_text(json.dumps(hf))
+    cfg = mc.load_model_config(Path(td) / "config.json")
+  dev = torch.device("cuda", 0)
+  L, nl = 2048, 32
+  kw = dict(device=0, max_batch_tokens=4096, max_seqs=3, max_tokens_per_seq=L + 64)
+  full = StageRuntime(Shard(mid, 0, nl - 1, nl), cfg, **kw)
+  s1 = StageRuntime(Shard(mid, 0, 15, nl), cfg, **kw)
+  s2 = StageRuntime(Shard(mid, 16, nl - 1, nl), cfg, **kw)
+  for st in (full, s1, s2):
+    st.load_hf_tensors(*gpu_random_getter(hf, 0, 0.02, dev))
+  g = torch.Generator(device=dev).manual_seed(4321)
+  prompt = torch.randint(1, cfg["vocab_size"], (L + 1,), generator=g, device=dev, dtype=torch.int32)
+  with torch.cuda.stream(torch.cuda.Stream()):
+    # one-shot prefill, full shard vs 2-shard ring
+    lg_full = full.forward([0], [L], [0], tokens=prompt[:L])
+    h = s1.forward([0], [L], [0], tokens=prompt[:L])
+    lg_ring = s2.forward([0], [L], [0], hidden=h)
+    assert torch.equal(lg_full, lg_ring), "2-shard split differs from the full shard"
+    # chunked prefill in slot 1
+    full.forward([1], [1024], [0], tokens=prompt[:1024])
+    lg_chunk = full.forward([1], [1024], [1024], tokens=prompt[1024:L])
+    e_chunk = _rel(lg_chunk, lg_full)
+    # decode step at position L vs prefill of L+1 tokens (slot 2)
+    lg_dec = full.forward([0], [1], [L], tokens=prompt[L:L + 1])
+    lg_ext = full.forward([2], [L + 1], [0], tokens=prompt)
+    e_dec = _rel(lg_dec, lg_ext)
+    # greedy: full shard vs ring, 8 tokens (decode path: CUDA-graph replays on both)
+    full.release_slot(1)
+    full.release_slot(2)
+    full.release_slot(0)
+    s1.release_slot(0)
+    s2.release_slot(0)
+    lg_a = full.forward([0], [L], [0], tokens=prompt[:L])
+    lg_b = s2.forward([0], [L], [0], hidden=s1.forward([0], [L], [0], tokens=prompt[:L]))
+    ta, tb = [], []
+    for k in range(8):
+      xa = full.sample(lg_a, temp=0.0)
+      xb = s2.sample(lg_b, temp=0.0)
+      ta.append(int(xa.item()))
+      tb.append(int(xb.item()))
+      lg_a = full.forward([0], [1], [L + k], tokens=xa)
+      lg_b = s2.forward([0], [1], [L + k], hidden=s1.forward([0], [1], [L + k], tokens=xb))
+  torch.cuda.synchronize()
+  print(f"\n[8B properties] chunked-vs-one-shot prefill rel err {e_chunk:.4f}; decode-vs-prefill rel err {e_dec:.4f}; "
+        f"tokens full {ta} ring {tb}")
+  assert ta == tb
+  assert torch.isfinite(lg_full).all() and e_chunk < REL_TOL / 2 and e_dec < 2 * REL_TOL
+  for st in (full, s1, s2):
+    st.close()
+  del full, s1, s2
+  torch.cuda.empty_cache()
+
+  # ---- the oracle at full size (fp32 = truth, bf16 = the reference's own precision)
+  import sys
+  sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+  from oracle import torch_oracle as O
+  from xotorch_support_jetson_b200.synth import hf_param_shapes
+  torch.backends.cuda.matmul.allow_bf16_reduced_precision_reduction = False
+  torch.backends.cuda.matmul.allow_tf32 = False
+  get, _ = gpu_random_getter(hf, 0, 0.02, dev)
+  state = {n: get(n) for n in hf_param_shapes(hf)}
+  ocfg = O.model_config_from_hf(hf)
+  cpu_prompt = prompt.cpu().long().reshape(1, -1)
+
+  def last_logits(dtype, opts, n_tok):
+    m = O.OracleShardModel(ocfg, mid, 0, nl - 1, state, opts, dtype=dtype, device="cuda")
+    _, lg, _ = O.greedy_generate([m], cpu_prompt[:, :n_tok], 1, collect_logits=True)
+    return torch.from_numpy(np.asarray(lg[0][0], dtype=np.float32))
+
+  o32 = O.OracleOptions(rope_table_dtype="fp32")
+  truth_L, truth_L1 = last_logits(torch.float32, o32, L), last_logits(torch.float32, o32, L + 1)
+  ref_L, ref_L1 = last_logits(torch.bfloat16, O.OracleOptions(), L), last_logits(torch.bfloat16, O.OracleOptions(), L + 1)
+  pre, dec, ext = lg_full.float().cpu()[0], lg_dec.float().cpu()[0], lg_ext.float().cpu()[0]
+  e = {"prefill": _rel(pre, truth_L), "decode": _rel(dec, truth_L1), "prefill+1": _rel(ext, truth_L1),
+       "oracle bf16 L": _rel(ref_L, truth_L), "oracle bf16 L+1": _rel(ref_L1, truth_L1),
+       "prefill vs oracle bf16": _rel(pre, ref_L), "decode vs oracle bf16": _rel(dec, ref_L1)}
+  print("[8B vs oracle] rel err to the fp32 evaluation: " + "; ".join(f"{k} {v:.4f}" for k, v in e.items()))
+  worst_ref = max(e["oracle bf16 L"], e["oracle bf16 L+1"])
+  assert e["prefill"] < 1.5 * worst_ref + 0.005
+  assert e["decode"] < 1.5 * worst_ref + 0.005
+  assert e["prefill+1"] < 1.5 * worst_ref + 0.005
