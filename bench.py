@@ -425,9 +425,26 @@ def e2e_engine_api(runner, cfg, prompt, K, W):
   dt = asyncio.run(go())
   V = cfg["vocab_size"]
   eng.end_request("bench")
+
+  # the same loop kept on the device (generate(): SURVEY 8f.1); rate from the arrival times of the
+  # ids at the host callback, first W steps (and the prefill) excluded
+  stamps = []
+
+  async def go_loop():
+    await eng.generate("bench", runner.shard, toks, max_generate_tokens=W + K + 1, temp=0.0, eos_token_id=-1,
+                       on_token=lambda rid, ids, fin: stamps.append(time.perf_counter()))
+    await asyncio.sleep(0)
+
+  asyncio.run(go_loop())
+  eng.end_request("bench")
+  loop_rate = B * K / (stamps[W + K] - stamps[W]) if len(stamps) > W + K else None
   return {"value": B * K / dt, "unit": "tok/s", "h2d_bytes_per_step": B * 4, "d2h_bytes_per_step": B * V * 4 + B * 4,
           "api": "B200ShardInferenceEngine.infer_tensor(np ids) -> np fp32 logits [B,V] (pinned staging); .sample(that array) -> np ids "
-                 "(reference plugin API, host buffers; the logits array handed back to sample() is recognised and not re-uploaded)"}
+                 "(reference plugin API, host buffers; the logits array handed back to sample() is recognised and not re-uploaded; "
+                 "sample() enqueues the next decode step on the ids it drew, infer_tensor() with those ids collects it)",
+          "device_loop": {"value": loop_rate, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": B * 4,
+                          "api": "B200ShardInferenceEngine.generate(np prompt ids, on_token=cb): sample->forward chained on the "
+                                 "device, ids streamed to a pinned table, reference-semantics sampler (top-k 35, q noise) every step"}}
 
 
 def main():

@@ -150,3 +150,105 @@ def test_native_error_behaviour_and_edge_cases(built_lib):
   torch.cuda.synchronize()
   assert torch.equal(c, b)
   st.close()
+
+
+def test_next_step_speculation_is_invisible(built_lib, tmp_path):
+  """sample() enqueues the next decode forward on the ids it just drew (b200_engine.py module
+  docstring).  Logits, ids and states must be bit-identical with it on and off: when the caller
+  feeds the sampled ids back (hit), when it feeds something else (miss: the real forward
+  overwrites the speculated KV entry), when it samples twice, and with two requests interleaved."""
+  from xotorch_support_jetson_b200.shard import Shard
+  mid, nl = "llama-3.2-tiny", 4
+  sh = Shard(mid, 0, nl - 1, nl)
+  rs = np.random.RandomState(5)
+  pa, pb = rs.randint(3, 200, (2, 21)).astype(np.int64), rs.randint(3, 200, (1, 9)).astype(np.int64)
+
+  async def script(eng):
+    rec = []
+    la, sa = await eng.infer_tensor("a", sh, pa, None)
+    lb, sb = await eng.infer_tensor("b", sh, pb, None)
+    rec += [la.copy(), lb.copy()]
+    ta = await eng.sample(la, temp=0.0)            # la is no longer the engine's last result: uploaded, no speculation
+    for step in range(6):
+      la, sa = await eng.infer_tensor("a", sh, ta, sa)
+      rec.append(la.copy())
+      ta = await eng.sample(la, temp=0.0)          # speculates step+1 of "a"
+      if step == 2:
+        ta = await eng.sample(la, temp=0.0)        # sampled twice: second speculation replaces the first
+      if step == 3:
+        ta = (ta + 1).astype(np.int32)             # caller overrides the ids: speculation must be discarded
+      if step % 2 == 1:                            # another request in between keeps its own state
+        tb = await eng.sample(lb, temp=0.0)
+        lb, sb = await eng.infer_tensor("b", sh, tb, sb)
+        rec.append(lb.copy())
+      rec.append(ta.copy())
+    assert sa["curr_pos"] == 21 + 6 and [len(r) for r in sa["tokens"]] == [27, 27]
+    return rec
+
+  async def run():
+    on, off = _engine(tmp_path, speculate_next=True), _engine(tmp_path, speculate_next=False)
+    r_on, r_off = await script(on), await script(off)
+    assert len(r_on) == len(r_off)
+    for i, (x, y) in enumerate(zip(r_on, r_off)):
+      assert x.shape == y.shape and np.array_equal(x, y), f"record {i} differs with speculation on"
+    assert off.spec_hits == 0 and off.spec_misses == 0
+    assert on.spec_hits >= 3 and on.spec_misses >= 1, (on.spec_hits, on.spec_misses)
+
+  asyncio.run(run())
+
+
+def test_generate_device_loop_equals_stepwise_calls(built_lib, tmp_path):
+  """generate() (token loop on the device) against the same loop driven from the host
+  call by call as Node does (node.py:109-147): same ids, same stop, same state afterwards --
+  greedy and with reference-mode noise (the noise stream must be rewound past the look-ahead)."""
+  from xotorch_support_jetson_b200.shard import Shard
+  mid, nl = "llama-3.2-tiny", 4
+  sh = Shard(mid, 0, nl - 1, nl)
+  rs = np.random.RandomState(11)
+  prompt = rs.randint(3, 200, (2, 17)).astype(np.int64)
+
+  async def stepwise(eng, rid, p, n, **kw):
+    logits, state = await eng.infer_tensor(rid, sh, p, None)
+    ids = []
+    for k in range(n):
+      tok = await eng.sample(logits, **kw)
+      ids.append(tok)
+      if k < n - 1:
+        logits, state = await eng.infer_tensor(rid, sh, tok, state)
+    return np.concatenate(ids, axis=1), state
+
+  async def run():
+    for kw in (dict(temp=0.0), dict(temp=0.9, top_k=12)):
+      a, b = _engine(tmp_path, speculate_next=False), _engine(tmp_path)
+      ids_a, st_a = await stepwise(a, "r", prompt, 9, **kw)
+      seen = []
+      ids_b, st_b = await b.generate("r", sh, prompt, max_generate_tokens=9, eos_token_id=-1, lookahead=4,
+                                     on_token=lambda rid, toks, fin: seen.append((rid, toks, fin)), **kw)
+      await asyncio.sleep(0)   # let the queued callbacks run
+      assert ids_b.shape == (2, 9) and ids_b.dtype == np.int32 and np.array_equal(ids_a, ids_b), (kw, ids_a, ids_b)
+      assert st_a["curr_pos"] == st_b["curr_pos"] == 17 + 8 and st_a["tokens"] == st_b["tokens"]
+      assert [t for _, t, _ in seen] == ids_b.T.tolist() and [f for _, _, f in seen] == [False] * 8 + [True]
+      # both continue call by call from where they stopped: same logits, same next ids (noise stream in step)
+      for _ in range(2):
+        la, st_a = await a.infer_tensor("r", sh, ids_a[:, -1:], st_a)
+        lb, st_b = await b.infer_tensor("r", sh, ids_b[:, -1:], st_b)
+        assert np.array_equal(la, lb)
+        ids_a, ids_b = await a.sample(la, **kw), await b.sample(lb, **kw)
+        assert np.array_equal(ids_a, ids_b)
+    # stop on eos: one row, eos := the third greedy id; a second generate() continues the request
+    a, b = _engine(tmp_path, speculate_next=False), _engine(tmp_path)
+    ref, _ = await stepwise(a, "e", prompt[:1], 8, temp=0.0)
+    eos = int(ref[0, 2])
+    n_stop = int(np.argmax(ref[0] == eos)) + 1
+    got, st = await b.generate("e", sh, prompt[:1], max_generate_tokens=8, temp=0.0, eos_token_id=eos, lookahead=3)
+    assert got.tolist() == ref[:, :n_stop].tolist() and st["curr_pos"] == 17 + n_stop - 1
+    more, st = await b.generate("e", sh, got[:, -1:], st, max_generate_tokens=8 - n_stop, temp=0.0, eos_token_id=-1)
+    assert more.tolist() == ref[:, n_stop:].tolist()
+    # the KV slot bounds the loop (max_tokens_per_seq = 128): 120-token prompt -> at most 9 ids
+    long_p = rs.randint(3, 200, (1, 120)).astype(np.int64)
+    got, st = await b.generate("cap", sh, long_p, max_generate_tokens=64, temp=0.0, eos_token_id=-1)
+    assert got.shape == (1, 9) and st["curr_pos"] == 128
+    with pytest.raises(ValueError):
+      await b.generate("x", Shard(mid, 0, 1, nl), prompt, max_generate_tokens=2)
+
+  asyncio.run(run())

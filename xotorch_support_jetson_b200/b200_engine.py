@@ -11,6 +11,15 @@ Differences that are deliberate ("known defects"):
 * a non-last shard returns the output of its last layer (the reference's off-by-one
   hand-off is not reproduced), so any split reproduces the full-shard result;
 * out-of-memory and every other native failure raise (the reference returns ``None``).
+
+Host round trip.  The plugin API makes every decode step cross the host twice (logits out,
+sampled ids back in).  When this engine holds the whole model (first AND last layer) it
+therefore enqueues the next decode forward from ``sample()`` itself, on the ids still in device
+memory, before handing those ids to the caller; ``infer_tensor`` called with exactly those ids at
+exactly that position returns the result already in flight, anything else discards it (a
+forward at the same position overwrites the KV entry, so nothing has to be undone).  The
+results are those of the unspeculated path bit for bit; ``speculate_next=False`` /
+``XB_API_SPECULATE=0`` turns it off.
 """
 import asyncio
 import functools
@@ -43,13 +52,17 @@ class _Request:
   def __init__(self, slots: List[int]):
     self.slots = slots
     self.pos = 0
-    self.tokens: Optional[np.ndarray] = None
+    # token history per row as Python ints: a decode step appends one id per row, so the
+    # ``tokens`` entry of the returned state costs O(B) + a pointer copy, not a fresh
+    # ndarray.tolist() of the whole history (1.2 ms per step at 32 x 2100 ids)
+    self.tokens: Optional[List[List[int]]] = None
 
 
 class B200ShardInferenceEngine(InferenceEngine):
   def __init__(self, shard_downloader, device: Optional[int] = None, max_seqs: Optional[int] = None,
                max_tokens_per_seq: Optional[int] = None, max_batch_tokens: Optional[int] = None,
-               page_tokens: Optional[int] = None, sample_mode: str = "reference"):
+               page_tokens: Optional[int] = None, sample_mode: str = "reference",
+               speculate_next: Optional[bool] = None):
     self.shard = None
     self.shard_downloader = shard_downloader
     self.stage: Optional[StageRuntime] = None
@@ -73,7 +86,10 @@ class B200ShardInferenceEngine(InferenceEngine):
     # they land in a small ring of PINNED buffers (a numpy view is returned, valid until the
     # ring wraps) and the device copy is kept so that sample() on that very array skips the upload
     self._pin_rings: Dict[torch.dtype, list] = {}   # dtype -> [buffers, next index]
-    self._last_logits = None   # (numpy view handed to the caller, device tensor it mirrors)
+    self._last_logits = None   # (numpy view handed to the caller, device tensor it mirrors, request id)
+    self.speculate_next = (env.get("XB_API_SPECULATE", "1") != "0") if speculate_next is None else bool(speculate_next)
+    self._spec = None          # the decode forward enqueued ahead of the caller's infer_tensor, see sample()
+    self.spec_hits = self.spec_misses = 0
 
   # ------------------------------------------------------------------ shard / weights
   async def ensure_shard(self, shard: Shard):
@@ -139,11 +155,17 @@ class B200ShardInferenceEngine(InferenceEngine):
       self.executor, functools.partial(self.tokenizer.decode, np.asarray(tokens).reshape(-1).tolist()))
 
   # ------------------------------------------------------------------ host staging
-  PIN_RING = 4
+  PIN_RING = 6
 
   def _to_host(self, dev: torch.Tensor) -> np.ndarray:
+    arr, ev = self._to_host_async(dev)
+    ev.synchronize()
+    return arr
+
+  def _to_host_async(self, dev: torch.Tensor):
     """Device tensor -> numpy through a pinned ring buffer (one DMA, no pageable bounce).  The
-    returned array is a read-only view that stays valid for the next PIN_RING-1 results."""
+    returned array is a read-only view that stays valid for the next PIN_RING-1 results; its
+    contents are defined once the returned event has completed."""
     n = dev.numel()
     ring = self._pin_rings.get(dev.dtype)
     if ring is None or ring[0][0].numel() < n:
@@ -152,10 +174,11 @@ class B200ShardInferenceEngine(InferenceEngine):
     buf = ring[0][ring[1]][:n].view(dev.shape)
     ring[1] = (ring[1] + 1) % self.PIN_RING
     buf.copy_(dev, non_blocking=True)
-    torch.cuda.current_stream(dev.device).synchronize()
+    ev = torch.cuda.Event()
+    ev.record(torch.cuda.current_stream(dev.device))
     arr = buf.numpy()
     arr.setflags(write=False)
-    return arr
+    return arr, ev
 
   # ------------------------------------------------------------------ sampling
   async def sample(self, x: np.ndarray, temp=TEMP, top_k=TOP_K, top_p: float = 0.0) -> np.ndarray:
@@ -165,8 +188,10 @@ class B200ShardInferenceEngine(InferenceEngine):
 
     def sample_body():
       st = self.stage
+      owner = None
       if self._last_logits is not None and x is self._last_logits[0]:
         logits = self._last_logits[1]      # the array we just returned (read-only): still on the device
+        owner = self._last_logits[2]
       else:
         logits = torch.as_tensor(np.ascontiguousarray(x, dtype=np.float32)).to(st.device)
       if logits.ndim == 1:
@@ -178,9 +203,45 @@ class B200ShardInferenceEngine(InferenceEngine):
       self.sample_calls += 1
       # reference semantics at any temperature: logits / max(temp, 1e-5) -> top-k -> softmax -> argmax(p/q)
       toks = st.sample(logits, temp=max(float(temp), 1e-5), top_k=int(top_k or 0), top_p=top_p, q=q, seed=self.sample_calls)
-      return np.array(self._to_host(toks), dtype=np.int32).reshape(-1, 1)
+      host_toks, ev = self._to_host_async(toks)
+      self._speculate(owner, toks, host_toks)   # enqueued BEHIND the id download: does not delay it
+      ev.synchronize()
+      return np.array(host_toks, dtype=np.int32).reshape(-1, 1)
 
     return await asyncio.get_running_loop().run_in_executor(self.executor, sample_wrapper)
+
+  def _speculate(self, request_id: Optional[str], toks: torch.Tensor, host_toks: np.ndarray):
+    """Enqueue the decode step the caller is about to ask for (see the module docstring).
+    Only when these logits came from ``request_id``'s last forward on a whole-model shard."""
+    if not self.speculate_next or request_id is None or self.shard is None:
+      return   # logits that are not the engine's latest result: nothing known about their request
+    self._spec = None   # one speculation at a time; a stale one for another request is simply dropped
+    if not (self.shard.is_first_layer() and self.shard.is_last_layer()):
+      return
+    req = self.requests.get(request_id)
+    st = self.stage
+    if req is None or len(req.slots) != toks.numel() or req.pos + 1 > st.max_tokens_per_seq or len(req.slots) > st.max_batch_tokens:
+      return
+    try:
+      out = st.forward(req.slots, [1] * len(req.slots), [req.pos] * len(req.slots), tokens=toks)
+    except RuntimeError:
+      return   # e.g. KV pool exhausted: the real call will report it
+    host, ev = self._to_host_async(out)
+    self._spec = {"request_id": request_id, "pos": req.pos, "toks": host_toks, "out": out, "host": host, "event": ev}
+
+  def _take_spec(self, request_id: str, pos: int, x: np.ndarray):
+    """The speculated result if (request, position, ids) are exactly the ones it was computed
+    for, else None (and the speculation, if it was this request's, is forgotten)."""
+    sp = self._spec
+    if sp is None or sp["request_id"] != request_id:
+      return None
+    self._spec = None
+    if x.ndim == 2 and x.shape[1] == 1 and sp["pos"] == pos and x.shape[0] == sp["toks"].shape[0] \
+       and np.array_equal(x[:, 0].astype(np.int64), sp["toks"].astype(np.int64)):
+      self.spec_hits += 1
+      return sp
+    self.spec_misses += 1
+    return None
 
   # ------------------------------------------------------------------ forward
   def _start_request(self, request_id: str, bsz: int) -> _Request:
@@ -206,6 +267,8 @@ class B200ShardInferenceEngine(InferenceEngine):
 
   def end_request(self, request_id: str):
     req = self.requests.pop(request_id, None)
+    if self._spec is not None and self._spec["request_id"] == request_id:
+      self._spec = None
     if req is not None:
       for s in req.slots:
         self.stage.release_slot(s)
@@ -266,20 +329,139 @@ class B200ShardInferenceEngine(InferenceEngine):
       if req is None or (state_pos == 0) or (state_pos is None and s > 1) or len(req.slots) != bsz:
         req = self._start_request(request_id, bsz)
       pos = req.pos if state_pos is None else int(state_pos)
+      sp = self._take_spec(request_id, pos, x) if self._spec is not None else None
       if x.ndim == 2:
+        if req.tokens is None or s > 1:
+          req.tokens = x.astype(np.int64).tolist()
+        else:
+          for row, t in zip(req.tokens, x[:, 0].tolist()):
+            row.append(int(t))
+      if x.ndim == 2:   # the caller's ids always go to the device, also when the step below is already in flight
         dev_in = torch.as_tensor(np.ascontiguousarray(x, dtype=np.int32)).to(st.device, non_blocking=True)
-        req.tokens = x.astype(np.int64) if (req.tokens is None or s > 1) else np.concatenate([req.tokens, x.astype(np.int64)], axis=-1)
-      else:
+      if sp is not None:   # this very step was enqueued by sample() on the same ids (checked on the host)
+        return finish(req, sp["out"], sp["host"], sp["event"], bsz, s, pos)
+      if x.ndim == 3:
         dev_in = torch.as_tensor(np.ascontiguousarray(x, dtype=np.float32)).to(st.device, non_blocking=True).to(torch.bfloat16)
       out = self._forward_chunked(st, req, dev_in, bsz, s, pos, x.ndim == 2)
+      return finish(req, out, None, None, bsz, s, pos)
+
+    def finish(req, out, host, ev, bsz, s, pos):
       req.pos = pos + s
       new_state = {"curr_pos": pos if not shard.is_last_layer() else pos + s}
       if req.tokens is not None:
-        new_state["tokens"] = req.tokens.tolist()
+        new_state["tokens"] = [row[:] for row in req.tokens]   # snapshot, like ShardInferenceState.to_dict (llm_utils.py:497-503)
       if shard.is_last_layer():
-        host = self._to_host(out)                      # fp32 [B, V]
-        self._last_logits = (host, out)
+        if host is None:
+          host, ev = self._to_host_async(out)          # fp32 [B, V]
+        ev.synchronize()
+        self._last_logits = (host, out, request_id)
         return host, new_state
       return self._to_host(out.float().reshape(bsz, s, -1)), new_state  # fp32 [B, s, D]
 
     return await asyncio.get_running_loop().run_in_executor(self.executor, infer_wrapper)
+
+  # ------------------------------------------------------------------ device-resident token loop
+  async def generate(self, request_id: str, shard: Shard, input_data: np.ndarray, inference_state: Optional[dict] = None, *,
+                     max_generate_tokens: int = 1024, temp: float = TEMP, top_k: int = TOP_K, top_p: float = 0.0,
+                     eos_token_id: Optional[int] = None, on_token=None, lookahead: int = 8) -> tuple[np.ndarray, dict]:
+    """The ring walk of a one-node ring without leaving the device.
+
+    In the reference every generated token costs ``process_inference_result`` -> ``sample`` ->
+    ``create_task(forward_tensor)`` -> ``process_tensor`` -> ``infer_tensor`` (node.py:109-147,
+    424-443,361-380): numpy logits out, numpy ids in, one asyncio task and one state dict per
+    token.  Here sample -> forward -> sample is chained on the stream with the ids staying in
+    device memory; each step's ids are also DMA-ed into a pinned table that the host drains
+    ``lookahead`` steps behind the device, applying the reference's stop rule (eos, or
+    ``max_generate_tokens`` buffered -- node.py:119,124) and firing ``on_token(request_id,
+    [ids of the step], is_finished)`` on the event-loop thread like
+    ``trigger_on_token_callbacks`` (node.py:136).  Up to ``lookahead`` steps computed past the
+    stop are discarded: positions and the noise stream are rewound to the accepted prefix, so the
+    ids and the state equal those of the step-by-step ``infer_tensor``/``sample`` calls.
+
+    input_data: int ids [B, s] -- a prompt (new request) or the ids to continue a request with.
+    Returns (ids [B, n] int32, state to continue from with ``infer_tensor(ids[:, -1:], state)``).
+    With B > 1 generation stops when every row has produced eos (or at the cap)."""
+    if not (shard.is_first_layer() and shard.is_last_layer()):
+      raise ValueError("generate() needs the whole model on this engine (first and last layer); "
+                       "a multi-stage ring keeps its token loop on the devices through PipelineRunner")
+    await self.ensure_shard(shard)
+    loop = asyncio.get_running_loop()
+
+    def gen_wrapper():
+      with torch.cuda.stream(self._stream):
+        return gen_body()
+
+    def gen_body():
+      st = self.stage
+      x = np.asarray(input_data)
+      if x.ndim != 2:
+        raise ValueError(f"generate() takes 2-D token ids, got ndim={x.ndim}")
+      bsz, s = x.shape
+      state_pos = None if not inference_state else inference_state.get("curr_pos")
+      req = self.requests.get(request_id)
+      if req is None or (state_pos == 0) or (state_pos is None and s > 1) or len(req.slots) != bsz:
+        req = self._start_request(request_id, bsz)
+      pos = req.pos if state_pos is None else int(state_pos)
+      self._spec = self._last_logits = None
+      if req.tokens is None or s > 1:
+        req.tokens = x.astype(np.int64).tolist()
+      else:
+        for row, t in zip(req.tokens, x[:, 0].tolist()):
+          row.append(int(t))
+      dev_in = torch.as_tensor(np.ascontiguousarray(x, dtype=np.int32)).to(st.device, non_blocking=True)
+      logits = self._forward_chunked(st, req, dev_in, bsz, s, pos, True)
+      pos += s
+      # id n is drawn from the forward at position pos+n-2, which must exist in the KV slot
+      cap = max(1, min(int(max_generate_tokens), st.max_tokens_per_seq - pos + 1))
+      depth = max(1, int(lookahead))
+      table, table_np = self._pinned_ids(cap, bsz)
+      eos = self.tokenizer.eos_token_id if (eos_token_id is None and self.tokenizer is not None) else eos_token_id
+      t_eff = max(float(temp), 1e-5)
+      events, rewind = [], []
+      done_rows = np.zeros(bsz, dtype=bool)
+      n_enq = n_acc = 0
+      stop = False
+      while not stop:
+        # keep the device up to `depth` steps ahead of what the host has looked at
+        while n_enq < cap and n_enq - n_acc < depth:
+          q = None
+          if self.sample_mode == "reference":
+            q = torch.empty((bsz, st.vocab), device=st.device).exponential_(1, generator=self.rng)
+          self.sample_calls += 1
+          toks = st.sample(logits, temp=t_eff, top_k=int(top_k or 0), top_p=top_p, q=q, seed=self.sample_calls)
+          table[n_enq].copy_(toks, non_blocking=True)
+          ev = torch.cuda.Event()
+          ev.record(torch.cuda.current_stream(st.device))
+          events.append(ev)
+          rewind.append((self.rng.get_state() if q is not None else None, self.sample_calls))
+          n_enq += 1
+          if n_enq < cap:   # id number n_enq enters the KV slot at position pos + n_enq - 1
+            logits = st.forward(req.slots, [1] * bsz, [pos + n_enq - 1] * bsz, tokens=toks)
+        events[n_acc].synchronize()
+        ids = table_np[n_acc]
+        n_acc += 1
+        if eos is not None:
+          done_rows |= (ids == eos)
+        stop = bool(done_rows.all()) or n_acc >= cap
+        if on_token is not None:
+          loop.call_soon_threadsafe(on_token, request_id, ids.tolist(), stop)
+      # forget what was computed past the stop: noise stream, call counter, positions
+      rng_state, calls = rewind[n_acc - 1]
+      if rng_state is not None:
+        self.rng.set_state(rng_state)
+      self.sample_calls = calls
+      out_ids = np.ascontiguousarray(table_np[:n_acc].T, dtype=np.int32)      # [B, n]
+      for row, fed in zip(req.tokens, out_ids[:, :n_acc - 1].tolist()):        # all but the last id went through the model
+        row.extend(fed)
+      req.pos = pos + n_acc - 1
+      return out_ids, {"curr_pos": req.pos, "tokens": [row[:] for row in req.tokens]}
+
+    return await loop.run_in_executor(self.executor, gen_wrapper)
+
+  def _pinned_ids(self, rows: int, bsz: int):
+    """[rows, bsz] int32 pinned table the device loop of generate() writes its ids into."""
+    t = getattr(self, "_ids_table", None)
+    if t is None or t.shape[0] < rows or t.shape[1] != bsz:
+      t = torch.empty((max(rows, 256), bsz), dtype=torch.int32).pin_memory()
+      self._ids_table = t
+    return t, t.numpy()
