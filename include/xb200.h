@@ -159,7 +159,9 @@ int xb_debug_linear(const void* x, const void* w, int T, int N, int K, float* y,
  * T token rows -- q/k/v, o, gate/up, down per layer (general_mha.py:83-102,
  * llm_utils.py:513-522) and the LM head on a last shard (llm_utils.py:425-435) -- `iters`
  * times back to back on `stream`, on the engine's own weights.  The caller brackets the
- * call with CUDA events; *n_launches receives the number of kernels enqueued. */
+ * call with CUDA events; *n_launches receives the number of kernels enqueued.
+ * With XB_FUSE_EPI=1 (decode Linears reduce and apply their epilogue themselves) T must equal the
+ * token-row count of the last xb_forward and the hook OVERWRITES the KV entries that call wrote. */
 int xb_bench_linears(xb_engine* e, int T, int iters, int* n_launches, void* stream);
 
 /* Measurement hook: the decode attention kernel(s) of this shard's first layer

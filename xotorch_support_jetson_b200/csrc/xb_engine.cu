@@ -83,6 +83,10 @@ struct xb_engine {
   size_t gemm_out_bytes = 0;
   float *o_part = nullptr, *ml_part = nullptr;
   int max_attn_splits = 32;
+  // decode Linears with a fused reduction (xb_gemm.cuh skinny_finish): arrival counters per 128-feature tile
+  int* tile_ctr = nullptr;
+  int fuse_epi = 0;       // XB_FUSE_EPI=1: reduce + q/k/v / SiLU epilogue inside the decode Linear (measured slower, see xb_gemm.cuh)
+  int meta_T = 0;         // token rows the device metadata currently describes
   std::map<long long, GemmPlan> plans;
   xb_counters c{};
 };
@@ -227,6 +231,11 @@ extern "C" int xb_engine_create(const xb_model_desc* desc, int device, xb_engine
   e->gemm_out_bytes = T * maxN * 2;
   if (e->gemm_out_bytes < ((size_t)64 << 20)) e->gemm_out_bytes = (size_t)64 << 20;
   XB_TRY(dmalloc(&e->gemm_out, e->gemm_out_bytes));
+  {
+    const size_t n_ctr = (maxN + 127) / 128;
+    XB_TRY(dmalloc((void**)&e->tile_ctr, n_ctr * sizeof(int)));
+    XB_CUDA(cudaMemset(e->tile_ctr, 0, n_ctr * sizeof(int)));
+  }
   // kv splits > 1 are only used while T * n_kv_heads < 2 * num_sms (see xb_forward)
   const size_t Tsplit = T < (size_t)2 * e->num_sms ? T : (size_t)2 * e->num_sms;
   XB_TRY(dmalloc((void**)&e->o_part, Tsplit * d.n_heads * e->max_attn_splits * d.head_dim * sizeof(float)));
@@ -253,6 +262,8 @@ extern "C" int xb_engine_create(const xb_model_desc* desc, int device, xb_engine
     if (g != nullptr && g[0] == '0') e->use_graphs = 0;
     g = getenv("XB_PDL");
     if (g != nullptr && g[0] == '0') e->use_pdl = 0;
+    g = getenv("XB_FUSE_EPI");
+    if (g != nullptr) e->fuse_epi = g[0] == '1';
   }
   *out = e;
   return 0;
@@ -278,7 +289,7 @@ extern "C" int xb_engine_destroy(xb_engine* e) {
   for (auto& kv : e->graphs)
     if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
   cudaFree(e->h); cudaFree(e->hn); cudaFree(e->q); cudaFree(e->attn); cudaFree(e->act);
-  cudaFree(e->last_rows); cudaFree(e->gemm_out); cudaFree(e->o_part); cudaFree(e->ml_part);
+  cudaFree(e->last_rows); cudaFree(e->gemm_out); cudaFree(e->tile_ctr); cudaFree(e->o_part); cudaFree(e->ml_part);
   delete e;
   return 0;
 }
@@ -411,11 +422,14 @@ static int get_plan(xb_engine* e, int site, int layer, const bf16* x, long long 
   if (it == e->plans.end()) {
     GemmPlan p;
     XB_TRY(xb_gemm_plan(&p, x, ldx, w, 1, T, N, K, out, ld_out, bias, round_bf16, e->num_sms, 0));
-    if (p.args.mode == XB_GEMM_WIDE && site == SITE_QKV) {
-      // prefill: bias + RoPE + q store + paged-KV append happen in the GEMM epilogue
+    const bool fuse = e->fuse_epi && p.args.mode == XB_GEMM_SKINNY && 128 % e->d.head_dim == 0 && N % 128 == 0;
+    if ((p.args.mode == XB_GEMM_WIDE || fuse) && site == SITE_QKV) {
+      // bias + RoPE + q store + paged-KV append happen in the GEMM epilogue (decode: in the block
+      // that completes a tile last)
       const xb_model_desc& d = e->d;
       GemmArgs& g = p.args;
       g.epi = XB_EPI_QKV;
+      g.tile_ctr = e->tile_ctr;
       g.rope = e->rope;
       g.q_out = e->q;
       g.k_pool = e->L[layer].k_pool;
@@ -435,7 +449,16 @@ static int get_plan(xb_engine* e, int site, int layer, const bf16* x, long long 
       p.args.epi = XB_EPI_SILU;
       p.args.out = e->act;
       p.args.ld_out = e->d.inter_dim;
-    } else if (out == e->gemm_out) {
+    } else if (fuse && site == SITE_GU) {
+      p.args.epi = XB_EPI_SILU;
+      p.args.tile_ctr = e->tile_ctr;
+      p.args.fin_out = e->act;
+      p.args.fin_ld = e->d.inter_dim;
+    }
+    if (p.args.mode == XB_GEMM_SKINNY && out == e->gemm_out) {
+      const size_t need = (size_t)p.split.splits * T * N * 4;
+      XB_CHECK(need <= e->gemm_out_bytes, "gemm workspace too small: need %zu have %zu", need, e->gemm_out_bytes);
+    } else if (p.args.mode == XB_GEMM_WIDE && site != SITE_QKV && site != SITE_GU && out == e->gemm_out) {
       const size_t need = p.args.mode == XB_GEMM_SKINNY ? (size_t)p.split.splits * T * N * 4 : (size_t)T * N * 2;
       XB_CHECK(need <= e->gemm_out_bytes, "gemm workspace too small: need %zu have %zu", need, e->gemm_out_bytes);
     }
@@ -576,7 +599,7 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
     XB_TRY(get_plan(e, SITE_QKV, l, e->hn, D, w.wqkv, T, e->NQKV, D, e->gemm_out, e->NQKV, w.bqkv, 0, &gp));
     XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
     LAUNCH_COUNT(e);
-    if (gp->args.mode == XB_GEMM_SKINNY) {
+    if (gp->args.mode == XB_GEMM_SKINNY && gp->args.epi == XB_EPI_PLAIN) {
       const int qkv_items = (d.n_heads + 2 * d.n_kv_heads) * (d.rope_kind == 0 ? hd / 4 : hd / 8);
       XB_TRY(launch_k(e, xb_qkv_finalize_kernel, dim3(T, (qkv_items + 255) / 256), dim3(256), 0, st, 1, (const float*)e->gemm_out, gp->split,
                       (long long)T * e->NQKV, w.bqkv, e->rope, e->q, w.k_pool, w.v_pool, m, d.n_heads, d.n_kv_heads, hd,
@@ -593,7 +616,7 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
     XB_TRY(get_plan(e, SITE_GU, l, e->hn, D, w.wgu, T, 2 * I, D, e->gemm_out, 2 * I, nullptr, 0, &gp));
     XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
     LAUNCH_COUNT(e);
-    if (gp->args.mode == XB_GEMM_SKINNY) {
+    if (gp->args.mode == XB_GEMM_SKINNY && gp->args.epi == XB_EPI_PLAIN) {
       const long long n = (long long)T * (I / 4);
       XB_TRY(launch_k(e, xb_silu_mul_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, st, 1, (const float*)e->gemm_out,
                       gp->split, (long long)T * 2 * I, e->act, T, I));
@@ -713,6 +736,7 @@ static int forward_impl(xb_engine* e, const xb_batch* b, void* out, void* const*
   } else {
     XB_CUDA(cudaMemcpyAsync(e->d_meta, hm, e->meta_ints * 4, cudaMemcpyHostToDevice, st));
   }
+  e->meta_T = T;
   if (ctl != nullptr) {
     XB_CHECK(decode_only, "the peer hand-off carries decode steps only");
     XB_CHECK(!ho_in || (!first && e->landing != nullptr && ctl[0] < e->ho_slots && T <= e->ho_rows),
@@ -823,6 +847,9 @@ extern "C" int xb_handoff_connect(xb_engine* e, const void* next_landing_handle,
 // the call with CUDA events; the launch count is returned in *n_launches.
 extern "C" int xb_bench_linears(xb_engine* e, int T, int iters, int* n_launches, void* stream) {
   XB_CHECK(e != nullptr && T > 0 && T <= e->d.max_batch_tokens && iters > 0, "bad argument");
+  // with XB_FUSE_EPI=1 the q/k/v epilogue stores through the batch metadata of the last forward
+  XB_CHECK(!e->fuse_epi || T == e->meta_T, "xb_bench_linears: T=%d must equal the row count of the last xb_forward (%d)", T,
+           e->meta_T);
   const xb_model_desc& d = e->d;
   cudaStream_t st = (cudaStream_t)stream;
   XB_CUDA(cudaSetDevice(e->device));

@@ -52,6 +52,11 @@ struct GemmArgs {
   bf16 *q_out, *k_pool, *v_pool;
   const int *tok_seq, *tok_pos, *seq_slot, *page_table;
   int max_pages, page_tokens, n_heads, n_kv_heads, head_dim, rope_kind;
+  // SKINNY with epi != PLAIN: the block that completes a 128-feature tile LAST (tile_ctr) sums the
+  // partial planes in plane order and applies the epilogue itself -- no separate reduce kernel
+  int* tile_ctr;           // [a_tiles], zero between launches (the last arriver resets its entry)
+  void* fin_out;           // XB_EPI_SILU: bf16 act[t][fin_ld]
+  long long fin_ld;
 };
 enum { XB_EPI_PLAIN = 0, XB_EPI_QKV = 1, XB_EPI_SILU = 2 };
 
@@ -228,6 +233,110 @@ __device__ __forceinline__ void epi_wide_silu(const GemmArgs& g, uint32_t t_addr
   }
 }
 
+// ---- SKINNY fused reduction (XB_FUSE_EPI=1, off by default): runs in the four epilogue warps after the
+// unit's partial plane is stored.  Measured on B200, Llama-3.1-8B: bit-identical to the separate
+// reduce kernels but SLOWER -- decode bs=32 6.16 ms/step against 4.95 ms, Linear kernel 0.53 of the
+// HBM peak against 0.81, bs=1 285.8 against 287.7 tok/s: the device-wide fence + atomic + two
+// block barriers per unit cost as much as the kernel boundary they replace (which programmatic
+// dependent launch already overlaps), and the 128 epilogue threads of ONE block then do a reduction
+// that the separate kernel spreads over every SM; on a block's last unit all of it is tail.
+// thread = output feature n = ta*128 + row_in_tile.  Sums are taken over ALL planes of the tile in
+// plane order (its own included, re-read from L2), so the result does not depend on which block
+// happens to arrive last and equals what xb_qkv_finalize_kernel / xb_silu_mul_kernel compute.
+__device__ __forceinline__ void skinny_sum8(const float* part, long long plane_stride, int nseg, long long ld, int n, int t0,
+                                            int T, float* acc) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  for (int s = 0; s < nseg; ++s) {
+    float v[8];
+    const float* p = part + s * plane_stride + (long long)t0 * ld + n;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = (t0 + j < T) ? __ldcg(p + j * ld) : 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] += v[j];
+  }
+}
+
+__device__ __forceinline__ void skinny_finish(const GemmArgs& g, int ta, int row_in_tile, int lane, volatile uint32_t* flag) {
+  const int nseg = xb_n_segments(SplitInfo{g.k_blocks, g.sk_q, g.splits}, ta * 128);
+  __threadfence();                                   // this thread's plane stores are visible device-wide
+  asm volatile("bar.sync 1, 128;" ::: "memory");     // ... and so are those of the other 127 epilogue threads
+  if (row_in_tile == 0) {
+    const int old = atomicAdd(g.tile_ctr + ta, 1);
+    const bool last = old == nseg - 1;
+    if (last) g.tile_ctr[ta] = 0;                    // every arrival is in: ready for the next launch
+    *flag = last ? 1u : 0u;
+  }
+  asm volatile("bar.sync 1, 128;" ::: "memory");
+  if (*flag == 0u) return;
+  __threadfence();
+  const float* part = reinterpret_cast<const float*>(g.out);
+  const int T = g.b_rows;
+  const long long ld = g.ld_out, ps = (long long)T * ld;
+  const int n = ta * 128 + row_in_tile;
+  const bool valid = n < g.a_rows;
+  const int nn = valid ? n : 0;
+  if (g.epi == XB_EPI_SILU) {
+    // lanes 0..15 hold gate, 16..31 up of the same 16 features (interleave of xb_tile_weight_kernel)
+    bf16* act = reinterpret_cast<bf16*>(g.fin_out);
+    const int feat = ta * 64 + (row_in_tile >> 5) * 16 + (lane & 15);
+#pragma unroll 1
+    for (int t0 = 0; t0 < T; t0 += 8) {
+      float acc[8];
+      skinny_sum8(part, ps, valid ? nseg : 0, ld, nn, t0, T, acc);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float x = rbf(acc[j]);
+        const float o = __shfl_xor_sync(0xffffffffu, x, 16);
+        if (lane < 16 && valid && t0 + j < T)
+          act[(long long)(t0 + j) * g.fin_ld + feat] = f2bf(rbf(x / (1.0f + expf(-x))) * o);
+      }
+    }
+  } else {
+    const int hd = g.head_dim, half = hd >> 1, H = g.n_heads, KV = g.n_kv_heads;
+    const int head = nn / hd, e = nn % hd;
+    const bool rot = head < H + KV;
+    const bool split_pairs = g.rope_kind != 0 && rot;   // partner hd/2 features away: other warp, so re-read it
+    const int np = split_pairs ? (e < half ? nn + half : nn - half) : nn;
+    const float bias_n = g.bias != nullptr ? bf2f(g.bias[nn]) : 0.f;
+    const float bias_p = g.bias != nullptr ? bf2f(g.bias[np]) : 0.f;
+#pragma unroll 1
+    for (int t0 = 0; t0 < T; t0 += 8) {
+      float own[8], par[8];
+      skinny_sum8(part, ps, valid ? nseg : 0, ld, nn, t0, T, own);
+      if (split_pairs) skinny_sum8(part, ps, valid ? nseg : 0, ld, np, t0, T, par);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int t = t0 + j;
+        const bool ok = valid && t < T;
+        float x = own[j];
+        if (g.bias != nullptr) x += bias_n;
+        x = rbf(x);
+        float y = __shfl_xor_sync(0xffffffffu, x, 1);   // interleaved pairs: neighbour lane
+        float r = x;
+        const int pos = ok ? g.tok_pos[t] : 0;
+        if (rot && ok) {
+          const float* rope_row = g.rope + (long long)pos * half * 2;
+          if (g.rope_kind == 0) {
+            const float2 cs = *reinterpret_cast<const float2*>(rope_row + (e >> 1) * 2);
+            r = (e & 1) == 0 ? __fsub_rn(__fmul_rn(x, cs.x), __fmul_rn(y, cs.y))
+                             : __fadd_rn(__fmul_rn(x, cs.x), __fmul_rn(y, cs.y));
+          } else {
+            y = par[j];
+            if (g.bias != nullptr) y += bias_p;
+            y = rbf(y);
+            const float2 cs = *reinterpret_cast<const float2*>(rope_row + (e % half) * 2);
+            const float cc = rbf(cs.x), sn = rbf(cs.y);
+            r = e < half ? __fadd_rn(rbf(__fmul_rn(x, cc)), rbf(__fmul_rn(-y, sn)))
+                         : __fadd_rn(rbf(__fmul_rn(x, cc)), rbf(__fmul_rn(y, sn)));
+          }
+        }
+        if (ok) *epi_qkv_dst(g, t, pos, head, e) = f2bf(r);
+      }
+    }
+  }
+}
+
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(192, 1)
 xb_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmArgs g) {
@@ -241,6 +350,7 @@ xb_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   uint64_t* tfull_bar = empty_bar + STAGES;
   uint64_t* tempty_bar = tfull_bar + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  volatile uint32_t* last_flag = tmem_slot + 1;   // skinny_finish: "this block completed the tile"
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -440,6 +550,8 @@ xb_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty_bar[acc]);
       if (++acc == Cfg::ACC_STAGES) { acc = 0; acc_phase ^= 1; }
+      // the accumulator is released: the next unit's MMAs run while the tile is reduced
+      if (BN <= 128 && g.mode == XB_GEMM_SKINNY && g.epi != XB_EPI_PLAIN) skinny_finish(g, ta, row_in_tile, lane, last_flag);
     }
   }
 
@@ -579,6 +691,9 @@ static int xb_gemm_plan(GemmPlan* p, const bf16* x, long long ldx, const bf16* w
   g.round_bf16 = round_bf16;
   g.w_tiled = w_tiled;
   g.epi = XB_EPI_PLAIN;
+  g.tile_ctr = nullptr;
+  g.fin_out = nullptr;
+  g.fin_ld = 0;
   const long long w_tiles = (N + 127) / 128;
   if (T <= 128) {
     const int bn = xb_pick_bn_skinny(T);
