@@ -151,8 +151,9 @@ template <int HD, int G, int NST>
 struct AttDecCfg {
   static constexpr int TILE_BYTES = XB_ATT_TILE * HD * 2;
   static constexpr int STAGE_BYTES = 2 * TILE_BYTES;
-  static constexpr int MERGE_BYTES = 4 * G * HD * 4 + 4 * 16 * 2 * 4;
-  static constexpr int SMEM_BYTES = NST * STAGE_BYTES + MERGE_BYTES + 1024 + 128;
+  static constexpr int MERGE_BYTES = 4 * G * HD * 4 + 4 * 16 * 2 * 4;   // aliases the K/V ring after the key loop
+  static_assert(MERGE_BYTES <= NST * STAGE_BYTES, "merge buffers must fit in the K/V ring");
+  static constexpr int SMEM_BYTES = NST * STAGE_BYTES + 1024 + 128;
 };
 
 template <int HD, int G, int NST>
@@ -164,15 +165,21 @@ __global__ void __launch_bounds__(160) xb_attn_decode_mma_kernel(
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* stages = smem;
-  float* mg_o = reinterpret_cast<float*>(smem + NST * Cfg::STAGE_BYTES);   // [4 warps][G][HD]
+  float* mg_o = reinterpret_cast<float*>(smem);                            // [4 warps][G][HD], reuses the ring
   float* mg_ml = mg_o + 4 * G * HD;                                       // [4 warps][16][2]
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(mg_ml + 4 * 16 * 2);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + NST * Cfg::STAGE_BYTES);
   uint64_t* empty_bar = full_bar + NST;
 
   const int t = blockIdx.x, kvh = blockIdx.y, sp = blockIdx.z;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   pdl_launch_dependents();
-  pdl_wait();
+  // The batch metadata and page table were uploaded before the step's first kernel started, and
+  // every K/V row below position `pos` was written by an EARLIER step: only q and the row at `pos`
+  // come from the kernel just upstream.  So the producer streams the older tiles before
+  // griddepcontrol.wait -- the K/V reads overlap the q/k/v Linear and its finalize kernel.
+  // (Safe because every forward call begins with the metadata H2D copy, a full stream dependency:
+  // no kernel of an earlier call can still be running, and within a call only the kernel just
+  // upstream writes this layer's pool, at row `pos`.)
   const int pos = m.tok_pos[t];
   const int slot = m.seq_slot[m.tok_seq[t]];
   const int* pt = m.page_table + (long long)slot * m.max_pages;
@@ -196,7 +203,12 @@ __global__ void __launch_bounds__(160) xb_attn_decode_mma_kernel(
       tma_prefetch_desc(&tmV);
       int stage = 0;
       uint32_t phase = 0;
+      bool waited = false;
       for (int kt = kt0; kt < kt1; ++kt) {
+        if (!waited && (kt - kt0 >= NST || kt >= n_tiles - 1)) {   // ring full, or the tile holding row `pos`
+          pdl_wait();
+          waited = true;
+        }
         mbar_wait(&empty_bar[stage], phase ^ 1);
         uint8_t* sK = stages + stage * Cfg::STAGE_BYTES;
         att_issue_tile<HD>(&tmK, &tmV, sK, sK + Cfg::TILE_BYTES, &full_bar[stage], pt, m.max_pages, kt, kvh, KV, m.page_tokens);
@@ -205,6 +217,7 @@ __global__ void __launch_bounds__(160) xb_attn_decode_mma_kernel(
     }
     return;
   }
+  pdl_wait();   // compute warps: q, and (through the last tile) the newest K/V row
 
   // ===================== 4 compute warps: each takes 16 keys of every tile =====================
   constexpr int KS = HD / 16, DT = HD / 8;
@@ -243,6 +256,7 @@ __global__ void __launch_bounds__(160) xb_attn_decode_mma_kernel(
   }
 
   // ---- merge the 4 warps (each saw a disjoint key subset); only rows < G are real
+  named_bar_sync(1, 128);   // every warp is done reading the ring: its memory now holds the merge buffers
   lrow[0] += __shfl_xor_sync(0xffffffffu, lrow[0], 1);
   lrow[0] += __shfl_xor_sync(0xffffffffu, lrow[0], 2);
   {

@@ -473,7 +473,10 @@ static int launch_attn_g(xb_engine* e, const LayerW& w, const BatchMeta& m, int 
                          cudaStream_t st) {
   const xb_model_desc& d = e->d;
   const float scale_log2 = (1.0f / sqrtf((float)d.head_dim)) * 1.4426950408889634f;
-  constexpr int NST = 3;
+#ifndef XB_ATT_DEC_NST
+#define XB_ATT_DEC_NST 3
+#endif
+  constexpr int NST = XB_ATT_DEC_NST;
   if (n_tiles == 0) {
     // decode: one block per (token, kv head, kv split)
     using Cfg = AttDecCfg<HD, G, NST>;

@@ -751,7 +751,10 @@ static int xb_gemm_plan(GemmPlan* p, const bf16* x, long long ldx, const bf16* w
 static int xb_gemm_run(const GemmPlan& p, cudaStream_t st, int pdl) {
   switch (p.bn) {
     case 16:  return xb_gemm_launch_t<16, 5>(p.tmA, p.tmB, p.args, p.grid, st, pdl);
-    case 32:  return xb_gemm_launch_t<32, 5>(p.tmA, p.tmB, p.args, p.grid, st, pdl);
+#ifndef XB_G32_STAGES
+#define XB_G32_STAGES 5
+#endif
+    case 32:  return xb_gemm_launch_t<32, XB_G32_STAGES>(p.tmA, p.tmB, p.args, p.grid, st, pdl);
     case 64:  return xb_gemm_launch_t<64, 4>(p.tmA, p.tmB, p.args, p.grid, st, pdl);
     case 128: return xb_gemm_launch_t<128, 6>(p.tmA, p.tmB, p.args, p.grid, st, pdl);
     case 256: return xb_gemm_launch_t<256, 4>(p.tmA, p.tmB, p.args, p.grid, st, pdl);
