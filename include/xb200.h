@@ -99,6 +99,22 @@ int xb_engine_destroy(xb_engine* e);
  * `src` may be host or device memory; `layer` is the absolute layer index or -1. */
 int xb_load_weight(xb_engine* e, int layer, int kind, const void* src, size_t nbytes);
 
+/* Replaces the safetensors walk of load_model_weights_torchtune (llm_utils.py:136-160: every file
+ * opened, every tensor read) for ONE checkpoint file: the file is mapped, the header parsed, and
+ * only the tensors of this shard (its layer range; embedding / final norm / head where the shard
+ * holds them) are streamed page cache -> pinned ring -> device, where one kernel per chunk casts
+ * (BF16/F16/F32 -> bf16), applies the reference's q/k row permutation when permute_qk != 0
+ * (llm_utils.py:126-134,213-231: Llama yes, Qwen no) and writes the engine's fused, tile-major
+ * layout.  HF tensor names (model.layers.N.self_attn.q_proj.weight ...).  *n_tensors / *n_bytes
+ * (either may be NULL) receive what was taken from this file.  Call once per file of a sharded
+ * checkpoint, then xb_weights_missing. */
+int xb_load_safetensors(xb_engine* e, const char* path, int permute_qk, int* n_tensors, uint64_t* n_bytes);
+
+/* *n_missing = weights of this shard that neither xb_load_weight nor xb_load_safetensors has
+ * supplied yet (0 = ready to run); buf (may be NULL) receives a readable list.  The reference
+ * surfaces the same condition as load_state_dict(strict=False) missing keys (llm_utils.py:262-284). */
+int xb_weights_missing(xb_engine* e, char* buf, size_t buflen, int* n_missing);
+
 /* Paged KV cache.  Replaces setup_caches / reset_caches / KVCache.update
  * (llm_utils.py:320-365; sharded_inference_engine.py:71-82,139-147): pages of
  * `page_tokens` positions are handed to a slot on demand as it grows and returned by

@@ -3,6 +3,7 @@
 #include "../../include/xb200.h"
 #include "xb_common.cuh"
 #include "xb_gemm.cuh"
+#include "xb_loader.cuh"
 #include "xb_kernels.cuh"
 #include "xb_attn_mma.cuh"
 
@@ -89,6 +90,8 @@ struct xb_engine {
   int meta_T = 0;         // token rows the device metadata currently describes
   std::map<long long, GemmPlan> plans;
   xb_counters c{};
+  std::map<long long, int> loaded;   // (layer + 1) * 64 + kind -> seen by xb_load_weight / xb_load_safetensors
+  StRing* ring = nullptr;            // loader staging, alive from the first file until the shard is complete
 };
 
 #define LAUNCH_COUNT(e) ((e)->c.launches++)
@@ -271,6 +274,11 @@ extern "C" int xb_engine_create(const xb_model_desc* desc, int device, xb_engine
 
 extern "C" int xb_engine_destroy(xb_engine* e) {
   if (e == nullptr) return 0;
+  if (e->ring != nullptr) {
+    e->ring->destroy();
+    delete e->ring;
+    e->ring = nullptr;
+  }
   cudaSetDevice(e->device);
   cudaDeviceSynchronize();
   for (LayerW& w : e->L) {
@@ -294,60 +302,245 @@ extern "C" int xb_engine_destroy(xb_engine* e) {
   return 0;
 }
 
-extern "C" int xb_load_weight(xb_engine* e, int layer, int kind, const void* src, size_t nbytes) {
-  XB_CHECK(e != nullptr && src != nullptr, "null argument");
-  XB_CUDA(cudaSetDevice(e->device));
+// Where a checkpoint tensor goes: a row range of a tile-major matrix, or a plain bf16 vector/table.
+struct WTarget {
+  bf16* tdst = nullptr;         // tiled matrix target
+  size_t row0 = 0, rows = 0, K = 0;
+  int il = 0, il_off = 0;       // gate/up rows are interleaved in 16-feature blocks
+  void* dst = nullptr;          // plain copy target (vectors, embedding, RoPE table)
+  size_t want = 0;              // bytes of a plain target
+  bool embed = false;           // embedding: row-major copy and/or the tied head's tiled copy
+};
+
+static int resolve_target(xb_engine* e, int layer, int kind, WTarget* t) {
   const xb_model_desc& d = e->d;
   const size_t D = d.dim, I = d.inter_dim;
-  void* dst = nullptr;          // plain copy target (vectors, embedding, RoPE table)
-  bf16* tdst = nullptr;         // tiled matrix target
-  size_t want = 0, row0 = 0, rows = 0, K = 0;
-  int il = 0, il_off = 0;       // gate/up rows are interleaved in 16-feature blocks
   if (layer >= 0) {
     XB_CHECK(layer >= d.start_layer && layer <= d.end_layer, "layer %d outside this shard [%d,%d]", layer, d.start_layer,
              d.end_layer);
     LayerW& w = e->L[layer - d.start_layer];
     switch (kind) {
-      case XB_W_Q: tdst = w.wqkv; row0 = 0; rows = e->NQ; K = D; break;
-      case XB_W_K: tdst = w.wqkv; row0 = e->NQ; rows = e->NKV; K = D; break;
-      case XB_W_V: tdst = w.wqkv; row0 = e->NQ + e->NKV; rows = e->NKV; K = D; break;
-      case XB_W_O: tdst = w.wo; rows = D; K = e->NQ; break;
-      case XB_W_GATE: tdst = w.wgu; rows = I; K = D; il = 1; il_off = 0; break;
-      case XB_W_UP: tdst = w.wgu; rows = I; K = D; il = 1; il_off = 16; break;
-      case XB_W_DOWN: tdst = w.wdown; rows = D; K = I; break;
-      case XB_W_SA_NORM: dst = w.sa_norm; want = D * 2; break;
-      case XB_W_MLP_NORM: dst = w.mlp_norm; want = D * 2; break;
-      case XB_W_Q_BIAS: XB_CHECK(w.bqkv, "model has no qkv bias"); dst = w.bqkv; want = (size_t)e->NQ * 2; break;
-      case XB_W_K_BIAS: XB_CHECK(w.bqkv, "model has no qkv bias"); dst = w.bqkv + e->NQ; want = (size_t)e->NKV * 2; break;
-      case XB_W_V_BIAS: XB_CHECK(w.bqkv, "model has no qkv bias"); dst = w.bqkv + e->NQ + e->NKV; want = (size_t)e->NKV * 2; break;
+      case XB_W_Q: t->tdst = w.wqkv; t->row0 = 0; t->rows = e->NQ; t->K = D; break;
+      case XB_W_K: t->tdst = w.wqkv; t->row0 = e->NQ; t->rows = e->NKV; t->K = D; break;
+      case XB_W_V: t->tdst = w.wqkv; t->row0 = e->NQ + e->NKV; t->rows = e->NKV; t->K = D; break;
+      case XB_W_O: t->tdst = w.wo; t->rows = D; t->K = e->NQ; break;
+      case XB_W_GATE: t->tdst = w.wgu; t->rows = I; t->K = D; t->il = 1; t->il_off = 0; break;
+      case XB_W_UP: t->tdst = w.wgu; t->rows = I; t->K = D; t->il = 1; t->il_off = 16; break;
+      case XB_W_DOWN: t->tdst = w.wdown; t->rows = D; t->K = I; break;
+      case XB_W_SA_NORM: t->dst = w.sa_norm; t->want = D * 2; break;
+      case XB_W_MLP_NORM: t->dst = w.mlp_norm; t->want = D * 2; break;
+      case XB_W_Q_BIAS: XB_CHECK(w.bqkv, "model has no qkv bias"); t->dst = w.bqkv; t->want = (size_t)e->NQ * 2; break;
+      case XB_W_K_BIAS: XB_CHECK(w.bqkv, "model has no qkv bias"); t->dst = w.bqkv + e->NQ; t->want = (size_t)e->NKV * 2; break;
+      case XB_W_V_BIAS: XB_CHECK(w.bqkv, "model has no qkv bias"); t->dst = w.bqkv + e->NQ + e->NKV; t->want = (size_t)e->NKV * 2; break;
       default: return xb_fail(1, "weight kind %d is not a per-layer kind", kind);
     }
   } else {
     switch (kind) {
       case XB_W_EMBED:
         XB_CHECK(e->embed || (e->lm_head && d.tied_head), "this shard holds no embedding");
-        want = (size_t)d.vocab * D * 2;
-        XB_CHECK(nbytes == want, "embedding: got %zu bytes, expected %zu", nbytes, want);
-        if (e->embed) XB_CUDA(cudaMemcpy(e->embed, src, nbytes, cudaMemcpyDefault));
-        if (e->lm_head && d.tied_head) XB_TRY(store_tiled(e->lm_head, src, 0, d.vocab, D));
-        e->plans.clear();
-        return 0;
-      case XB_W_FINAL_NORM: XB_CHECK(e->final_norm, "this shard holds no final norm"); dst = e->final_norm; want = D * 2; break;
+        t->embed = true; t->rows = d.vocab; t->K = D; t->want = (size_t)d.vocab * D * 2;
+        break;
+      case XB_W_FINAL_NORM: XB_CHECK(e->final_norm, "this shard holds no final norm"); t->dst = e->final_norm; t->want = D * 2; break;
       case XB_W_LM_HEAD:
         XB_CHECK(e->lm_head && !d.tied_head, "this shard holds no separate LM head");
-        tdst = e->lm_head; rows = d.vocab; K = D;
+        t->tdst = e->lm_head; t->rows = d.vocab; t->K = D;
         break;
-      case XB_W_ROPE_TABLE: dst = e->rope; want = (size_t)d.max_positions * (d.head_dim / 2) * 2 * sizeof(float); break;
+      case XB_W_ROPE_TABLE: t->dst = e->rope; t->want = (size_t)d.max_positions * (d.head_dim / 2) * 2 * sizeof(float); break;
       default: return xb_fail(1, "weight kind %d is not a global kind", kind);
     }
   }
-  if (tdst != nullptr) {
-    want = rows * K * 2;
-    XB_CHECK(nbytes == want, "weight kind %d layer %d: got %zu bytes, expected %zu", kind, layer, nbytes, want);
-    return store_tiled(tdst, src, row0, rows, K, il, il_off);
+  if (t->tdst != nullptr) t->want = t->rows * t->K * 2;
+  return 0;
+}
+
+extern "C" int xb_load_weight(xb_engine* e, int layer, int kind, const void* src, size_t nbytes) {
+  XB_CHECK(e != nullptr && src != nullptr, "null argument");
+  XB_CUDA(cudaSetDevice(e->device));
+  WTarget t;
+  XB_TRY(resolve_target(e, layer, kind, &t));
+  XB_CHECK(nbytes == t.want, "weight kind %d layer %d: got %zu bytes, expected %zu", kind, layer, nbytes, t.want);
+  if (t.embed) {
+    if (e->embed) XB_CUDA(cudaMemcpy(e->embed, src, nbytes, cudaMemcpyDefault));
+    if (e->lm_head && e->d.tied_head) XB_TRY(store_tiled(e->lm_head, src, 0, e->d.vocab, e->d.dim));
+    e->plans.clear();
+  } else if (t.tdst != nullptr) {
+    XB_TRY(store_tiled(t.tdst, src, t.row0, t.rows, t.K, t.il, t.il_off));
+  } else {
+    XB_CUDA(cudaMemcpy(t.dst, src, nbytes, cudaMemcpyDefault));
   }
-  XB_CHECK(nbytes == want, "weight kind %d layer %d: got %zu bytes, expected %zu", kind, layer, nbytes, want);
-  XB_CUDA(cudaMemcpy(dst, src, nbytes, cudaMemcpyDefault));
+  e->loaded[(long long)(layer + 1) * 64 + kind] = 1;
+  return 0;
+}
+
+// HF tensor name -> (layer, kind) of this ABI; false for names the path does not use (rotary inv_freq ...)
+static bool hf_name_to_kind(const std::string& name, int* layer, int* kind) {
+  static const struct { const char* suffix; int kind; } per_layer[] = {
+    {"self_attn.q_proj.weight", XB_W_Q}, {"self_attn.k_proj.weight", XB_W_K}, {"self_attn.v_proj.weight", XB_W_V},
+    {"self_attn.o_proj.weight", XB_W_O}, {"mlp.gate_proj.weight", XB_W_GATE}, {"mlp.up_proj.weight", XB_W_UP},
+    {"mlp.down_proj.weight", XB_W_DOWN}, {"input_layernorm.weight", XB_W_SA_NORM},
+    {"post_attention_layernorm.weight", XB_W_MLP_NORM}, {"self_attn.q_proj.bias", XB_W_Q_BIAS},
+    {"self_attn.k_proj.bias", XB_W_K_BIAS}, {"self_attn.v_proj.bias", XB_W_V_BIAS}};
+  const std::string pre = "model.layers.";
+  if (name.compare(0, pre.size(), pre) == 0) {
+    size_t i = pre.size();
+    int l = 0;
+    if (i >= name.size() || name[i] < '0' || name[i] > '9') return false;
+    while (i < name.size() && name[i] >= '0' && name[i] <= '9') l = l * 10 + (name[i++] - '0');
+    if (i >= name.size() || name[i] != '.') return false;
+    const std::string rest = name.substr(i + 1);
+    for (const auto& pl : per_layer)
+      if (rest == pl.suffix) { *layer = l; *kind = pl.kind; return true; }
+    return false;
+  }
+  *layer = -1;
+  if (name == "model.embed_tokens.weight") { *kind = XB_W_EMBED; return true; }
+  if (name == "model.norm.weight") { *kind = XB_W_FINAL_NORM; return true; }
+  if (name == "lm_head.weight") { *kind = XB_W_LM_HEAD; return true; }
+  return false;
+}
+
+static bool shard_wants(const xb_engine* e, int layer, int kind) {
+  const xb_model_desc& d = e->d;
+  if (layer >= 0) {
+    if (layer < d.start_layer || layer > d.end_layer) return false;
+    return (kind != XB_W_Q_BIAS && kind != XB_W_K_BIAS && kind != XB_W_V_BIAS) || d.qkv_bias;
+  }
+  const bool first = d.start_layer == 0, last = d.end_layer == d.n_layers - 1;
+  if (kind == XB_W_EMBED) return first || (last && d.tied_head);
+  if (kind == XB_W_FINAL_NORM) return last;
+  if (kind == XB_W_LM_HEAD) return last && !d.tied_head;
+  return false;
+}
+
+// One .safetensors file -> every tensor of this shard found in it (see xb_loader.cuh).
+extern "C" int xb_load_safetensors(xb_engine* e, const char* path, int permute_qk, int* n_tensors, uint64_t* n_bytes) {
+  XB_CHECK(e != nullptr && path != nullptr, "null argument");
+  XB_CUDA(cudaSetDevice(e->device));
+  StFile f;
+  XB_TRY(f.open_map(path));
+  uint64_t hlen = 0;
+  memcpy(&hlen, f.base, 8);
+  XB_CHECK(hlen > 0 && hlen <= f.size - 8, "%s: bad safetensors header length %llu", path, (unsigned long long)hlen);
+  std::vector<StEntry> entries;
+  XB_CHECK(st_parse_header((const char*)f.base + 8, (size_t)hlen, &entries), "%s: cannot parse the safetensors header", path);
+  const uint8_t* data = f.base + 8 + hlen;
+  const size_t data_size = f.size - 8 - (size_t)hlen;
+  int rc = 0;
+  if (e->ring == nullptr) {
+    e->ring = new StRing();
+    rc = e->ring->init((size_t)32 << 20);
+  }
+  StRing& ring = *e->ring;
+  int count = 0;
+  uint64_t total = 0;
+  const xb_model_desc& d = e->d;
+  for (size_t ei = 0; rc == 0 && ei < entries.size(); ++ei) {
+    const StEntry& en = entries[ei];
+    int layer = 0, kind = 0;
+    if (!hf_name_to_kind(en.name, &layer, &kind) || !shard_wants(e, layer, kind)) continue;
+    const int dt = st_dtype_code(en.dtype);
+    if (dt < 0) { rc = xb_fail(1, "%s: tensor %s has unsupported dtype %s (BF16, F16, F32)", path, en.name.c_str(), en.dtype.c_str()); break; }
+    WTarget t;
+    if ((rc = resolve_target(e, layer, kind, &t)) != 0) break;
+    const size_t es = st_dtype_size(dt);
+    long long numel = 1;
+    for (long long x : en.shape) numel *= x;
+    const size_t want_elems = t.want / 2;
+    if ((size_t)numel != want_elems || en.end - en.begin != (size_t)numel * es || en.end > data_size) {
+      rc = xb_fail(1, "%s: tensor %s has %lld elements / %zu bytes, this model wants %zu elements", path, en.name.c_str(), numel,
+                   en.end - en.begin, want_elems);
+      break;
+    }
+    if ((t.tdst != nullptr || t.embed) && (en.shape.size() != 2 || (size_t)en.shape[0] != t.rows || (size_t)en.shape[1] != t.K)) {
+      rc = xb_fail(1, "%s: tensor %s is not [%zu, %zu]", path, en.name.c_str(), t.rows, t.K);
+      break;
+    }
+    const uint8_t* src = data + en.begin;
+    if (t.tdst != nullptr || t.embed) {
+      // matrix: row chunks through the ring; Llama q/k rows are permuted on the way (llm_utils.py:213-231)
+      const int perm = (permute_qk && (kind == XB_W_Q || kind == XB_W_K)) ? d.head_dim : 0;
+      const size_t row_bytes = t.K * es;
+      size_t rows_per = ring.chunk / row_bytes;
+      if (rows_per > 128) rows_per &= ~(size_t)127;
+      if (rows_per == 0) { rc = xb_fail(1, "row of %zu bytes exceeds the loader chunk", row_bytes); break; }
+      if (t.K % 8 != 0) { rc = xb_fail(1, "K=%zu must be a multiple of 8", t.K); break; }
+      for (size_t j0 = 0; rc == 0 && j0 < t.rows; j0 += rows_per) {
+        const size_t nr = j0 + rows_per <= t.rows ? rows_per : t.rows - j0;
+        void* dsrc = nullptr;
+        int bi = 0;
+        if ((rc = ring.stage(src + j0 * row_bytes, nr * row_bytes, &dsrc, &bi)) != 0) break;
+        const long long n = (long long)nr * (long long)(t.K / 8);
+        const unsigned blocks = (unsigned)((n + 255) / 256);
+        if (t.embed) {
+          if (e->embed) xb_load_copy_kernel<<<blocks, 256, 0, ring.st>>>(dsrc, dt, n, e->embed + j0 * t.K);
+          if (e->lm_head && d.tied_head)
+            xb_load_rows_tiled_kernel<<<blocks, 256, 0, ring.st>>>(dsrc, dt, (long long)j0, (long long)nr, (int)t.K, e->lm_head,
+                                                                   (int)((t.K + 63) / 64), 0, 0, 0, 0);
+        } else {
+          xb_load_rows_tiled_kernel<<<blocks, 256, 0, ring.st>>>(dsrc, dt, (long long)j0, (long long)nr, (int)t.K, t.tdst,
+                                                                 (int)((t.K + 63) / 64), (long long)t.row0, t.il, t.il_off, perm);
+        }
+        rc = ring.done(bi);
+      }
+    } else {
+      // vector (norm scale, bias): one small chunk
+      void* dsrc = nullptr;
+      int bi = 0;
+      if ((size_t)numel % 8 != 0) { rc = xb_fail(1, "%s: length of %s must be a multiple of 8", path, en.name.c_str()); break; }
+      if ((rc = ring.stage(src, (size_t)numel * es, &dsrc, &bi)) != 0) break;
+      xb_load_copy_kernel<<<(unsigned)((numel / 8 + 255) / 256), 256, 0, ring.st>>>(dsrc, dt, numel / 8, (bf16*)t.dst);
+      rc = ring.done(bi);
+    }
+    if (rc != 0) break;
+    e->loaded[(long long)(layer + 1) * 64 + kind] = 1;
+    ++count;
+    total += en.end - en.begin;
+  }
+  if (rc == 0) {
+    cudaError_t ce = cudaStreamSynchronize(ring.st);
+    if (ce != cudaSuccess) rc = xb_fail(2, "%s: loader stream failed: %s", path, cudaGetErrorString(ce));
+  }
+  if (rc != 0) {
+    ring.destroy();
+    delete e->ring;
+    e->ring = nullptr;
+    return rc;
+  }
+  e->plans.clear();
+  if (n_tensors) *n_tensors = count;
+  if (n_bytes) *n_bytes = total;
+  return 0;
+}
+
+// Names (ABI kinds) this shard still lacks; 0 in *n_missing = ready.  `buf` receives a readable list.
+extern "C" int xb_weights_missing(xb_engine* e, char* buf, size_t buflen, int* n_missing) {
+  XB_CHECK(e != nullptr && n_missing != nullptr, "null argument");
+  static const char* names[] = {"q_proj", "k_proj", "v_proj", "o_proj", "gate_proj", "up_proj", "down_proj", "input_layernorm",
+                                "post_attention_layernorm", "q_proj.bias", "k_proj.bias", "v_proj.bias", "embed_tokens",
+                                "final norm", "lm_head", "rope table"};
+  std::string out;
+  int n = 0;
+  auto need = [&](int layer, int kind) {
+    if (e->loaded.count((long long)(layer + 1) * 64 + kind)) return;
+    ++n;
+    if (out.size() < 900) out += (layer >= 0 ? "layer " + std::to_string(layer) + " " : std::string()) + names[kind] + "; ";
+  };
+  for (int l = e->d.start_layer; l <= e->d.end_layer; ++l)
+    for (int k = XB_W_Q; k <= XB_W_V_BIAS; ++k)
+      if (shard_wants(e, l, k)) need(l, k);
+  for (int k = XB_W_EMBED; k <= XB_W_LM_HEAD; ++k)
+    if (shard_wants(e, -1, k)) need(-1, k);
+  need(-1, XB_W_ROPE_TABLE);
+  *n_missing = n;
+  if (n == 0 && e->ring != nullptr) {   // complete: the staging buffers are no longer needed
+    e->ring->destroy();
+    delete e->ring;
+    e->ring = nullptr;
+  }
+  if (buf != nullptr && buflen > 0) {
+    strncpy(buf, out.c_str(), buflen - 1);
+    buf[buflen - 1] = 0;
+  }
   return 0;
 }
 

@@ -138,9 +138,36 @@ class StageRuntime:
       if not self.tied:
         self._load(-1, _cabi.W_LM_HEAD, get("lm_head.weight"))
 
-  def load_dir(self, path: Path):
-    idx = _SafetensorsIndex(path)
-    self.load_hf_tensors(idx.get, idx.has)
+  def load_dir(self, path: Path, native: bool = True) -> dict:
+    """Load this shard's layer range from the ``*.safetensors`` files of a checkpoint directory.
+    native=True (default): libxb200 maps each file and streams only this shard's tensors to the
+    device (``xb_load_safetensors``); native=False: through the safetensors Python package and
+    ``load_hf_tensors`` (same result, used to cross-check).  Returns {files, tensors, bytes, seconds}."""
+    import time
+    t0 = time.perf_counter()
+    if not native:
+      idx = _SafetensorsIndex(path)
+      self.load_hf_tensors(idx.get, idx.has)
+      return {"files": len(idx.files), "tensors": None, "bytes": None, "seconds": time.perf_counter() - t0}
+    files = sorted(Path(path).glob("*.safetensors"))
+    if not files:
+      raise FileNotFoundError(f"No safetensors files found in {path}")
+    tensors, nbytes = 0, 0
+    for f in files:
+      n, b = C.c_int(), C.c_uint64()
+      _cabi.check(self.lib.xb_load_safetensors(self._h, str(f).encode(), int(self.family == "llama"), C.byref(n), C.byref(b)))
+      tensors += n.value
+      nbytes += b.value
+    missing = self.weights_missing()
+    if missing:
+      raise RuntimeError(f"checkpoint {path} lacks weights of {self.shard}: {missing}")
+    return {"files": len(files), "tensors": tensors, "bytes": nbytes, "seconds": time.perf_counter() - t0}
+
+  def weights_missing(self) -> str:
+    """Readable list of this shard's weights that have not been supplied yet ('' = complete)."""
+    buf, n = C.create_string_buffer(1024), C.c_int()
+    _cabi.check(self.lib.xb_weights_missing(self._h, buf, 1024, C.byref(n)))
+    return f"{n.value} missing: {buf.value.decode()}" if n.value else ""
 
   def load_state(self, state: Dict[str, torch.Tensor]):
     self.load_hf_tensors(state.__getitem__, state.__contains__)
