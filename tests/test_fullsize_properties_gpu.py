@@ -1,4 +1,4 @@
-"""Size-independent properties at BASELINE.json's full size (Llama-3.1-8B bf16, 2048-token prompt),
+"""Size-independent properties at BASELINE.json's full size (Llama-3.1-8B and Qwen2.5-7B bf16, 2048-token prompt),
 where the CPU oracle is too slow to be the checker:
   * a 2-shard split (layers 0-15 | 16-31, hidden state handed over in bf16) gives EXACTLY the
     full-shard logits and greedy tokens (the reference's contract,
@@ -24,7 +24,8 @@ def _rel(a, b):
   return float((a.float() - b.float()).abs().max() / b.float().abs().max())
 
 
-def test_llama31_8b_properties(built_lib):
+@pytest.mark.parametrize("mid", ["llama-3.1-8b", "qwen-2.5-7b"])
+def test_fullsize_properties(built_lib, mid):
   from xotorch_support_jetson_b200 import model_config as mc
   from xotorch_support_jetson_b200.models import model_cards
   from xotorch_support_jetson_b200.pipeline import gpu_random_getter
@@ -32,17 +33,17 @@ def test_llama31_8b_properties(built_lib):
   from xotorch_support_jetson_b200.stage import StageRuntime
   if torch.cuda.get_device_properties(0).total_memory < 60e9:
     pytest.skip("needs ~40 GB of HBM")
-  mid = "llama-3.1-8b"
   hf = model_cards[mid]["hf_config"]
   with tempfile.TemporaryDirectory() as td:
     (Path(td) / "config.json").write_text(json.dumps(hf))
     cfg = mc.load_model_config(Path(td) / "config.json")
   dev = torch.device("cuda", 0)
-  L, nl = 2048, 32
+  L, nl = 2048, hf["num_hidden_layers"]
+  cut = nl // 2
   kw = dict(device=0, max_batch_tokens=4096, max_seqs=3, max_tokens_per_seq=L + 64)
   full = StageRuntime(Shard(mid, 0, nl - 1, nl), cfg, **kw)
-  s1 = StageRuntime(Shard(mid, 0, 15, nl), cfg, **kw)
-  s2 = StageRuntime(Shard(mid, 16, nl - 1, nl), cfg, **kw)
+  s1 = StageRuntime(Shard(mid, 0, cut - 1, nl), cfg, **kw)
+  s2 = StageRuntime(Shard(mid, cut, nl - 1, nl), cfg, **kw)
   for st in (full, s1, s2):
     st.load_hf_tensors(*gpu_random_getter(hf, 0, 0.02, dev))
   g = torch.Generator(device=dev).manual_seed(4321)
@@ -78,7 +79,7 @@ def test_llama31_8b_properties(built_lib):
       lg_a = full.forward([0], [1], [L + k], tokens=xa)
       lg_b = s2.forward([0], [1], [L + k], hidden=s1.forward([0], [1], [L + k], tokens=xb))
   torch.cuda.synchronize()
-  print(f"\n[8B properties] chunked-vs-one-shot prefill rel err {e_chunk:.4f}; decode-vs-prefill rel err {e_dec:.4f}; "
+  print(f"\n[{mid} properties] chunked-vs-one-shot prefill rel err {e_chunk:.4f}; decode-vs-prefill rel err {e_dec:.4f}; "
         f"tokens full {ta} ring {tb}")
   assert ta == tb
   assert torch.isfinite(lg_full).all() and e_chunk < REL_TOL / 2 and e_dec < 2 * REL_TOL
@@ -111,7 +112,7 @@ def test_llama31_8b_properties(built_lib):
   e = {"prefill": _rel(pre, truth_L), "decode": _rel(dec, truth_L1), "prefill+1": _rel(ext, truth_L1),
        "oracle bf16 L": _rel(ref_L, truth_L), "oracle bf16 L+1": _rel(ref_L1, truth_L1),
        "prefill vs oracle bf16": _rel(pre, ref_L), "decode vs oracle bf16": _rel(dec, ref_L1)}
-  print("[8B vs oracle] rel err to the fp32 evaluation: " + "; ".join(f"{k} {v:.4f}" for k, v in e.items()))
+  print(f"[{mid} vs oracle] rel err to the fp32 evaluation: " + "; ".join(f"{k} {v:.4f}" for k, v in e.items()))
   worst_ref = max(e["oracle bf16 L"], e["oracle bf16 L+1"])
   assert e["prefill"] < 1.5 * worst_ref + 0.005
   assert e["decode"] < 1.5 * worst_ref + 0.005
