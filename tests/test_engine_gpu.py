@@ -436,3 +436,50 @@ def test_fused_decode_reduction_is_bit_identical(built_lib, mid, hf_override, mo
     assert torch.equal(x, y), f"output {i}: fused and separate reductions differ by {float((x - y).abs().max())}"
   a.close()
   b.close()
+
+
+@pytest.mark.parametrize("V", [128256, 152064, 50257, 1000])
+def test_sampler_large_vocab_both_kernels(built_lib, V, monkeypatch):
+  """Real vocabulary sizes (Llama-3 128256, Qwen2.5 152064), one that is not a multiple of 4 and a
+  small one: the 4-block-cluster sampler (row resident in shared memory) and the one-block-per-row
+  kernel (XB_SAMPLE_CLUSTER=0) must both pick the reference's token for the same noise."""
+  import json
+  import tempfile
+  from pathlib import Path
+  from oracle import torch_oracle as O
+  from xotorch_support_jetson_b200 import model_config as mc
+  from xotorch_support_jetson_b200.models import model_cards
+  from xotorch_support_jetson_b200.shard import Shard
+  from xotorch_support_jetson_b200.stage import StageRuntime
+  hf = dict(model_cards["llama-3.2-tiny"]["hf_config"])
+  hf["vocab_size"] = V
+  with tempfile.TemporaryDirectory() as td:
+    (Path(td) / "config.json").write_text(json.dumps(hf))
+    cfg = mc.load_model_config(Path(td) / "config.json")
+  nl = cfg["num_layers"]
+  st = StageRuntime(Shard("llama-3.2-tiny", 0, nl - 1, nl), cfg, device=0, max_batch_tokens=16, max_seqs=8, max_tokens_per_seq=32)
+  g = torch.Generator().manual_seed(V)
+  rows = 5
+  for temp, top_k in ((0.6, 35), (1.0, 5), (1e-5, 35), (0.85, 0), (2.0, 100)):
+    logits = (torch.randn(rows, V, generator=g) * 3).to(torch.bfloat16).float()
+    q = torch.empty(rows, V).exponential_(1, generator=g)
+    ref = O.sample(logits.clone(), temperature=temp, top_k=top_k if top_k else None, q=q).reshape(-1).to(torch.int64)
+    for cluster in ("1", "0"):
+      monkeypatch.setenv("XB_SAMPLE_CLUSTER", cluster)
+      got = st.sample(logits.cuda(), temp=temp, top_k=top_k, q=q.cuda()).cpu().to(torch.int64)
+      assert torch.equal(got, ref), (V, temp, top_k, cluster, got, ref)
+  # nucleus + counter noise: both kernels use the same noise function, so they agree with each other,
+  # and the draw lies inside the nucleus
+  logits = (torch.randn(rows, V, generator=g) * 2).float()
+  probs = torch.softmax(logits / 0.9, -1)
+  sp, si = probs.sort(-1, descending=True)
+  cut = (sp.cumsum(-1) - sp) < 0.7
+  for seed in range(3):
+    picks = []
+    for cluster in ("1", "0"):
+      monkeypatch.setenv("XB_SAMPLE_CLUSTER", cluster)
+      picks.append(st.sample(logits.cuda(), temp=0.9, top_k=0, top_p=0.7, seed=seed).cpu().to(torch.int64))
+    assert torch.equal(picks[0], picks[1]), (V, seed, picks)
+    for r in range(rows):
+      assert picks[0][r].item() in set(si[r][cut[r]].tolist())
+  st.close()

@@ -6,6 +6,7 @@
 #include "xb_loader.cuh"
 #include "xb_kernels.cuh"
 #include "xb_attn_mma.cuh"
+#include "xb_sample_cluster.cuh"
 
 #include <stdarg.h>
 #include <stdlib.h>
@@ -1125,7 +1126,36 @@ extern "C" int xb_sample(xb_engine* e, const float* logits, int n, float temp, i
   if (temp <= 0.f) {
     xb_argmax_kernel<1024><<<n, 1024, 0, st>>>(logits, e->d.vocab, tokens_out);
   } else {
-    xb_sample_kernel<1024><<<n, 1024, 0, st>>>(logits, e->d.vocab, temp, top_k, top_p, q, (unsigned long long)seed, tokens_out);
+    // a cluster of 4 blocks per row keeps the row in shared memory (xb_sample_cluster.cuh); rows too long
+    // for 4 x 200 KB, or XB_SAMPLE_CLUSTER=0, take the one-block-per-row kernel
+    constexpr int CL = 4;
+    const int V = e->d.vocab;
+    const int chunk = (((V + CL - 1) / CL) + 3) & ~3;
+    const char* cv = getenv("XB_SAMPLE_CLUSTER");
+    const bool use_cluster = !(cv != nullptr && cv[0] == '0');
+    if (use_cluster && (size_t)chunk * 4 <= (size_t)200 * 1024) {
+      static bool attr_set = false;
+      if (!attr_set) {
+        XB_CUDA(cudaFuncSetAttribute(xb_sample_cluster_kernel<1024, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr_set = true;
+      }
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(n * CL);
+      cfg.blockDim = dim3(1024);
+      cfg.dynamicSmemBytes = (size_t)chunk * 4;
+      cfg.stream = st;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = CL;
+      attr[0].val.clusterDim.y = 1;
+      attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr;
+      cfg.numAttrs = 1;
+      XB_CUDA(cudaLaunchKernelEx(&cfg, xb_sample_cluster_kernel<1024, CL>, logits, V, chunk, temp, top_k, top_p, q,
+                                 (unsigned long long)seed, (int*)tokens_out));
+    } else {
+      xb_sample_kernel<1024><<<n, 1024, 0, st>>>(logits, V, temp, top_k, top_p, q, (unsigned long long)seed, tokens_out);
+    }
   }
   XB_CUDA(cudaGetLastError());
   LAUNCH_COUNT(e);

@@ -453,6 +453,32 @@ __device__ __forceinline__ uint32_t mix32(uint64_t x) {
   return (uint32_t)(x >> 11);
 }
 
+// f(i, v) for every element of a row, one block per row.  A 128 K-entry fp32 row is read from L2 by a
+// single SM, so the loop is latency bound unless many loads are in flight: four float4 loads per
+// thread per trip (64 B x 1024 threads) instead of one scalar.  (Even so one SM pulls only ~40 GB/s of
+// a row out of L2 -- ~14 us per pass over 128256 logits -- which is why the sampler proper keeps its
+// slice of the row in shared memory across passes, xb_sample_cluster.cuh.)
+template <int NT, typename F>
+__device__ __forceinline__ void row_for_each(const float* __restrict__ row, int V, F&& f) {
+  if ((V & 3) == 0 && (reinterpret_cast<uintptr_t>(row) & 15) == 0) {
+    const float4* r4 = reinterpret_cast<const float4*>(row);
+    const int n4 = V >> 2;
+    int i = threadIdx.x;
+    for (; i + 3 * NT < n4; i += 4 * NT) {
+      const float4 a = r4[i], b = r4[i + NT], c = r4[i + 2 * NT], d = r4[i + 3 * NT];
+      f(4 * i, a.x); f(4 * i + 1, a.y); f(4 * i + 2, a.z); f(4 * i + 3, a.w);
+      f(4 * (i + NT), b.x); f(4 * (i + NT) + 1, b.y); f(4 * (i + NT) + 2, b.z); f(4 * (i + NT) + 3, b.w);
+      f(4 * (i + 2 * NT), c.x); f(4 * (i + 2 * NT) + 1, c.y); f(4 * (i + 2 * NT) + 2, c.z); f(4 * (i + 2 * NT) + 3, c.w);
+      f(4 * (i + 3 * NT), d.x); f(4 * (i + 3 * NT) + 1, d.y); f(4 * (i + 3 * NT) + 2, d.z); f(4 * (i + 3 * NT) + 3, d.w);
+    }
+    for (; i < n4; i += NT) {
+      const float4 a = r4[i];
+      f(4 * i, a.x); f(4 * i + 1, a.y); f(4 * i + 2, a.z); f(4 * i + 3, a.w);
+    }
+  } else {
+    for (int i = threadIdx.x; i < V; i += NT) f(i, row[i]);
+  }
+}
 // first-index argmax of each row (greedy): one block per row
 template <int NT>
 __global__ void __launch_bounds__(NT) xb_argmax_kernel(const float* __restrict__ logits, int V, int* __restrict__ out) {
@@ -461,10 +487,9 @@ __global__ void __launch_bounds__(NT) xb_argmax_kernel(const float* __restrict__
   const float* row = logits + (long long)blockIdx.x * V;
   float best = -INFINITY;
   int bi = 0x7fffffff;
-  for (int i = threadIdx.x; i < V; i += NT) {
-    const float v = row[i];
+  row_for_each<NT>(row, V, [&](int i, float v) {
     if (v > best || (v == best && i < bi)) { best = v; bi = i; }
-  }
+  });
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     const float ov = __shfl_xor_sync(0xffffffffu, best, o);
@@ -511,10 +536,10 @@ __global__ void __launch_bounds__(NT) xb_sample_kernel(const float* __restrict__
       for (int i = threadIdx.x; i < 256; i += NT) hist[i] = 0;
       __syncthreads();
       const uint32_t mask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
-      for (int i = threadIdx.x; i < V; i += NT) {
-        const uint32_t key = float_order_key(row[i] * inv_t);
+      row_for_each<NT>(row, V, [&](int, float x) {
+        const uint32_t key = float_order_key(x * inv_t);
         if ((key & mask) == (prefix & mask)) atomicAdd(&hist[(key >> shift) & 255], 1u);
-      }
+      });
       __syncthreads();
       if (threadIdx.x == 0) {
         int n = need;
@@ -537,10 +562,10 @@ __global__ void __launch_bounds__(NT) xb_sample_kernel(const float* __restrict__
 
   // ---- 2. softmax statistics over kept values (logits >= pivot)
   float mxv = -INFINITY;
-  for (int i = threadIdx.x; i < V; i += NT) {
-    const float v = row[i] * inv_t;
+  row_for_each<NT>(row, V, [&](int, float x) {
+    const float v = x * inv_t;
     if (v >= pivot) mxv = fmaxf(mxv, v);
-  }
+  });
   mxv = warp_max(mxv);
   if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = mxv;
   __syncthreads();
@@ -548,10 +573,10 @@ __global__ void __launch_bounds__(NT) xb_sample_kernel(const float* __restrict__
   for (int w = 1; w < NT / 32; ++w) mxv = fmaxf(mxv, red[w]);
   __syncthreads();
   float sum = 0.f;
-  for (int i = threadIdx.x; i < V; i += NT) {
-    const float v = row[i] * inv_t;
+  row_for_each<NT>(row, V, [&](int, float x) {
+    const float v = x * inv_t;
     if (v >= pivot) sum += expf(v - mxv);
-  }
+  });
   sum = block_sum<NT>(sum, red);
 
   // ---- 2b. nucleus: largest probability threshold whose upper set has mass >= top_p
@@ -564,14 +589,14 @@ __global__ void __launch_bounds__(NT) xb_sample_kernel(const float* __restrict__
       for (int i = threadIdx.x; i < 256; i += NT) fhist[i] = 0.f;
       __syncthreads();
       const uint32_t mask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
-      for (int i = threadIdx.x; i < V; i += NT) {
-        const float v = row[i] * inv_t;
+      row_for_each<NT>(row, V, [&](int, float x) {
+        const float v = x * inv_t;
         if (v >= pivot) {
           const float e = expf(v - mxv);
           const uint32_t key = float_order_key(e);
           if ((key & mask) == (prefix & mask)) atomicAdd(&fhist[(key >> shift) & 255], e);
         }
-      }
+      });
       __syncthreads();
       if (threadIdx.x == 0) {
         float n = needf;
@@ -594,11 +619,11 @@ __global__ void __launch_bounds__(NT) xb_sample_kernel(const float* __restrict__
   // ---- 3. argmax(p / q)
   float best = -INFINITY;
   int bi = 0x7fffffff;
-  for (int i = threadIdx.x; i < V; i += NT) {
-    const float v = row[i] * inv_t;
-    if (v < pivot) continue;
+  row_for_each<NT>(row, V, [&](int i, float x) {
+    const float v = x * inv_t;
+    if (v < pivot) return;
     const float e = expf(v - mxv);
-    if (e < p_cut) continue;
+    if (e < p_cut) return;
     float qv;
     if (q_noise != nullptr) {
       qv = q_noise[(long long)rowi * V + i];
@@ -609,7 +634,7 @@ __global__ void __launch_bounds__(NT) xb_sample_kernel(const float* __restrict__
     }
     const float sc = (e / sum) / qv;
     if (sc > best || (sc == best && i < bi)) { best = sc; bi = i; }
-  }
+  });
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     const float ov = __shfl_xor_sync(0xffffffffu, best, o);
