@@ -134,6 +134,14 @@ int xb_kv_slot_len(xb_engine* e, int slot, int* len);
  * receive the residual stream after each layer (parity instrumentation). */
 int xb_forward(xb_engine* e, const xb_batch* batch, void* out, void* const* taps, void* stream);
 
+/* xb_forward on a last shard whose logits must reach the host every step, as the plugin API
+ * requires (infer_tensor returns them as a numpy array, sharded_inference_engine.py:361-367:
+ * `.float().numpy(force=True)` = a blocking device-to-host copy after the forward).  The LM-head
+ * kernel stores the fp32 [n_seqs, vocab] logits into `host_logits` (page-locked, device-addressable
+ * host memory) from its own epilogue while it streams the weights, in addition to the device copy
+ * in `out` (may be NULL); they are complete when the work enqueued on `stream` has finished. */
+int xb_forward_host_logits(xb_engine* e, const xb_batch* batch, void* out, float* host_logits, void* stream);
+
 /* Intra-box hand-off between pipeline stages over NVLink peer memory, replacing the per-token gRPC
  * SendTensor hop of the reference (Node.forward_tensor, xotorch/orchestration/node.py:424-443;
  * GRPCPeerHandle.send_tensor, xotorch/networking/grpc/grpc_peer_handle.py:117-136) for decode steps.

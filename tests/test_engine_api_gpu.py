@@ -252,3 +252,52 @@ def test_generate_device_loop_equals_stepwise_calls(built_lib, tmp_path):
       await b.generate("x", Shard(mid, 0, 1, nl), prompt, max_generate_tokens=2)
 
   asyncio.run(run())
+
+
+def test_lm_head_writes_host_logits_directly(built_lib, tmp_path, monkeypatch):
+  """xb_forward_host_logits: the LM-head kernel stores the logits into pinned host memory from its
+  epilogue.  Same bits as the device copy, at stage level (prefill, eager and graph-replayed decode,
+  ragged batch) and through the plugin API with the path on and off."""
+  from xotorch_support_jetson_b200.shard import Shard
+  mid, nl = "llama-3.2-tiny", 4
+  sh = Shard(mid, 0, nl - 1, nl)
+  rs = np.random.RandomState(3)
+  prompt = rs.randint(3, 200, (3, 13)).astype(np.int64)
+
+  async def run():
+    monkeypatch.setenv("XB_API_DIRECT_LOGITS", "1")
+    a = _engine(tmp_path, speculate_next=False)
+    monkeypatch.setenv("XB_API_DIRECT_LOGITS", "0")
+    b = _engine(tmp_path, speculate_next=False)
+    assert a.direct_host_logits and not b.direct_host_logits
+    la, sa = await a.infer_tensor("r", sh, prompt, None)
+    lb, sb = await b.infer_tensor("r", sh, prompt, None)
+    assert np.array_equal(la, lb) and la.dtype == np.float32 and la.shape == (3, a.stage.vocab)
+    for _ in range(5):
+      ta, tb = await a.sample(la, temp=0.0), await b.sample(lb, temp=0.0)
+      assert np.array_equal(ta, tb)
+      la, sa = await a.infer_tensor("r", sh, ta, sa)
+      lb, sb = await b.infer_tensor("r", sh, tb, sb)
+      assert np.array_equal(la, lb)
+    # stage level: host buffer == device result, ragged decode batch
+    st = a.stage
+    with torch.cuda.stream(torch.cuda.Stream()):
+      host = torch.empty((3, st.vocab), dtype=torch.float32).pin_memory()
+      slots = a.requests["r"].slots
+      pos = a.requests["r"].pos
+      tok = torch.tensor([5, 6, 7], dtype=torch.int32, device="cuda")
+      for k in range(3):   # eager, capture, replay
+        dev = st.forward(slots, [1, 1, 1], [pos + k] * 3, tokens=tok, host_logits=host)
+        torch.cuda.current_stream().synchronize()
+        assert torch.equal(dev.cpu(), host)
+    with pytest.raises(RuntimeError, match="page-locked"):
+      st.lib.xb_forward_host_logits.restype = __import__("ctypes").c_int
+      bad = torch.empty((3, st.vocab), dtype=torch.float32)
+      object.__setattr__(bad, "_fake", True)
+      import ctypes as C
+      from xotorch_support_jetson_b200 import _cabi
+      arr = (C.c_int32 * 3)
+      bt = _cabi.Batch(n_seqs=3, slot_ids=arr(*slots), q_lens=arr(1, 1, 1), positions=arr(pos, pos, pos), tokens=tok.data_ptr(), hidden_in=None)
+      _cabi.check(st.lib.xb_forward_host_logits(st._h, C.byref(bt), None, C.c_void_p(bad.data_ptr()), None))
+
+  asyncio.run(run())

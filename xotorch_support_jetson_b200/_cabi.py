@@ -11,7 +11,7 @@ _LIB_NAME = "libxb200.so"
 SYMBOLS = (
   "xb_last_error", "xb_abi_version", "xb_engine_create", "xb_engine_destroy", "xb_load_weight",
   "xb_load_safetensors", "xb_weights_missing",
-  "xb_kv_reserve", "xb_kv_release_slot", "xb_kv_slot_len", "xb_forward", "xb_sample",
+  "xb_kv_reserve", "xb_kv_release_slot", "xb_kv_slot_len", "xb_forward", "xb_forward_host_logits", "xb_sample",
   "xb_handoff_create", "xb_handoff_connect", "xb_forward_handoff",
   "xb_get_counters", "xb_debug_linear", "xb_bench_linears", "xb_bench_attention", "xb_linear_noalloc",
 )
@@ -78,6 +78,7 @@ def load():
   lib.xb_kv_release_slot.argtypes = [C.c_void_p, C.c_int]
   lib.xb_kv_slot_len.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int)]
   lib.xb_forward.argtypes = [C.c_void_p, C.POINTER(Batch), C.c_void_p, C.POINTER(C.c_void_p), C.c_void_p]
+  lib.xb_forward_host_logits.argtypes = [C.c_void_p, C.POINTER(Batch), C.c_void_p, C.c_void_p, C.c_void_p]
   lib.xb_handoff_create.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
   lib.xb_handoff_connect.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
   lib.xb_forward_handoff.argtypes = [C.c_void_p, C.POINTER(Batch), C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]

@@ -88,6 +88,7 @@ class B200ShardInferenceEngine(InferenceEngine):
     self._pin_rings: Dict[torch.dtype, list] = {}   # dtype -> [buffers, next index]
     self._last_logits = None   # (numpy view handed to the caller, device tensor it mirrors, request id)
     self.speculate_next = (env.get("XB_API_SPECULATE", "1") != "0") if speculate_next is None else bool(speculate_next)
+    self.direct_host_logits = env.get("XB_API_DIRECT_LOGITS", "1") != "0"   # LM head stores the logits into pinned host memory itself
     self._spec = None          # the decode forward enqueued ahead of the caller's infer_tensor, see sample()
     self.spec_hits = self.spec_misses = 0
 
@@ -166,19 +167,42 @@ class B200ShardInferenceEngine(InferenceEngine):
     """Device tensor -> numpy through a pinned ring buffer (one DMA, no pageable bounce).  The
     returned array is a read-only view that stays valid for the next PIN_RING-1 results; its
     contents are defined once the returned event has completed."""
-    n = dev.numel()
-    ring = self._pin_rings.get(dev.dtype)
-    if ring is None or ring[0][0].numel() < n:
-      ring = [[torch.empty(max(n, 1), dtype=dev.dtype).pin_memory() for _ in range(self.PIN_RING)], 0]
-      self._pin_rings[dev.dtype] = ring
-    buf = ring[0][ring[1]][:n].view(dev.shape)
-    ring[1] = (ring[1] + 1) % self.PIN_RING
+    buf = self._ring_buffer(dev.dtype, dev.shape)
     buf.copy_(dev, non_blocking=True)
     ev = torch.cuda.Event()
     ev.record(torch.cuda.current_stream(dev.device))
     arr = buf.numpy()
     arr.setflags(write=False)
     return arr, ev
+
+  def _ring_buffer(self, dtype: torch.dtype, shape) -> torch.Tensor:
+    """Next pinned host buffer of the ring for this dtype, viewed as ``shape``."""
+    n = 1
+    for d in shape:
+      n *= int(d)
+    ring = self._pin_rings.get(dtype)
+    if ring is None or ring[0][0].numel() < n:
+      ring = [[torch.empty(max(n, 1), dtype=dtype).pin_memory() for _ in range(self.PIN_RING)], 0]
+      self._pin_rings[dtype] = ring
+    buf = ring[0][ring[1]][:n].view(tuple(shape))
+    ring[1] = (ring[1] + 1) % self.PIN_RING
+    return buf
+
+  def _forward_logits(self, st: StageRuntime, slots, q_lens, positions, **inp):
+    """One native forward on a last shard whose logits go to the host: (device logits, numpy
+    view, event).  With ``direct_host_logits`` the LM-head kernel stores them into the pinned ring
+    buffer itself (xb_forward_host_logits); otherwise a device-to-host copy follows the forward."""
+    if not self.direct_host_logits:
+      out = st.forward(slots, q_lens, positions, **inp)
+      host, ev = self._to_host_async(out)
+      return out, host, ev
+    buf = self._ring_buffer(torch.float32, (len(slots), st.vocab))
+    out = st.forward(slots, q_lens, positions, host_logits=buf, **inp)
+    ev = torch.cuda.Event()
+    ev.record(torch.cuda.current_stream(st.device))
+    arr = buf.numpy()
+    arr.setflags(write=False)
+    return out, arr, ev
 
   # ------------------------------------------------------------------ sampling
   async def sample(self, x: np.ndarray, temp=TEMP, top_k=TOP_K, top_p: float = 0.0) -> np.ndarray:
@@ -223,10 +247,9 @@ class B200ShardInferenceEngine(InferenceEngine):
     if req is None or len(req.slots) != toks.numel() or req.pos + 1 > st.max_tokens_per_seq or len(req.slots) > st.max_batch_tokens:
       return
     try:
-      out = st.forward(req.slots, [1] * len(req.slots), [req.pos] * len(req.slots), tokens=toks)
+      out, host, ev = self._forward_logits(st, req.slots, [1] * len(req.slots), [req.pos] * len(req.slots), tokens=toks)
     except RuntimeError:
       return   # e.g. KV pool exhausted: the real call will report it
-    host, ev = self._to_host_async(out)
     self._spec = {"request_id": request_id, "pos": req.pos, "toks": host_toks, "out": out, "host": host, "event": ev}
 
   def _take_spec(self, request_id: str, pos: int, x: np.ndarray):
@@ -275,7 +298,7 @@ class B200ShardInferenceEngine(InferenceEngine):
         self.free_slots.append(s)
 
   def _forward_chunked(self, st: StageRuntime, req: _Request, dev_in: torch.Tensor, bsz: int, s: int, pos: int,
-                       is_tokens: bool) -> torch.Tensor:
+                       is_tokens: bool, to_host: bool = True):
     """One logical forward over [bsz, s] rows, split so that no native call carries more
     than max_batch_tokens rows: whole sequences per call, or position chunks of one
     sequence (chunked prefill) when a single sequence is longer than that."""
@@ -283,7 +306,10 @@ class B200ShardInferenceEngine(InferenceEngine):
     last = self.shard.is_last_layer()
     if bsz * s <= cap:
       flat = dev_in.reshape(-1) if is_tokens else dev_in.reshape(bsz * s, -1)
-      return st.forward(req.slots, [s] * bsz, [pos] * bsz, **({"tokens": flat} if is_tokens else {"hidden": flat}))
+      inp = {"tokens": flat} if is_tokens else {"hidden": flat}
+      if last and to_host:
+        return self._forward_logits(st, req.slots, [s] * bsz, [pos] * bsz, **inp)   # (device logits, host view, event)
+      return st.forward(req.slots, [s] * bsz, [pos] * bsz, **inp)
     outs = []
     if s <= cap:
       per = max(1, cap // s)
@@ -343,6 +369,8 @@ class B200ShardInferenceEngine(InferenceEngine):
       if x.ndim == 3:
         dev_in = torch.as_tensor(np.ascontiguousarray(x, dtype=np.float32)).to(st.device, non_blocking=True).to(torch.bfloat16)
       out = self._forward_chunked(st, req, dev_in, bsz, s, pos, x.ndim == 2)
+      if isinstance(out, tuple):
+        return finish(req, out[0], out[1], out[2], bsz, s, pos)
       return finish(req, out, None, None, bsz, s, pos)
 
     def finish(req, out, host, ev, bsz, s, pos):
@@ -409,7 +437,7 @@ class B200ShardInferenceEngine(InferenceEngine):
         for row, t in zip(req.tokens, x[:, 0].tolist()):
           row.append(int(t))
       dev_in = torch.as_tensor(np.ascontiguousarray(x, dtype=np.int32)).to(st.device, non_blocking=True)
-      logits = self._forward_chunked(st, req, dev_in, bsz, s, pos, True)
+      logits = self._forward_chunked(st, req, dev_in, bsz, s, pos, True, to_host=False)
       pos += s
       # id n is drawn from the forward at position pos+n-2, which must exist in the KV slot
       cap = max(1, min(int(max_generate_tokens), st.max_tokens_per_seq - pos + 1))

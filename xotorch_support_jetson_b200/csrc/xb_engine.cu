@@ -760,8 +760,30 @@ static int choose_kv_splits(xb_engine* e, int T, int max_ctx) {
 // e->h (other shards); leaves the residual stream in e->h and, on a last shard, the logits
 // of each sequence's last position in e->logits.  Pure stream work on fixed addresses, so it
 // can be captured into a CUDA graph.
+// LM head on the last position of each sequence (the final norm is fused into the last layer's
+// residual kernel).  host_logits != nullptr: the Linear's epilogue ALSO stores the fp32 logits
+// straight into that pinned host buffer -- for the plugin API, which has to hand them to the host
+// every step: stores over PCIe (~51 GB/s measured) while the weights stream, instead of a D2H
+// copy (~54 GB/s) that can only start when the kernel has finished.
+static int run_head(xb_engine* e, int n_seqs, cudaStream_t st, float* host_logits) {
+  const xb_model_desc& d = e->d;
+  const int D = d.dim;
+  XB_TRY(launch_k(e, xb_gather_rows_kernel, dim3(n_seqs), dim3(256), 0, st, 1, e->hn, e->d_seq_last, e->last_rows, D));
+  const GemmPlan* gp;
+  XB_TRY(get_plan(e, SITE_HEAD, 0, e->last_rows, D, e->lm_head, n_seqs, d.vocab, D, e->logits, d.vocab, nullptr, 1, &gp));
+  if (host_logits != nullptr) {
+    GemmPlan p = *gp;
+    p.args.out2 = host_logits;
+    XB_TRY(xb_gemm_run(p, st, e->use_pdl));
+  } else {
+    XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
+  }
+  LAUNCH_COUNT(e);
+  return 0;
+}
+
 static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, void* const* taps, cudaStream_t st,
-                    int ho_in = 0, int ho_out = 0) {
+                    int ho_in = 0, int ho_out = 0, int with_head = 1) {
   const xb_model_desc& d = e->d;
   const bool first = d.start_layer == 0, last = d.end_layer == d.n_layers - 1;
   BatchMeta m;
@@ -834,19 +856,12 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
       XB_CUDA(cudaMemcpyAsync(taps[l], e->h, (size_t)T * D * 2, cudaMemcpyDeviceToDevice, st));
   }
 
-  if (last) {
-    // final norm was fused above; LM head on the last position of each sequence only
-    XB_TRY(launch_k(e, xb_gather_rows_kernel, dim3(n_seqs), dim3(256), 0, st, 1, e->hn, e->d_seq_last, e->last_rows, D));
-    const bf16* head = e->lm_head;
-    const GemmPlan* gp;
-    XB_TRY(get_plan(e, SITE_HEAD, 0, e->last_rows, D, head, n_seqs, d.vocab, D, e->logits, d.vocab, nullptr, 1, &gp));
-    XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
-    LAUNCH_COUNT(e);
-  }
+  if (last && with_head) XB_TRY(run_head(e, n_seqs, st, nullptr));
   return 0;
 }
 
-static int forward_impl(xb_engine* e, const xb_batch* b, void* out, void* const* taps, void* stream, const int* ctl) {
+static int forward_impl(xb_engine* e, const xb_batch* b, void* out, void* const* taps, void* stream, const int* ctl,
+                        float* host_logits = nullptr) {
   XB_CHECK(e != nullptr && b != nullptr, "null argument");
   const int ho_in = ctl != nullptr && ctl[0] >= 0, ho_out = ctl != nullptr && ctl[2] >= 0;
   const xb_model_desc& d = e->d;
@@ -960,13 +975,15 @@ static int forward_impl(xb_engine* e, const xb_batch* b, void* out, void* const*
   if (decode_only && e->use_graphs && taps == nullptr && st != nullptr && st != cudaStreamLegacy) {
     // decode step: replay a captured graph (first call of a shape runs eagerly to build the
     // launch plans and set kernel attributes, second call captures)
-    const long long key = ((long long)b->n_seqs << 16) | (n_splits << 2) | (ho_in << 1) | ho_out;
+    // host_logits: the head runs after the graph (its host pointer changes from call to call)
+    const int headless = host_logits != nullptr && last;
+    const long long key = ((long long)b->n_seqs << 16) | (n_splits << 3) | (headless << 2) | (ho_in << 1) | ho_out;
     xb_engine::StepGraph& sg = e->graphs[key];
     if (sg.exec == nullptr && sg.warmed) {
       cudaGraph_t graph = nullptr;
       const uint64_t before = e->c.launches;
       XB_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-      const int rc = run_body(e, T, b->n_seqs, n_splits, 0, nullptr, st, ho_in, ho_out);
+      const int rc = run_body(e, T, b->n_seqs, n_splits, 0, nullptr, st, ho_in, ho_out, !headless);
       cudaError_t ce = cudaStreamEndCapture(st, &graph);
       if (rc != 0) { if (graph) cudaGraphDestroy(graph); return rc; }
       XB_CUDA(ce);
@@ -979,11 +996,14 @@ static int forward_impl(xb_engine* e, const xb_batch* b, void* out, void* const*
       XB_CUDA(cudaGraphLaunch(sg.exec, st));
       e->c.launches += sg.launches;
     } else {
-      XB_TRY(run_body(e, T, b->n_seqs, n_splits, 0, nullptr, st, ho_in, ho_out));
+      XB_TRY(run_body(e, T, b->n_seqs, n_splits, 0, nullptr, st, ho_in, ho_out, !headless));
       sg.warmed = 1;
     }
+    if (headless) XB_TRY(run_head(e, b->n_seqs, st, host_logits));
   } else {
-    XB_TRY(run_body(e, T, b->n_seqs, n_splits, n_tiles, taps, st, ho_in, ho_out));
+    const int headless = host_logits != nullptr && last;
+    XB_TRY(run_body(e, T, b->n_seqs, n_splits, n_tiles, taps, st, ho_in, ho_out, !headless));
+    if (headless) XB_TRY(run_head(e, b->n_seqs, st, host_logits));
   }
 
   if (out != nullptr && !(ho_out && !last)) {
@@ -996,6 +1016,15 @@ static int forward_impl(xb_engine* e, const xb_batch* b, void* out, void* const*
 
 extern "C" int xb_forward(xb_engine* e, const xb_batch* b, void* out, void* const* taps, void* stream) {
   return forward_impl(e, b, out, taps, stream, nullptr);
+}
+
+extern "C" int xb_forward_host_logits(xb_engine* e, const xb_batch* b, void* out, float* host_logits, void* stream) {
+  XB_CHECK(e != nullptr && host_logits != nullptr, "null argument");
+  XB_CHECK(e->d.end_layer == e->d.n_layers - 1, "xb_forward_host_logits needs a last shard (it produces logits)");
+  cudaPointerAttributes pa;
+  XB_CHECK(cudaPointerGetAttributes(&pa, host_logits) == cudaSuccess && pa.type == cudaMemoryTypeHost && pa.devicePointer != nullptr,
+           "host_logits must be page-locked host memory the device can address (cudaHostAlloc / torch pin_memory)");
+  return forward_impl(e, b, out, nullptr, stream, nullptr, (float*)pa.devicePointer);
 }
 
 extern "C" int xb_forward_handoff(xb_engine* e, const xb_batch* b, int slot_in, int wait_value, int slot_out, int signal_value,

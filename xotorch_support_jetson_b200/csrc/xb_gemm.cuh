@@ -57,6 +57,7 @@ struct GemmArgs {
   int* tile_ctr;           // [a_tiles], zero between launches (the last arriver resets its entry)
   void* fin_out;           // XB_EPI_SILU: bf16 act[t][fin_ld]
   long long fin_ld;
+  float* out2;             // SKINNY: second copy of the result (same layout as `out`), e.g. pinned host memory
 };
 enum { XB_EPI_PLAIN = 0, XB_EPI_QKV = 1, XB_EPI_SILU = 2 };
 
@@ -514,6 +515,7 @@ xb_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
                 float x = __uint_as_float(v[j]);
                 if (g.round_bf16) x = rbf(x);
                 out[((long long)s * g.b_rows + t) * g.ld_out + arow] = x;
+                if (g.out2 != nullptr) g.out2[((long long)s * g.b_rows + t) * g.ld_out + arow] = x;
               }
             }
           }
@@ -694,6 +696,7 @@ static int xb_gemm_plan(GemmPlan* p, const bf16* x, long long ldx, const bf16* w
   g.tile_ctr = nullptr;
   g.fin_out = nullptr;
   g.fin_ld = 0;
+  g.out2 = nullptr;
   const long long w_tiles = (N + 127) / 128;
   if (T <= 128) {
     const int bn = xb_pick_bn_skinny(T);

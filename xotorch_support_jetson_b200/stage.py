@@ -176,9 +176,11 @@ class StageRuntime:
   def forward(self, slot_ids: Sequence[int], q_lens: Sequence[int], positions: Sequence[int],
               tokens: Optional[torch.Tensor] = None, hidden: Optional[torch.Tensor] = None,
               out: Optional[torch.Tensor] = None, taps: Optional[List[torch.Tensor]] = None,
-              handoff: Optional[tuple] = None) -> Optional[torch.Tensor]:
+              handoff: Optional[tuple] = None, host_logits: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
     """tokens: int32 [T] (first shard) / hidden: bf16 [T, D].  Returns bf16 [T, D] hidden
-    or fp32 [n_seqs, V] logits (last shard).  Enqueued on the current torch stream."""
+    or fp32 [n_seqs, V] logits (last shard).  Enqueued on the current torch stream.
+    host_logits (last shard): pinned fp32 [n_seqs, V] CPU tensor the LM-head kernel also stores the
+    logits into (xb_forward_host_logits); valid once the stream has reached this point."""
     n = len(slot_ids)
     T = int(sum(q_lens))
     arr = (C.c_int32 * n)
@@ -206,6 +208,11 @@ class StageRuntime:
       _cabi.check(self.lib.xb_forward_handoff(self._h, C.byref(b), int(handoff[0]), int(handoff[1]), int(handoff[2]),
                                               int(handoff[3]), optr, C.c_void_p(stream)))
       return None if sends else out
+    if host_logits is not None:
+      assert taps is None and host_logits.dtype == torch.float32 and host_logits.is_pinned() and host_logits.is_contiguous() \
+        and host_logits.numel() >= n * self.vocab
+      _cabi.check(self.lib.xb_forward_host_logits(self._h, C.byref(b), optr, C.c_void_p(host_logits.data_ptr()), C.c_void_p(stream)))
+      return out
     _cabi.check(self.lib.xb_forward(self._h, C.byref(b), optr, tap_ptrs, C.c_void_p(stream)))
     return out
 
