@@ -24,8 +24,13 @@ def _rel(a, b):
   return float((a.float() - b.float()).abs().max() / b.float().abs().max())
 
 
-@pytest.mark.parametrize("mid", ["llama-3.1-8b", "qwen-2.5-7b"])
-def test_fullsize_properties(built_lib, mid):
+@pytest.mark.parametrize("mid,n_layers", [
+  ("llama-3.1-8b", None), ("qwen-2.5-7b", None),
+  ("llama-3.2-1b", None),     # tied head, head_dim 64
+  ("llama-3.2-3b", None),     # tied head, 3 query heads per kv head
+  ("llama-3.1-70b", 8),       # 70B geometry (D 8192, 8 query heads per kv head, I 28672), first 8 layers as the model
+])
+def test_fullsize_properties(built_lib, mid, n_layers):
   from xotorch_support_jetson_b200 import model_config as mc
   from xotorch_support_jetson_b200.models import model_cards
   from xotorch_support_jetson_b200.pipeline import gpu_random_getter
@@ -33,7 +38,9 @@ def test_fullsize_properties(built_lib, mid):
   from xotorch_support_jetson_b200.stage import StageRuntime
   if torch.cuda.get_device_properties(0).total_memory < 60e9:
     pytest.skip("needs ~40 GB of HBM")
-  hf = model_cards[mid]["hf_config"]
+  hf = dict(model_cards[mid]["hf_config"])
+  if n_layers is not None:
+    hf["num_hidden_layers"] = n_layers
   with tempfile.TemporaryDirectory() as td:
     (Path(td) / "config.json").write_text(json.dumps(hf))
     cfg = mc.load_model_config(Path(td) / "config.json")
