@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define XB_ABI_VERSION 1
+#define XB_ABI_VERSION 2
 
 typedef struct xb_engine xb_engine;
 
@@ -51,6 +51,13 @@ typedef struct xb_model_desc {
   int32_t max_positions;     /* rows of the RoPE table uploaded with XB_W_ROPE_TABLE */
   int32_t max_batch_tokens;  /* most token rows one xb_forward call may carry */
   int32_t max_seqs;          /* most sequences one xb_forward call may carry */
+  /* Half-layer stage boundaries (no counterpart in the reference, whose Shard is whole layers): a
+   * pipeline stage may begin at the MLP block of start_layer (its attention block ran on the previous
+   * stage) and/or end after the attention block of end_layer.  The residual stream is what crosses
+   * the boundary, as between whole layers.  Lets a ring of GPUs balance layers + LM head to half a
+   * layer.  A stage with first_from_mlp is never a first shard (no embedding), one with last_to_attn
+   * never a last shard (no final norm / head). */
+  int32_t first_from_mlp, last_to_attn;
 } xb_model_desc;
 
 /* Weight slots.  Row order is the reference's torchtune layout AFTER its HF->torchtune

@@ -483,3 +483,64 @@ def test_sampler_large_vocab_both_kernels(built_lib, V, monkeypatch):
     for r in range(rows):
       assert picks[0][r].item() in set(si[r][cut[r]].tolist())
   st.close()
+
+
+@pytest.mark.parametrize("mid", ["llama-3.1-tiny", "qwen-2.5-tiny"])
+def test_half_layer_stage_boundaries_are_exact(built_lib, mid, tmp_path):
+  """Pipeline stages may be cut between the attention and the MLP block of a layer (xb200.h
+  first_from_mlp / last_to_attn; topology.half_layer_stages).  Any such cut must reproduce the
+  full-shard logits bit for bit, prefill and cached decode, also when the weights come from the
+  native checkpoint loader (which then reads only the half of the boundary layer it owns)."""
+  from xotorch_support_jetson_b200.shard import Shard
+  from xotorch_support_jetson_b200.stage import StageRuntime
+  from xotorch_support_jetson_b200.synth import write_random_checkpoint
+  from xotorch_support_jetson_b200.models import model_cards
+  from xotorch_support_jetson_b200.topology import half_layer_stages
+  O, cfg, state = _setup(mid)
+  nl = cfg["num_layers"]
+  kw = dict(device=0, max_batch_tokens=64, max_seqs=2, max_tokens_per_seq=96, page_tokens=16)
+  full = StageRuntime(Shard(mid, 0, nl - 1, nl), cfg, **kw)
+  full.load_state(state)
+  ck = write_random_checkpoint(tmp_path / mid, model_cards[mid]["hf_config"], seed=0, std=0.05, norm_jitter=0.1)
+  g = torch.Generator().manual_seed(2)
+  toks = torch.randint(1, cfg["vocab_size"], (23,), generator=g).to(torch.int32).cuda()
+
+  def run(stages):
+    outs = []
+    with torch.cuda.stream(torch.cuda.Stream()):
+      def ring(q_len, pos, tok):
+        h = None
+        for st in stages:
+          h = st.forward([0], [q_len], [pos], tokens=tok) if h is None else st.forward([0], [q_len], [pos], hidden=h)
+        return h
+      lg = ring(23, 0, toks)
+      outs.append(lg)
+      for k in range(4):
+        lg = ring(1, 23 + k, lg.argmax(-1).to(torch.int32))
+        outs.append(lg)
+    torch.cuda.synchronize()
+    return outs
+
+  ref = run([full])
+  # hand-made cuts: [attn 0] | [mlp 0 .. attn 2] | [mlp 2 .. end]   and the partitioner's own for 3 and 5 stages
+  cuts = [[(0, 0, False, True), (0, 2, True, True), (2, nl - 1, True, False)]]
+  for n in (3, 5):
+    cuts.append([(s.start_layer, s.end_layer, a, b) for s, a, b in half_layer_stages(mid, nl, n, 1.0, 1.3, 0.8)])
+  assert any(a or b for c in cuts[1:] for (_, _, a, b) in c)
+  for ci, cut in enumerate(cuts):
+    stages = []
+    for (a, b, fm, la) in cut:
+      st = StageRuntime(Shard(mid, a, b, nl), cfg, first_from_mlp=fm, last_to_attn=la, **kw)
+      if ci == 0:
+        st.load_dir(ck)                      # native loader
+        assert st.weights_missing() == ""
+      else:
+        st.load_state(state)
+      stages.append(st)
+    assert stages[0].is_first and stages[-1].is_last and not any(s.is_last for s in stages[:-1])
+    got = run(stages)
+    for i, (x, y) in enumerate(zip(got, ref)):
+      assert torch.equal(x, y), f"cut {cut}: output {i} differs from the full shard by {float((x - y).abs().max())}"
+    for st in stages:
+      st.close()
+  full.close()

@@ -127,9 +127,9 @@ def test_cabi_exports_every_declared_symbol(built_lib):
   raw = ctypes.CDLL(str(_cabi.lib_path()))
   for name in declared:
     assert hasattr(raw, name), f"libxb200.so does not export {name}"
-  assert built_lib.xb_abi_version() == 1
+  assert built_lib.xb_abi_version() == 2
   # struct layouts the Python side mirrors
-  assert ctypes.sizeof(_cabi.ModelDesc) == 17 * 4 and ctypes.sizeof(_cabi.Counters) == 6 * 8
+  assert ctypes.sizeof(_cabi.ModelDesc) == 19 * 4 and ctypes.sizeof(_cabi.Counters) == 6 * 8
 
 
 @pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
@@ -173,3 +173,34 @@ def test_engine_request_bookkeeping_without_gpu():
   assert sorted(e.free_slots) == sorted(set(range(4)) - set(c.slots))
   with pytest.raises(RuntimeError):
     e._start_request("d", 5)
+
+
+def test_half_layer_stages_cover_and_balance():
+  """topology.half_layer_stages: contiguous cover of [attn_0, mlp_0, ..., mlp_{n-1}+head], slowest
+  stage never worse than the whole-layer ring strategy, flags consistent with the Shard ranges."""
+  from xotorch_support_jetson_b200.topology import half_layer_stages, pipeline_shards
+  for (nl, n, a, m, h) in ((32, 8, 352.0, 352.0, 1050.0), (32, 4, 352.0, 352.0, 1050.0), (80, 8, 1.0, 2.3, 1.2),
+                           (28, 4, 0.4, 1.0, 2.0), (4, 5, 1.0, 1.3, 0.8), (16, 1, 1.0, 1.0, 1.0), (6, 2, 1.0, 1.0, 0.0)):
+    st = half_layer_stages("llama-x", nl, n, a, m, h)
+    assert len(st) == min(n, 2 * nl)
+    # walk the unit sequence
+    unit = 0
+    costs = []
+    for (sh, from_mlp, to_attn) in st:
+      first_unit = 2 * sh.start_layer + (1 if from_mlp else 0)
+      last_unit = 2 * sh.end_layer + (0 if to_attn else 1)
+      assert first_unit == unit and last_unit >= first_unit, (nl, n, st)
+      c = sum((a if u % 2 == 0 else m) for u in range(first_unit, last_unit + 1))
+      if last_unit == 2 * nl - 1:
+        c += h
+      costs.append(c)
+      unit = last_unit + 1
+    assert unit == 2 * nl
+    assert not st[0][1] and not st[-1][2]
+    if n <= nl:
+      whole = pipeline_shards("llama-x", nl, n, h / (a + m))
+      whole_cost = max(s.get_layer_count() * (a + m) + (h if i == len(whole) - 1 else 0.0) for i, s in enumerate(whole))
+      assert max(costs) <= whole_cost + 1e-9, (nl, n, costs, whole_cost)
+  # the 8-GPU case of the bench: slowest stage 4.5 layer-equivalents instead of 5
+  st = half_layer_stages("llama-3.1-8b", 32, 8, 352.0, 352.0, 1050.0)
+  assert sum(1 for (_, a, b) in st if a or b) == 2

@@ -31,6 +31,7 @@ class ModelDesc(C.Structure):
     ("norm_eps", C.c_float),
     ("rope_kind", C.c_int32), ("rmsnorm_two_round", C.c_int32), ("qkv_bias", C.c_int32), ("tied_head", C.c_int32),
     ("max_positions", C.c_int32), ("max_batch_tokens", C.c_int32), ("max_seqs", C.c_int32),
+    ("first_from_mlp", C.c_int32), ("last_to_attn", C.c_int32),
   ]
 
 

@@ -97,6 +97,11 @@ struct xb_engine {
 
 #define LAUNCH_COUNT(e) ((e)->c.launches++)
 
+// a stage that begins at the MLP block of layer 0 does not hold the embedding; one that stops after the
+// attention block of the last layer does not hold the final norm / LM head
+static inline bool shard_is_first(const xb_model_desc& d) { return d.start_layer == 0 && !d.first_from_mlp; }
+static inline bool shard_is_last(const xb_model_desc& d) { return d.end_layer == d.n_layers - 1 && !d.last_to_attn; }
+
 // Launch one kernel of the forward: programmatic dependent launch (the kernel calls
 // griddepcontrol.wait before touching upstream data) and an optional cluster dimension.
 template <typename... KArgs, typename... Args>
@@ -180,6 +185,7 @@ extern "C" int xb_engine_create(const xb_model_desc* desc, int device, xb_engine
   XB_CHECK(d.start_layer >= 0 && d.end_layer >= d.start_layer && d.end_layer < d.n_layers, "bad layer range [%d,%d] of %d",
            d.start_layer, d.end_layer, d.n_layers);
   XB_CHECK(d.head_dim == 64 || d.head_dim == 128, "head_dim %d not supported (64 or 128)", d.head_dim);
+  XB_CHECK(!(d.first_from_mlp && d.last_to_attn && d.start_layer == d.end_layer), "a stage holding neither block of its only layer is empty");
   XB_CHECK(d.n_heads % d.n_kv_heads == 0 && d.n_heads / d.n_kv_heads <= 8, "n_heads %d must be 1..8 x n_kv_heads %d",
            d.n_heads, d.n_kv_heads);
   XB_CHECK(d.dim % 8 == 0 && d.inter_dim % 16 == 0, "dim must be a multiple of 8 and inter_dim of 16");
@@ -207,9 +213,11 @@ extern "C" int xb_engine_create(const xb_model_desc* desc, int device, xb_engine
       XB_TRY(dmalloc((void**)&w.bqkv, (size_t)e->NQKV * 2));
       XB_CUDA(cudaMemset(w.bqkv, 0, (size_t)e->NQKV * 2));
     }
-    wbytes += ((size_t)e->NQKV * D + D * e->NQ + 3 * I * D) * 2;
+    const bool has_attn = !(l == 0 && d.first_from_mlp), has_mlp = !(l + 1 == e->nl && d.last_to_attn);
+    if (has_attn) wbytes += ((size_t)e->NQKV * D + D * e->NQ) * 2;
+    if (has_mlp) wbytes += (size_t)3 * I * D * 2;
   }
-  const bool first = d.start_layer == 0, last = d.end_layer == d.n_layers - 1;
+  const bool first = shard_is_first(d), last = shard_is_last(d);
   // the embedding table stays row-major (row gather); the LM head is tile-major like every
   // other matrix, so a tied head on a last shard is a second, tiled copy of the table
   if (first) XB_TRY(dmalloc((void**)&e->embed, (size_t)d.vocab * D * 2));
@@ -220,7 +228,7 @@ extern "C" int xb_engine_create(const xb_model_desc* desc, int device, xb_engine
   }
   XB_TRY(dmalloc((void**)&e->rope, (size_t)d.max_positions * (d.head_dim / 2) * 2 * sizeof(float)));
   e->c.weight_bytes = wbytes;
-  e->c.kv_bytes_per_pos = (uint64_t)2 * e->nl * e->NKV * 2;
+  e->c.kv_bytes_per_pos = (uint64_t)2 * (e->nl - (d.first_from_mlp ? 1 : 0)) * e->NKV * 2;   // layers whose attention block runs here
   // workspaces
   const size_t T = d.max_batch_tokens;
   XB_TRY(dmalloc((void**)&e->h, T * D * 2));
@@ -404,9 +412,13 @@ static bool shard_wants(const xb_engine* e, int layer, int kind) {
   const xb_model_desc& d = e->d;
   if (layer >= 0) {
     if (layer < d.start_layer || layer > d.end_layer) return false;
+    const bool attn_kind = kind == XB_W_Q || kind == XB_W_K || kind == XB_W_V || kind == XB_W_O || kind == XB_W_SA_NORM ||
+                           kind == XB_W_Q_BIAS || kind == XB_W_K_BIAS || kind == XB_W_V_BIAS;
+    if (attn_kind && layer == d.start_layer && d.first_from_mlp) return false;   // that block lives on the previous stage
+    if (!attn_kind && layer == d.end_layer && d.last_to_attn) return false;      // ... on the next stage
     return (kind != XB_W_Q_BIAS && kind != XB_W_K_BIAS && kind != XB_W_V_BIAS) || d.qkv_bias;
   }
-  const bool first = d.start_layer == 0, last = d.end_layer == d.n_layers - 1;
+  const bool first = shard_is_first(d), last = shard_is_last(d);
   if (kind == XB_W_EMBED) return first || (last && d.tied_head);
   if (kind == XB_W_FINAL_NORM) return last;
   if (kind == XB_W_LM_HEAD) return last && !d.tied_head;
@@ -785,7 +797,7 @@ static int run_head(xb_engine* e, int n_seqs, cudaStream_t st, float* host_logit
 static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, void* const* taps, cudaStream_t st,
                     int ho_in = 0, int ho_out = 0, int with_head = 1) {
   const xb_model_desc& d = e->d;
-  const bool first = d.start_layer == 0, last = d.end_layer == d.n_layers - 1;
+  const bool first = shard_is_first(d), last = shard_is_last(d);
   BatchMeta m;
   m.tok_seq = e->d_tok_seq;
   m.tok_pos = e->d_tok_pos;
@@ -798,22 +810,29 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
   m.page_tokens = e->page_tokens;
   const int D = d.dim, I = d.inter_dim, hd = d.head_dim;
   const size_t norm_smem = (size_t)D * sizeof(float);
+  // half-layer shards: a stage may start at the MLP block of its first layer (the attention block ran
+  // on the previous GPU) and/or stop after the attention block of its last layer; the residual stream
+  // crosses the boundary exactly as it does between whole layers
+  const bf16* norm0 = d.first_from_mlp ? e->L[0].mlp_norm : e->L[0].sa_norm;
   if (first) {
     XB_TRY(launch_k(e, xb_embed_norm_kernel<256>, dim3(T), dim3(256), 0, st, 1, e->in_tokens, e->embed, e->L[0].sa_norm, e->h, e->hn, D, d.vocab, d.norm_eps,
                                                   d.rmsnorm_two_round));
   } else if (ho_in) {
     // stage input arrives in the landing buffer, stored there by the previous GPU's last kernel
     XB_TRY(launch_k(e, xb_recv_norm_kernel<256>, dim3(T), dim3(256), norm_smem, st, 1, (const bf16*)e->landing,
-                    (const uint32_t*)e->flags, (const HandoffCtl*)e->d_ctl, (long long)e->ho_rows * D, e->h, e->L[0].sa_norm, e->hn, D,
+                    (const uint32_t*)e->flags, (const HandoffCtl*)e->d_ctl, (long long)e->ho_rows * D, e->h, norm0, e->hn, D,
                     d.norm_eps, d.rmsnorm_two_round));
   } else {
-    XB_TRY(launch_k(e, xb_resid_norm_kernel<256, 2>, dim3(T), dim3(256), norm_smem, st, 1, nullptr, SplitInfo{1, 0, 1}, 0, nullptr, e->h, e->L[0].sa_norm, e->hn, D,
+    XB_TRY(launch_k(e, xb_resid_norm_kernel<256, 2>, dim3(T), dim3(256), norm_smem, st, 1, nullptr, SplitInfo{1, 0, 1}, 0, nullptr, e->h, norm0, e->hn, D,
                                                              d.norm_eps, d.rmsnorm_two_round));
   }
 
   for (int l = 0; l < e->nl; ++l) {
     const LayerW& w = e->L[l];
     const GemmPlan* gp;
+    const bool do_attn = !(l == 0 && d.first_from_mlp);
+    const bool do_mlp = !(l + 1 == e->nl && d.last_to_attn);
+    if (do_attn) {
     // q/k/v projections as one GEMM (general_mha.py:83-97)
     XB_TRY(get_plan(e, SITE_QKV, l, e->hn, D, w.wqkv, T, e->NQKV, D, e->gemm_out, e->NQKV, w.bqkv, 0, &gp));
     XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
@@ -830,7 +849,9 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
     XB_TRY(get_plan(e, SITE_O, l, e->attn, e->NQ, w.wo, T, D, e->NQ, e->gemm_out, D, nullptr, 0, &gp));
     XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
     LAUNCH_COUNT(e);
-    XB_TRY(launch_resid_norm(e, gp, T, w.mlp_norm, st));
+    if (do_mlp) XB_TRY(launch_resid_norm(e, gp, T, w.mlp_norm, st));
+    }
+    if (do_mlp) {
     // gate/up as one GEMM, SiLU*up, down projection (llm_utils.py:513-522)
     XB_TRY(get_plan(e, SITE_GU, l, e->hn, D, w.wgu, T, 2 * I, D, e->gemm_out, 2 * I, nullptr, 0, &gp));
     XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
@@ -843,6 +864,8 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
     XB_TRY(get_plan(e, SITE_DOWN, l, e->act, I, w.wdown, T, D, I, e->gemm_out, D, nullptr, 0, &gp));
     XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
     LAUNCH_COUNT(e);
+    }
+    // `gp` is the block's last Linear (down, or the output projection of a stage that stops after attention)
     const bf16* next_norm = (l + 1 < e->nl) ? e->L[l + 1].sa_norm : (last ? e->final_norm : nullptr);
     if (ho_out && l + 1 == e->nl && gp->args.mode == XB_GEMM_SKINNY) {
       // stage output: reduce + residual, stored straight into the next GPU's landing buffer
@@ -869,7 +892,7 @@ static int forward_impl(xb_engine* e, const xb_batch* b, void* out, void* const*
   XB_CUDA(cudaSetDevice(e->device));
   XB_CHECK(e->n_slots > 0, "xb_kv_reserve must be called before xb_forward");
   XB_CHECK(b->n_seqs > 0 && b->n_seqs <= d.max_seqs, "n_seqs %d out of range (max %d)", b->n_seqs, d.max_seqs);
-  const bool first = d.start_layer == 0, last = d.end_layer == d.n_layers - 1;
+  const bool first = shard_is_first(d), last = shard_is_last(d);
   XB_CHECK(first ? (b->tokens != nullptr) : (ho_in || b->hidden_in != nullptr),
            first ? "first shard needs token ids" : "non-first shard needs a hidden state");
   XB_CHECK(!last || b->n_seqs <= 128, "LM head path supports up to 128 sequences per call");
@@ -1020,7 +1043,7 @@ extern "C" int xb_forward(xb_engine* e, const xb_batch* b, void* out, void* cons
 
 extern "C" int xb_forward_host_logits(xb_engine* e, const xb_batch* b, void* out, float* host_logits, void* stream) {
   XB_CHECK(e != nullptr && host_logits != nullptr, "null argument");
-  XB_CHECK(e->d.end_layer == e->d.n_layers - 1, "xb_forward_host_logits needs a last shard (it produces logits)");
+  XB_CHECK(shard_is_last(e->d), "xb_forward_host_logits needs a last shard (it produces logits)");
   cudaPointerAttributes pa;
   XB_CHECK(cudaPointerGetAttributes(&pa, host_logits) == cudaSuccess && pa.type == cudaMemoryTypeHost && pa.devicePointer != nullptr,
            "host_logits must be page-locked host memory the device can address (cudaHostAlloc / torch pin_memory)");
@@ -1079,7 +1102,7 @@ extern "C" int xb_bench_linears(xb_engine* e, int T, int iters, int* n_launches,
   const xb_model_desc& d = e->d;
   cudaStream_t st = (cudaStream_t)stream;
   XB_CUDA(cudaSetDevice(e->device));
-  const bool last = d.end_layer == d.n_layers - 1;
+  const bool last = shard_is_last(d);
   const int D = d.dim, I = d.inter_dim;
   // XB_BENCH_SITE=0..4 restricts the pass to one site (qkv, o, gate/up, down, head) for per-site numbers
   const char* sv = getenv("XB_BENCH_SITE");

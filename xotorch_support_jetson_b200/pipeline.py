@@ -22,7 +22,7 @@ from .model_config import load_model_config  # noqa: F401  (re-exported for call
 from .shard import Shard
 from .stage import StageRuntime
 from .synth import hf_param_shapes
-from .topology import pipeline_shards
+from .topology import half_layer_stages, pipeline_shards
 
 
 def gpu_random_tensor(name: str, shape, seed: int, std: float, device, dtype=torch.bfloat16) -> torch.Tensor:
@@ -56,7 +56,7 @@ class PipelineRunner:
                micro_batches: int, max_ctx: int, max_batch_tokens: int = 8192, page_tokens: int = 64,
                seed: int = 0, std: float = 0.02, dist=None, weights: Optional[tuple] = None,
                stage_factory: Optional[Callable] = None, ret_group=None,
-               balance_head: bool = True):
+               balance_head: bool = True, half_layers: Optional[bool] = None):
     """``stage_factory(shard) -> stage`` lets the host-side protocol (ordering of the
     send/recv pairs, micro-batching, token return edge) be exercised without a GPU (the
     world_size-2 gloo tests plug the CPU oracle in; the product never does)."""
@@ -69,8 +69,25 @@ class PipelineRunner:
     D, I = config["embed_dim"], config["intermediate_dim"]
     layer_params = 2 * D * config["num_heads"] * config["head_dim"] + 2 * D * config["num_kv_heads"] * config["head_dim"] + 3 * D * I
     head_equiv = config["vocab_size"] * D / layer_params if balance_head else 0.0
-    self.shard: Shard = pipeline_shards(model_id, n_layers, world, head_equiv)[rank]
+    # stage boundaries: half-layer granularity by bytes streamed per decode step (weights + the KV cache
+    # of one micro-batch at the expected context), or the reference's whole-layer ring strategy
+    self.first_from_mlp = self.last_to_attn = False
+    if half_layers is None:
+      half_layers = os.environ.get("XB_HALF_LAYERS", "1") != "0"
+    if half_layers and world > 1 and stage_factory is None:
+      H, KV, hd = config["num_heads"], config["num_kv_heads"], config["head_dim"]
+      attn_cost = 2.0 * (D * H * hd * 2 + 2 * D * KV * hd) + batch * max_ctx * (2 * KV * hd * 2)
+      mlp_cost = 2.0 * 3 * D * I
+      head_cost = 2.0 * config["vocab_size"] * D if balance_head else 0.0
+      self.shard, self.first_from_mlp, self.last_to_attn = half_layer_stages(model_id, n_layers, world, attn_cost, mlp_cost,
+                                                                              head_cost)[rank]
+    else:
+      self.shard: Shard = pipeline_shards(model_id, n_layers, world, head_equiv)[rank]
     self.first, self.last = self.shard.is_first_layer(), self.shard.is_last_layer()
+    if self.first_from_mlp:
+      self.first = False
+    if self.last_to_attn:
+      self.last = False
     if stage_factory is not None:
       self.stage = stage_factory(self.shard)
       self.device = torch.device("cpu")
@@ -78,7 +95,8 @@ class PipelineRunner:
     else:
       self.device = torch.device("cuda", device)
       self.stage = StageRuntime(self.shard, config, device=device, max_batch_tokens=max_batch_tokens,
-                                max_seqs=batch * micro_batches, max_tokens_per_seq=max_ctx, page_tokens=page_tokens)
+                                max_seqs=batch * micro_batches, max_tokens_per_seq=max_ctx, page_tokens=page_tokens,
+                                first_from_mlp=self.first_from_mlp, last_to_attn=self.last_to_attn)
       get, has = weights if weights is not None else gpu_random_getter(hf_cfg, seed, std, self.device)
       self.stage.load_hf_tensors(get, has)
       self.stream = torch.cuda.Stream(device=self.device)

@@ -55,7 +55,8 @@ class _SafetensorsIndex:
 class StageRuntime:
   def __init__(self, shard: Shard, config: dict, device: int = 0, max_batch_tokens: int = 4096,
                max_seqs: int = 32, max_tokens_per_seq: int = 4096, page_tokens: int = 64,
-               rope_table_bf16: bool = True, rmsnorm_two_round: bool = True, max_positions: Optional[int] = None):
+               rope_table_bf16: bool = True, rmsnorm_two_round: bool = True, max_positions: Optional[int] = None,
+               first_from_mlp: bool = False, last_to_attn: bool = False):
     if not torch.cuda.is_available():
       raise RuntimeError("B200 engine needs a CUDA device: there is no CPU fallback")
     self.lib = _cabi.load()
@@ -78,7 +79,13 @@ class StageRuntime:
       norm_eps=config["norm_eps"],
       rope_kind=_cabi.ROPE_HALF_SPLIT if self.family == "qwen" else _cabi.ROPE_INTERLEAVED,
       rmsnorm_two_round=int(rmsnorm_two_round), qkv_bias=int(self.qkv_bias), tied_head=int(self.tied),
-      max_positions=max_positions, max_batch_tokens=max_batch_tokens, max_seqs=max_seqs)
+      max_positions=max_positions, max_batch_tokens=max_batch_tokens, max_seqs=max_seqs,
+      first_from_mlp=int(first_from_mlp), last_to_attn=int(last_to_attn))
+    # half-layer stage boundaries (xb200.h): the attention block of start_layer / the MLP block of
+    # end_layer may belong to the neighbouring pipeline stage
+    self.first_from_mlp, self.last_to_attn = bool(first_from_mlp), bool(last_to_attn)
+    self.is_first = shard.is_first_layer() and not self.first_from_mlp    # holds the embedding
+    self.is_last = shard.is_last_layer() and not self.last_to_attn        # holds the final norm + LM head
     self.desc = d
     self._h = C.c_void_p()
     _cabi.check(self.lib.xb_engine_create(C.byref(d), device, C.byref(self._h)))
@@ -115,25 +122,29 @@ class StageRuntime:
     llama = self.family == "llama"
     for l in range(sh.start_layer, sh.end_layer + 1):
       p = f"model.layers.{l}."
-      q, k = get(p + "self_attn.q_proj.weight"), get(p + "self_attn.k_proj.weight")
-      if llama:  # reference permutes q/k for Llama only (llm_utils.py:213-231)
-        q, k = _permute(q, H, hd, D), _permute(k, KV, hd, D)
-      self._load(l, _cabi.W_Q, q)
-      self._load(l, _cabi.W_K, k)
-      self._load(l, _cabi.W_V, get(p + "self_attn.v_proj.weight"))
-      self._load(l, _cabi.W_O, get(p + "self_attn.o_proj.weight"))
-      self._load(l, _cabi.W_GATE, get(p + "mlp.gate_proj.weight"))
-      self._load(l, _cabi.W_UP, get(p + "mlp.up_proj.weight"))
-      self._load(l, _cabi.W_DOWN, get(p + "mlp.down_proj.weight"))
-      self._load(l, _cabi.W_SA_NORM, get(p + "input_layernorm.weight"))
-      self._load(l, _cabi.W_MLP_NORM, get(p + "post_attention_layernorm.weight"))
-      if self.qkv_bias:
+      has_attn = not (l == sh.start_layer and self.first_from_mlp)
+      has_mlp = not (l == sh.end_layer and self.last_to_attn)
+      if has_attn:
+        q, k = get(p + "self_attn.q_proj.weight"), get(p + "self_attn.k_proj.weight")
+        if llama:  # reference permutes q/k for Llama only (llm_utils.py:213-231)
+          q, k = _permute(q, H, hd, D), _permute(k, KV, hd, D)
+        self._load(l, _cabi.W_Q, q)
+        self._load(l, _cabi.W_K, k)
+        self._load(l, _cabi.W_V, get(p + "self_attn.v_proj.weight"))
+        self._load(l, _cabi.W_O, get(p + "self_attn.o_proj.weight"))
+        self._load(l, _cabi.W_SA_NORM, get(p + "input_layernorm.weight"))
+      if has_mlp:
+        self._load(l, _cabi.W_GATE, get(p + "mlp.gate_proj.weight"))
+        self._load(l, _cabi.W_UP, get(p + "mlp.up_proj.weight"))
+        self._load(l, _cabi.W_DOWN, get(p + "mlp.down_proj.weight"))
+        self._load(l, _cabi.W_MLP_NORM, get(p + "post_attention_layernorm.weight"))
+      if self.qkv_bias and has_attn:
         for nm, kind in (("q_proj", _cabi.W_Q_BIAS), ("k_proj", _cabi.W_K_BIAS), ("v_proj", _cabi.W_V_BIAS)):
           if has(p + f"self_attn.{nm}.bias"):
             self._load(l, kind, get(p + f"self_attn.{nm}.bias"))
-    if sh.is_first_layer() or (sh.is_last_layer() and self.tied):
+    if self.is_first or (self.is_last and self.tied):
       self._load(-1, _cabi.W_EMBED, get("model.embed_tokens.weight"))
-    if sh.is_last_layer():
+    if self.is_last:
       self._load(-1, _cabi.W_FINAL_NORM, get("model.norm.weight"))
       if not self.tied:
         self._load(-1, _cabi.W_LM_HEAD, get("lm_head.weight"))
@@ -194,7 +205,7 @@ class StageRuntime:
       b.hidden_in = hidden.data_ptr()
     sends = handoff is not None and handoff[2] >= 0
     if out is None and not sends:
-      if self.shard.is_last_layer():
+      if self.is_last:
         out = torch.empty((n, self.vocab), dtype=torch.float32, device=self.device)
       else:
         out = torch.empty((T, self.dim), dtype=torch.bfloat16, device=self.device)

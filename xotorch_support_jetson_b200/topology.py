@@ -165,3 +165,48 @@ def pipeline_shards(model_id: str, n_layers: int, n_gpus: int, head_layer_equiv:
     if best_cost is None or cost < best_cost - 1e-9:
       best, best_cost = sh, cost
   return best if best is not None else shards_for(0.0)
+
+
+def half_layer_stages(model_id: str, n_layers: int, n_gpus: int, attn_cost: float, mlp_cost: float,
+                      head_cost: float) -> List[tuple]:
+  """Stage boundaries at HALF-layer granularity: the per-step cost of a decode stage is bytes
+  streamed, and a decoder layer is two blocks of similar weight -- attention (q/k/v/o matrices +
+  the KV cache of the batch) and MLP (gate/up/down) -- plus the LM head on the last stage, so
+  whole-layer ranges (``pipeline_shards``, the reference's ring strategy) leave up to a layer of
+  imbalance (32 layers + head over 8 GPUs: slowest stage 5 layers against a mean of 4.3).
+
+  Minimises the slowest stage over contiguous splits of [attn_0, mlp_0, ..., attn_{n-1}, mlp_{n-1} + head].
+  Returns, per rank, ``(Shard, first_from_mlp, last_to_attn)``: a layer cut in the middle appears
+  in both neighbouring Shards (end_layer of one, start_layer of the next)."""
+  units = []
+  for _ in range(n_layers):
+    units += [float(attn_cost), float(mlp_cost)]
+  units[-1] += float(head_cost)
+  U = len(units)
+  n = max(1, min(n_gpus, U))
+  pre = [0.0]
+  for u in units:
+    pre.append(pre[-1] + u)
+  INF = float("inf")
+  # best[k][i] = smallest possible slowest-stage cost when the first i units form k stages
+  best = [[INF] * (U + 1) for _ in range(n + 1)]
+  cut = [[0] * (U + 1) for _ in range(n + 1)]
+  best[0][0] = 0.0
+  for k in range(1, n + 1):
+    for i in range(k, U + 1):
+      for j in range(k - 1, i):
+        c = max(best[k - 1][j], pre[i] - pre[j])
+        if c < best[k][i] - 1e-12:
+          best[k][i], cut[k][i] = c, j
+  bounds, i = [], U
+  for k in range(n, 0, -1):
+    j = cut[k][i]
+    bounds.append((j, i))
+    i = j
+  bounds.reverse()
+  out = []
+  for (a, b) in bounds:            # units [a, b): unit 2l = attention of layer l, 2l+1 = its MLP
+    start_layer, end_layer = a // 2, (b - 1) // 2
+    out.append((Shard(model_id, start_layer, end_layer, n_layers), a % 2 == 1, (b - 1) % 2 == 0))
+  return out
+
