@@ -180,7 +180,9 @@ def run_reference(args):
 def workload_config(args):
   return {"workload": f"{args.model} bf16 random-init, {args.prompt_len}-token synthetic prompts, greedy decode from context "
                       f"{args.prompt_len}, batch {args.batch} per micro-batch x {args.gpus} micro-batches in flight "
-                      f"({args.gpus}-stage layer pipeline, ring partition)",
+                      f"({args.gpus}-stage layer pipeline, "
+                      + ("stage boundaries at half-layer granularity balanced by bytes per step)" if args.gpus > 1 and os.environ.get("XB_HALF_LAYERS", "1") != "0"
+                         else "whole-layer ring partition)"),
           "global_batch": args.batch * args.gpus, "prompt_len": args.prompt_len, "parallelism": f"pp{args.gpus}",
           "l2_policy": "inputs larger than L2 (weights 15 GB per pass >> 126 MB L2)"}
 
