@@ -6,7 +6,8 @@
 Workload (BASELINE.json configs[2], the one the metric is quoted on): Llama-3.1-8B bf16,
 random-init weights, synthetic 2048-token prompts, decode at context 2048.., batch 32 per
 pipeline micro-batch.  A "step" is one decode step of every in-flight sequence.  At N GPUs
-the model is an N-stage layer pipeline (the ranges the reference's ring strategy assigns)
+the model is an N-stage layer pipeline (stage boundaries at half-layer granularity balanced by
+bytes per step; XB_HALF_LAYERS=0: the whole-layer ranges the reference's ring strategy assigns)
 with N micro-batches of 32 sequences in flight: per-GPU work is fixed -> "weak" scaling.
 
 One JSON line on stdout (rank 0).  `value` = decode tokens/s with ids resident in HBM;
