@@ -371,18 +371,38 @@ __device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t smem_addr, uint3
          (1ull << 46) | (2ull << 61);
 }
 
+// D[tmem] (+)= A[tmem] * B[smem desc]: the A operand (128 rows = lanes, K bf16 elements packed two per
+// 32-bit column) is read from tensor memory -- P of the attention never visits shared memory
+__device__ __forceinline__ void tc_mma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc,
+                                               uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+#ifndef XB_ATT_P_TMEM
+#define XB_ATT_P_TMEM 1
+#endif
+
 #define XB_ATT_PG_CACHE 128   // page ids prefetched per block (8k keys at 64-token pages; beyond: on demand)
 
 template <int HD>
 struct AttTcCfg {
   static constexpr int Q_BYTES = 128 * HD * 2;
   static constexpr int TILE_BYTES = XB_ATT_TILE * HD * 2;   // one K or V tile
-  static constexpr int P_BYTES = 128 * XB_ATT_TILE * 2;
+  static constexpr int P_BYTES = XB_ATT_P_TMEM ? 0 : 128 * XB_ATT_TILE * 2;   // P lives in tensor memory
   static constexpr int NST = 2;                             // K and V ring depth
   // TWO blocks per SM (measured: 240 us vs 328 us for one block with double-buffered P and 4-deep
   // rings at 4 x 2048 tokens -- the four softmax warps of a block are latency bound, a second
-  // block doubles the warps per scheduler).  No alignment slack: 2 x (112.75 KB + 1 KB reserved)
-  // must fit 228 KB; the kernel traps if the dynamic shared memory base is not 1024-byte aligned.
+  // block doubles the warps per scheduler).  No alignment slack (with the shared-memory P buffer,
+  // XB_ATT_P_TMEM=0, 2 x (112.75 KB + 1 KB reserved) only just fits 228 KB); the kernel traps if the
+  // dynamic shared memory base is not 1024-byte aligned.
+  // P in tensor memory (XB_ATT_P_TMEM=1, default): the softmax warps store bf16 P over the first 32
+  // columns of the tile's S buffer with tcgen05.st and O += P V takes its A operand from there -- no
+  // shared-memory round trip, no proxy fence, and the softmax of tile kt no longer waits for PV of
+  // tile kt-1 to release a single P buffer: 212 us against 238 us per layer at 4 x 2048 tokens.
   static constexpr int SMEM_BYTES = Q_BYTES + NST * 2 * TILE_BYTES + P_BYTES + 256 + XB_ATT_PG_CACHE * 4;
   static constexpr int TM_COLS = 256;                       // S: 64 columns, O: HD columns
 };
@@ -530,9 +550,15 @@ __global__ void __launch_bounds__(192, 2) xb_attn_prefill_tc_kernel(
         tc_fence_after();
 #pragma unroll
         for (int ks = 0; ks < XB_ATT_TILE / 16; ++ks) {
-          const uint32_t a = p_addr + ks * 32;
           const uint32_t b = v_addr + ks * 2048;
+#if XB_ATT_P_TMEM
+          // P(kt) sits in the first 32 columns of S buffer kt&1 (16 keys = 8 packed columns per step)
+          tc_mma_bf16_ts(tm_O, tm_S + (uint32_t)((kt & 1) * XB_ATT_TILE) + ks * 8, umma_desc_mn_sw128(b, XB_ATT_TILE * 128), idesc_o,
+                         (kt > 0 || ks > 0) ? 1u : 0u);
+#else
+          const uint32_t a = p_addr + ks * 32;
           tc_mma_bf16(tm_O, umma_desc_sw128(a), umma_desc_mn_sw128(b, XB_ATT_TILE * 128), idesc_o, (kt > 0 || ks > 0) ? 1u : 0u);
+#endif
         }
         tc_commit(&v_empty[stage]);
         tc_commit(&o_done[kt & 1]);
@@ -583,14 +609,22 @@ __global__ void __launch_bounds__(192, 2) xb_attn_prefill_tc_kernel(
         for (int j = 0; j < XB_ATT_TILE; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], __uint_as_float(v[j]));
       }
       const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * scale_log2;   // scale > 0
+#if !XB_ATT_P_TMEM
       // ---- the (single) P buffer was last read by PV of tile kt-1
       if (kt > 0) {
         mbar_wait(&o_done[(kt - 1) & 1], ((kt - 1) >> 1) & 1);
         tc_fence_after();
       }
+#endif
       // ---- lazy rescale: only when some row of the warp moved by more than 2^8
       const bool need = mx > m_used + 8.0f;
       if (__any_sync(0xffffffffu, need)) {
+#if XB_ATT_P_TMEM
+        if (kt > 0) {   // O must be quiescent: PV of tile kt-1 retired
+          mbar_wait(&o_done[(kt - 1) & 1], ((kt - 1) >> 1) & 1);
+          tc_fence_after();
+        }
+#endif
         const float m_new = need ? mx : m_used;
         const float corr = (m_used == -INFINITY) ? 0.f : exp2f(m_used - m_new);
         l_sum *= corr;
@@ -611,6 +645,9 @@ __global__ void __launch_bounds__(192, 2) xb_attn_prefill_tc_kernel(
       // ---- p = 2^(s*scale - m_used) -> bf16 -> swizzled smem (A operand of the PV MMA)
       const float nmref = (m_used == -INFINITY) ? 0.f : -m_used;
       float ps[4] = {0.f, 0.f, 0.f, 0.f};
+#if XB_ATT_P_TMEM
+      uint32_t pw[XB_ATT_TILE / 2];
+#endif
 #pragma unroll
       for (int c = 0; c < XB_ATT_TILE; c += 8) {
         float p[8];
@@ -624,12 +661,23 @@ __global__ void __launch_bounds__(192, 2) xb_attn_prefill_tc_kernel(
         }
 #pragma unroll
         for (int j = 0; j < 8; ++j) ps[j & 3] += p[j];
+#if XB_ATT_P_TMEM
+        pw[(c >> 1)] = f2_to_bf2(p[0], p[1]); pw[(c >> 1) + 1] = f2_to_bf2(p[2], p[3]);
+        pw[(c >> 1) + 2] = f2_to_bf2(p[4], p[5]); pw[(c >> 1) + 3] = f2_to_bf2(p[6], p[7]);
+      }
+      // P -> tensor memory, over the first 32 columns of this tile's S buffer (this row's scores are
+      // already in registers; the MMA warp reads them as the A operand of O += P V)
+      tmem_st16(tm_Sk + lane_base, pw);
+      tmem_st16(tm_Sk + lane_base + 16, pw + 16);
+      tmem_st_wait();
+#else
         uint4 w;
         w.x = f2_to_bf2(p[0], p[1]); w.y = f2_to_bf2(p[2], p[3]); w.z = f2_to_bf2(p[4], p[5]); w.w = f2_to_bf2(p[6], p[7]);
         *reinterpret_cast<uint4*>(sP + r * 128 + ((((c >> 3)) ^ (r & 7)) << 4)) = w;
       }
-      l_sum += (ps[0] + ps[1]) + (ps[2] + ps[3]);
       fence_proxy_async();
+#endif
+      l_sum += (ps[0] + ps[1]) + (ps[2] + ps[3]);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&p_full[kt & 1]);
