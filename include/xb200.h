@@ -122,6 +122,12 @@ int xb_load_safetensors(xb_engine* e, const char* path, int permute_qk, int* n_t
  * surfaces the same condition as load_state_dict(strict=False) missing keys (llm_utils.py:262-284). */
 int xb_weights_missing(xb_engine* e, char* buf, size_t buflen, int* n_missing);
 
+/* The header of a .safetensors file as text, one tensor per line: "name dtype begin end dim0 dim1 ..."
+ * (offsets relative to the data section) -- what xb_load_safetensors parses; needs no GPU.  The
+ * reference reads the same information through safetensors' safe_open (llm_utils.py:151-160).
+ * buf may be NULL to get the count only. */
+int xb_safetensors_list(const char* path, char* buf, size_t buflen, int* n_tensors);
+
 /* Paged KV cache.  Replaces setup_caches / reset_caches / KVCache.update
  * (llm_utils.py:320-365; sharded_inference_engine.py:71-82,139-147): pages of
  * `page_tokens` positions are handed to a slot on demand as it grows and returned by

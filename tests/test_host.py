@@ -204,3 +204,60 @@ def test_half_layer_stages_cover_and_balance():
   # the 8-GPU case of the bench: slowest stage 4.5 layer-equivalents instead of 5
   st = half_layer_stages("llama-3.1-8b", 32, 8, 352.0, 352.0, 1050.0)
   assert sum(1 for (_, a, b) in st if a or b) == 2
+
+
+def test_safetensors_header_parser_without_gpu(built_lib, tmp_path):
+  """xb_safetensors_list (the header parser behind xb_load_safetensors) against the safetensors
+  package: names, dtypes, shapes, byte ranges; metadata with quotes/braces; malformed files."""
+  import ctypes as C
+  import struct
+  import torch
+  from safetensors import safe_open
+  from safetensors.torch import save_file
+  from xotorch_support_jetson_b200 import _cabi
+  tensors = {
+    "model.layers.0.self_attn.q_proj.weight": torch.zeros(16, 8, dtype=torch.bfloat16),
+    "model.layers.10.mlp.up_proj.weight": torch.zeros(24, 8, dtype=torch.float16),
+    "model.norm.weight": torch.ones(8, dtype=torch.float32),
+    "odd \"name\" {x}": torch.zeros(3, dtype=torch.int64),
+    "scalar": torch.tensor(1.5),
+  }
+  f = tmp_path / "m.safetensors"
+  save_file(tensors, str(f), metadata={"format": "pt", "note": "a \"quoted\" value, {braces}, [brackets]"})
+
+  def listing(path):
+    n = C.c_int()
+    buf = C.create_string_buffer(1 << 16)
+    _cabi.check(built_lib.xb_safetensors_list(str(path).encode(), buf, len(buf), C.byref(n)))
+    rows = {}
+    for line in buf.value.decode().splitlines():
+      # names may contain spaces: the last fields are numeric, dtype is the token before them
+      parts = line.split(" ")
+      k = len(parts) - 1
+      while k > 0 and parts[k].lstrip("-").isdigit():
+        k -= 1
+      name, dtype, nums = " ".join(parts[:k]), parts[k], [int(x) for x in parts[k + 1:]]
+      rows[name] = (dtype, nums[0], nums[1], nums[2:])
+    assert len(rows) == n.value
+    return rows
+
+  rows = listing(f)
+  with safe_open(str(f), framework="pt") as h:
+    assert set(rows) == set(h.keys())
+    for k in h.keys():
+      t = h.get_tensor(k)
+      dtype, b, e, shape = rows[k]
+      assert shape == list(t.shape) and e - b == t.numel() * t.element_size()
+      assert dtype == {torch.bfloat16: "BF16", torch.float16: "F16", torch.float32: "F32", torch.int64: "I64"}[t.dtype]
+  # byte ranges tile the data section without overlap
+  spans = sorted((b, e) for _, b, e, _ in rows.values())
+  assert spans[0][0] == 0 and all(spans[i][1] == spans[i + 1][0] for i in range(len(spans) - 1))
+  # malformed: header length beyond the file, truncated JSON, offsets past the end, not a file
+  bad = tmp_path / "bad.safetensors"
+  for payload in (struct.pack("<Q", 1 << 40) + b"{}", struct.pack("<Q", 5) + b'{"a":', struct.pack("<Q", 2) + b"[]",
+                  struct.pack("<Q", 60) + b'{"t":{"dtype":"F32","shape":[4],"data_offsets":[0,16]}}    ', b"abc"):
+    bad.write_bytes(payload)
+    with pytest.raises(RuntimeError):
+      listing(bad)
+  with pytest.raises(RuntimeError):
+    listing(tmp_path / "missing.safetensors")

@@ -10,7 +10,7 @@ _LIB_NAME = "libxb200.so"
 # symbols include/xb200.h declares (tests check the built library exports every one)
 SYMBOLS = (
   "xb_last_error", "xb_abi_version", "xb_engine_create", "xb_engine_destroy", "xb_load_weight",
-  "xb_load_safetensors", "xb_weights_missing",
+  "xb_load_safetensors", "xb_weights_missing", "xb_safetensors_list",
   "xb_kv_reserve", "xb_kv_release_slot", "xb_kv_slot_len", "xb_forward", "xb_forward_host_logits", "xb_sample",
   "xb_handoff_create", "xb_handoff_connect", "xb_forward_handoff",
   "xb_get_counters", "xb_debug_linear", "xb_bench_linears", "xb_bench_attention", "xb_linear_noalloc",
@@ -75,6 +75,7 @@ def load():
   lib.xb_load_weight.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t]
   lib.xb_load_safetensors.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_uint64)]
   lib.xb_weights_missing.argtypes = [C.c_void_p, C.c_char_p, C.c_size_t, C.POINTER(C.c_int)]
+  lib.xb_safetensors_list.argtypes = [C.c_char_p, C.c_char_p, C.c_size_t, C.POINTER(C.c_int)]
   lib.xb_kv_reserve.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
   lib.xb_kv_release_slot.argtypes = [C.c_void_p, C.c_int]
   lib.xb_kv_slot_len.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int)]

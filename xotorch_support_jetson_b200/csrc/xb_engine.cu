@@ -525,6 +525,32 @@ extern "C" int xb_load_safetensors(xb_engine* e, const char* path, int permute_q
   return 0;
 }
 
+// Header of a .safetensors file as text, one tensor per line: "name dtype begin end dim0 dim1 ...".
+// Pure host code (no CUDA call): what xb_load_safetensors would see, for tools and CPU-side tests.
+extern "C" int xb_safetensors_list(const char* path, char* buf, size_t buflen, int* n_tensors) {
+  XB_CHECK(path != nullptr && n_tensors != nullptr, "null argument");
+  StFile f;
+  XB_TRY(f.open_map(path));
+  uint64_t hlen = 0;
+  memcpy(&hlen, f.base, 8);
+  XB_CHECK(hlen > 0 && hlen <= f.size - 8, "%s: bad safetensors header length %llu", path, (unsigned long long)hlen);
+  std::vector<StEntry> entries;
+  XB_CHECK(st_parse_header((const char*)f.base + 8, (size_t)hlen, &entries), "%s: cannot parse the safetensors header", path);
+  std::string out;
+  for (const StEntry& en : entries) {
+    XB_CHECK(en.end <= f.size - 8 - (size_t)hlen, "%s: tensor %s reaches past the end of the file", path, en.name.c_str());
+    out += en.name + " " + en.dtype + " " + std::to_string(en.begin) + " " + std::to_string(en.end);
+    for (long long x : en.shape) out += " " + std::to_string(x);
+    out += "\n";
+  }
+  *n_tensors = (int)entries.size();
+  if (buf != nullptr && buflen > 0) {
+    XB_CHECK(out.size() < buflen, "listing needs %zu bytes, buffer has %zu", out.size() + 1, buflen);
+    memcpy(buf, out.c_str(), out.size() + 1);
+  }
+  return 0;
+}
+
 // Names (ABI kinds) this shard still lacks; 0 in *n_missing = ready.  `buf` receives a readable list.
 extern "C" int xb_weights_missing(xb_engine* e, char* buf, size_t buflen, int* n_missing) {
   XB_CHECK(e != nullptr && n_missing != nullptr, "null argument");
