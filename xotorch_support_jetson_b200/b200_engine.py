@@ -112,6 +112,7 @@ class B200ShardInferenceEngine(InferenceEngine):
       self.rng = torch.Generator(device=st.device)
       self.rng.manual_seed(1234)
       self._stream = torch.cuda.Stream(device=st.device)  # non-default stream: decode steps replay CUDA graphs
+      self._copy_stream = torch.cuda.Stream(device=st.device)   # sampled ids -> host, beside the next step
 
     await asyncio.get_running_loop().run_in_executor(self.executor, start_model)
     self.shard = shard
@@ -127,6 +128,7 @@ class B200ShardInferenceEngine(InferenceEngine):
     self.rng = torch.Generator(device=stage.device)
     self.rng.manual_seed(1234)
     self._stream = torch.cuda.Stream(device=stage.device)
+    self._copy_stream = torch.cuda.Stream(device=stage.device)   # sampled ids -> host, beside the next step
 
   async def _resolve_tokenizer(self, path):
     try:
@@ -227,14 +229,24 @@ class B200ShardInferenceEngine(InferenceEngine):
       self.sample_calls += 1
       # reference semantics at any temperature: logits / max(temp, 1e-5) -> top-k -> softmax -> argmax(p/q)
       toks = st.sample(logits, temp=max(float(temp), 1e-5), top_k=int(top_k or 0), top_p=top_p, q=q, seed=self.sample_calls)
-      host_toks, ev = self._to_host_async(toks)
-      self._speculate(owner, toks, host_toks)   # enqueued BEHIND the id download: does not delay it
+      # The next decode step goes onto the stream right behind the sampler (the GPU never waits for
+      # the host); the ids reach the host through a second stream that only waits for the sampler.
+      sampled = torch.cuda.Event()
+      sampled.record(torch.cuda.current_stream(st.device))
+      self._speculate(owner, toks)
+      side = self._copy_stream
+      side.wait_event(sampled)
+      toks.record_stream(side)
+      with torch.cuda.stream(side):
+        host_toks, ev = self._to_host_async(toks)
+      if self._spec is not None and self._spec.get("toks") is None:
+        self._spec["toks"] = host_toks
       ev.synchronize()
       return np.array(host_toks, dtype=np.int32).reshape(-1, 1)
 
     return await asyncio.get_running_loop().run_in_executor(self.executor, sample_wrapper)
 
-  def _speculate(self, request_id: Optional[str], toks: torch.Tensor, host_toks: np.ndarray):
+  def _speculate(self, request_id: Optional[str], toks: torch.Tensor):
     """Enqueue the decode step the caller is about to ask for (see the module docstring).
     Only when these logits came from ``request_id``'s last forward on a whole-model shard."""
     if not self.speculate_next or request_id is None or self.shard is None:
@@ -250,7 +262,7 @@ class B200ShardInferenceEngine(InferenceEngine):
       out, host, ev = self._forward_logits(st, req.slots, [1] * len(req.slots), [req.pos] * len(req.slots), tokens=toks)
     except RuntimeError:
       return   # e.g. KV pool exhausted: the real call will report it
-    self._spec = {"request_id": request_id, "pos": req.pos, "toks": host_toks, "out": out, "host": host, "event": ev}
+    self._spec = {"request_id": request_id, "pos": req.pos, "toks": None, "out": out, "host": host, "event": ev}   # "toks": filled by sample()
 
   def _take_spec(self, request_id: str, pos: int, x: np.ndarray):
     """The speculated result if (request, position, ids) are exactly the ones it was computed
