@@ -442,9 +442,10 @@ def e2e_engine_api(runner, cfg, prompt, K, W):
   eng.end_request("bench")
   loop_rate = B * K / (stamps[W + K] - stamps[W]) if len(stamps) > W + K else None
   return {"value": B * K / dt, "unit": "tok/s", "h2d_bytes_per_step": B * 4, "d2h_bytes_per_step": B * V * 4 + B * 4,
-          "api": "B200ShardInferenceEngine.infer_tensor(np ids) -> np fp32 logits [B,V] (pinned staging); .sample(that array) -> np ids "
-                 "(reference plugin API, host buffers; the logits array handed back to sample() is recognised and not re-uploaded; "
-                 "sample() enqueues the next decode step on the ids it drew, infer_tensor() with those ids collects it)",
+          "api": "B200ShardInferenceEngine.infer_tensor(np ids) -> np fp32 logits [B,V] (written into pinned host memory by the "
+                 "LM-head kernel itself); .sample(that array) -> np ids (reference plugin API, host buffers; the logits array "
+                 "handed back to sample() is recognised and not re-uploaded; sample() enqueues the next decode step on the ids "
+                 "it drew, infer_tensor() with those ids collects it)",
           "device_loop": {"value": loop_rate, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": B * 4,
                           "api": "B200ShardInferenceEngine.generate(np prompt ids, on_token=cb): sample->forward chained on the "
                                  "device, ids streamed to a pinned table, reference-semantics sampler (top-k 35, q noise) every step"}}
