@@ -393,7 +393,8 @@ struct AttTcCfg {
   static constexpr int Q_BYTES = 128 * HD * 2;
   static constexpr int TILE_BYTES = XB_ATT_TILE * HD * 2;   // one K or V tile
   static constexpr int P_BYTES = XB_ATT_P_TMEM ? 0 : 128 * XB_ATT_TILE * 2;   // P lives in tensor memory
-  static constexpr int NST = 2;                             // K and V ring depth
+  static constexpr int NST = 2;                             // V ring depth
+  static constexpr int NSTK = XB_ATT_P_TMEM ? 3 : 2;        // K ring depth: the 16 KB the P buffer used to take hold a third K tile
   // TWO blocks per SM (measured: 240 us vs 328 us for one block with double-buffered P and 4-deep
   // rings at 4 x 2048 tokens -- the four softmax warps of a block are latency bound, a second
   // block doubles the warps per scheduler).  No alignment slack (with the shared-memory P buffer,
@@ -403,7 +404,7 @@ struct AttTcCfg {
   // columns of the tile's S buffer with tcgen05.st and O += P V takes its A operand from there -- no
   // shared-memory round trip, no proxy fence, and the softmax of tile kt no longer waits for PV of
   // tile kt-1 to release a single P buffer: 212 us against 238 us per layer at 4 x 2048 tokens.
-  static constexpr int SMEM_BYTES = Q_BYTES + NST * 2 * TILE_BYTES + P_BYTES + 256 + XB_ATT_PG_CACHE * 4;
+  static constexpr int SMEM_BYTES = Q_BYTES + (NSTK + NST) * TILE_BYTES + P_BYTES + 256 + XB_ATT_PG_CACHE * 4;
   static constexpr int TM_COLS = 256;                       // S: 64 columns, O: HD columns
 };
 
@@ -421,12 +422,13 @@ __global__ void __launch_bounds__(192, 2) xb_attn_prefill_tc_kernel(
   }
   uint8_t* sQ = smem;
   uint8_t* sKV = sQ + Cfg::Q_BYTES;
-  uint8_t* sP = sKV + Cfg::NST * 2 * Cfg::TILE_BYTES;
+  uint8_t* sVr = sKV + Cfg::NSTK * Cfg::TILE_BYTES;          // K ring first, then the V ring
+  uint8_t* sP = sVr + Cfg::NST * Cfg::TILE_BYTES;
   // K and V have separate rings: a K slot is free as soon as QK^T of its tile retires, a V slot
   // after PV -- the next K load starts a whole tile earlier than with a shared ring
   uint64_t* k_full = reinterpret_cast<uint64_t*>(sP + Cfg::P_BYTES);
-  uint64_t* k_empty = k_full + Cfg::NST;
-  uint64_t* v_full = k_empty + Cfg::NST;
+  uint64_t* k_empty = k_full + Cfg::NSTK;
+  uint64_t* v_full = k_empty + Cfg::NSTK;
   uint64_t* v_empty = v_full + Cfg::NST;
   // the per-tile barriers come in pairs indexed by (tile & 1): each completes every other tile, so a
   // parity wait can never be overrun by the next completion
@@ -450,9 +452,11 @@ __global__ void __launch_bounds__(192, 2) xb_attn_prefill_tc_kernel(
 
   if (warp == 1) {
     if (lane == 0) {
-      for (int i = 0; i < Cfg::NST; ++i) {
+      for (int i = 0; i < Cfg::NSTK; ++i) {
         mbar_init(&k_full[i], 1);
         mbar_init(&k_empty[i], 1);
+      }
+      for (int i = 0; i < Cfg::NST; ++i) {
         mbar_init(&v_full[i], 1);
         mbar_init(&v_empty[i], 1);
       }
@@ -504,14 +508,18 @@ __global__ void __launch_bounds__(192, 2) xb_attn_prefill_tc_kernel(
           for (int db = 0; db < HD / 64; ++db) tma_load_2d(dst + db * (XB_ATT_TILE * 128) + rg * BR * 128, tm, bar, db * 64, row);
         }
       };
+      auto issue_k = [&](int kt) {
+        const int ks = kt % Cfg::NSTK;
+        mbar_wait(&k_empty[ks], ((kt / Cfg::NSTK) & 1) ^ 1);
+        issue(&tmK, sKV + ks * Cfg::TILE_BYTES, &k_full[ks], kt);
+      };
+      // K runs one tile ahead of V (QK^T of tile kt+1 is issued before PV of tile kt)
+      issue_k(0);
       for (int kt = 0; kt < n_kt; ++kt) {
-        const int stage = kt % Cfg::NST;
-        const uint32_t ph = (kt / Cfg::NST) & 1;
-        uint8_t* sK = sKV + stage * 2 * Cfg::TILE_BYTES;
-        mbar_wait(&k_empty[stage], ph ^ 1);
-        issue(&tmK, sK, &k_full[stage], kt);
-        mbar_wait(&v_empty[stage], ph ^ 1);
-        issue(&tmV, sK + Cfg::TILE_BYTES, &v_full[stage], kt);
+        if (kt + 1 < n_kt) issue_k(kt + 1);
+        const int vs = kt % Cfg::NST;
+        mbar_wait(&v_empty[vs], ((kt / Cfg::NST) & 1) ^ 1);
+        issue(&tmV, sVr + vs * Cfg::TILE_BYTES, &v_full[vs], kt);
       }
     }
   } else if (warp == 1) {
@@ -523,10 +531,10 @@ __global__ void __launch_bounds__(192, 2) xb_attn_prefill_tc_kernel(
       tc_fence_after();
       const uint32_t q_addr = smem_u32(sQ), p_addr = smem_u32(sP);
       auto issue_qk = [&](int kt) {
-        const int stage = kt % Cfg::NST;
-        mbar_wait(&k_full[stage], (kt / Cfg::NST) & 1);
+        const int stage = kt % Cfg::NSTK;
+        mbar_wait(&k_full[stage], (kt / Cfg::NSTK) & 1);
         tc_fence_after();
-        const uint32_t k_addr = smem_u32(sKV + stage * 2 * Cfg::TILE_BYTES);
+        const uint32_t k_addr = smem_u32(sKV + stage * Cfg::TILE_BYTES);
         const uint32_t d = tm_S + (uint32_t)((kt & 1) * XB_ATT_TILE);
         // S = Q K^T over hd in steps of 16; dims 64.. live in the second 128-byte-wide region
 #pragma unroll
@@ -543,7 +551,7 @@ __global__ void __launch_bounds__(192, 2) xb_attn_prefill_tc_kernel(
         // S buffer (kt+1)&1 was last read by the softmax of tile kt-1, which finished before p_full(kt-1)
         if (kt + 1 < n_kt) issue_qk(kt + 1);
         const int stage = kt % Cfg::NST;
-        const uint32_t v_addr = smem_u32(sKV + stage * 2 * Cfg::TILE_BYTES) + Cfg::TILE_BYTES;
+        const uint32_t v_addr = smem_u32(sVr + stage * Cfg::TILE_BYTES);
         // O += P V over the 64 keys in steps of 16
         mbar_wait(&v_full[stage], (kt / Cfg::NST) & 1);
         mbar_wait(&p_full[kt & 1], (kt >> 1) & 1);
