@@ -36,6 +36,7 @@ from __future__ import annotations
 
 import json
 import math
+import os
 from dataclasses import dataclass, field
 from pathlib import Path
 from typing import Dict, List, Optional, Tuple
@@ -83,6 +84,9 @@ def model_config_from_hf(base: dict) -> dict:
   if cfg.get("rope_scaling") is not None:
     # llm_utils.py:68-69 -- reads "rope_factor" (absent in HF configs) => always 32
     cfg["rope_scaling_factor"] = cfg["rope_scaling"].get("rope_factor", 32)
+    # llm_utils.py:71-73 (found by the reference-run fixture, tests/golden/ref_config_permute_state.json)
+    if os.getenv("TORCH_USE_ORG_SEQ", "False").lower() == "true":
+      cfg["max_seq_len"] = cfg["rope_scaling"]["original_max_position_embeddings"]
   return cfg
 
 
@@ -401,8 +405,12 @@ class OracleEngine:
     self.rng = torch.Generator(device=model.device)
     self.rng.manual_seed(seed)
 
-  def start_request(self, tokens: torch.Tensor):
-    """encode() after tokenisation (sharded_inference_engine.py:131-186), no-pad branch."""
+  def start_request(self, tokens: torch.Tensor, pad_id: Optional[int] = None):
+    """encode() after tokenisation (sharded_inference_engine.py:131-186).  ``pad_id``: what the
+    reference resolves at :153-163 (tokenizer.pad_id, else pad_token_id, else 0); None = treat
+    no id as padding.  A prompt holding that id takes the padded branch (:165-177): positions
+    skip the padded slots and padded keys are never attended (torchtune.generation's
+    get_causal_mask_from_padding_mask / get_position_ids_from_padding_mask, 0.6.1, restated)."""
     m = self.model
     self.curr_pos = 0
     if m.caches_are_enabled():
@@ -412,8 +420,18 @@ class OracleEngine:
     total = tklng + m.options.max_generated_tokens
     if not m.caches_are_enabled() or m.cache_len != total or next(iter(m.k_cache.values())).size(0) != bsz:
       m.setup_caches(bsz, total)
-    self.mask = torch.tril(torch.ones(total, total, dtype=torch.bool, device=m.device)).unsqueeze(0)
-    self.input_pos = torch.arange(0, total, device=m.device).unsqueeze(0)
+    padding_masks = tokens != pad_id if pad_id is not None else torch.ones_like(tokens, dtype=torch.bool)
+    if not padding_masks.all():
+      padding_masks = F.pad(padding_masks, (0, m.options.max_generated_tokens), value=True)
+      seq_len = padding_masks.size(1)
+      mask = torch.tril(torch.ones(seq_len, total, dtype=torch.bool, device=m.device)).repeat(bsz, 1, 1)
+      mask.narrow(2, 0, seq_len).mul_(padding_masks[:, None, :].expand(-1, seq_len, seq_len))
+      mask.diagonal(dim1=1, dim2=2).fill_(True)
+      self.mask = mask
+      self.input_pos = ((padding_masks.cumsum(-1) - 1) * padding_masks).to(torch.int)
+    else:
+      self.mask = torch.tril(torch.ones(total, total, dtype=torch.bool, device=m.device)).unsqueeze(0)
+      self.input_pos = torch.arange(0, total, device=m.device).unsqueeze(0)
 
   def infer_tensor(self, input_data: np.ndarray, taps=None) -> np.ndarray:
     """sharded_inference_engine.py:230-370: 2-D int = tokens, 3-D float = hidden."""

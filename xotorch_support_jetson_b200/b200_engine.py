@@ -10,7 +10,9 @@ Differences that are deliberate ("known defects"):
   from positions;
 * a non-last shard returns the output of its last layer (the reference's off-by-one
   hand-off is not reproduced), so any split reproduces the full-shard result;
-* out-of-memory and every other native failure raise (the reference returns ``None``).
+* out-of-memory and every other native failure raise (the reference returns ``None``);
+* a prompt that holds the pad id (the reference's padded branch) is run compacted: same result for
+  every real token, padded slots get no KV entry (``_forward_padded_prompt``).
 
 Host round trip.  The plugin API makes every decode step cross the host twice (logits out,
 sampled ids back in).  When this engine holds the whole model (first AND last layer) it
@@ -46,12 +48,67 @@ TEMP = 0.6
 TOP_K = 35
 
 
+def state_position(inference_state: Optional[dict]) -> Optional[int]:
+  """``curr_pos`` of the state dict that travels with a request (the reference's
+  ``ShardInferenceState.to_dict``, llm_utils.py:497-503; its ``input_pos`` / ``mask`` entries, when a
+  reference node made the dict, are ignored: causality follows from the position)."""
+  if not inference_state:
+    return None
+  p = inference_state.get("curr_pos")
+  return None if p is None else int(p)
+
+
+def state_to_dict(tokens: Optional[List[List[int]]], curr_pos: int) -> dict:
+  """The state this engine hands back: the reference's field names, types and nesting for the two
+  entries it needs (JSON-able, survives the gRPC hop of grpc_peer_handle.py:209-230)."""
+  out = {"curr_pos": int(curr_pos)}
+  if tokens is not None:
+    out["tokens"] = [row[:] for row in tokens]   # snapshot, like ShardInferenceState.to_dict
+  return out
+
+
+class _PinnedPool:
+  """Page-locked host buffers behind the numpy arrays the plugin API hands out.
+
+  SURVEY 8b: results are host-owned arrays the caller may keep (the reference's own contract test
+  holds two results and compares them, xotorch/inference/test_inference_engine.py:43-44; a node may
+  hold a hidden state while it serialises it for the next peer).  So a buffer belongs to the array
+  that was returned -- and to every view derived from it -- for as long as the caller keeps it:
+  a ``weakref.finalize`` on the array puts the buffer back on the free list when the last reference
+  goes away; nothing is ever overwritten under a live array, and in steady state (the caller drops
+  each result before asking for the next few) no page-locked memory is allocated after warm-up."""
+
+  def __init__(self):
+    self.free: Dict[tuple, list] = {}
+    self.allocated = 0
+
+  def take(self, dtype: torch.dtype, shape) -> tuple:
+    """(pinned tensor viewed as ``shape``, read-only numpy array over the same memory)."""
+    import weakref
+    n = 1
+    for d in shape:
+      n *= int(d)
+    n = max(n, 1)
+    cap = 1 << (n - 1).bit_length()           # power-of-two size classes
+    lst = self.free.setdefault((dtype, cap), [])
+    base = lst.pop() if lst else None
+    if base is None:
+      base = torch.empty(cap, dtype=dtype).pin_memory()
+      self.allocated += 1
+    buf = base[:n].view(tuple(int(d) for d in shape))
+    arr = buf.numpy()
+    arr.setflags(write=False)
+    weakref.finalize(arr, lst.append, base)
+    return buf, arr
+
+
 class _Request:
-  __slots__ = ("slots", "pos", "tokens")
+  __slots__ = ("slots", "pos", "tokens", "skip")
 
   def __init__(self, slots: List[int]):
     self.slots = slots
-    self.pos = 0
+    self.pos = 0          # the reference's curr_pos: counts every prompt slot, padded ones included
+    self.skip = [0] * len(slots)   # padded prompt slots of each row (they occupy no KV position here)
     # token history per row as Python ints: a decode step appends one id per row, so the
     # ``tokens`` entry of the returned state costs O(B) + a pointer copy, not a fresh
     # ndarray.tolist() of the whole history (1.2 ms per step at 32 x 2100 ids)
@@ -83,9 +140,9 @@ class B200ShardInferenceEngine(InferenceEngine):
     self.rng = None
     self.sample_calls = 0
     # host staging: the [B, vocab] fp32 logits the plugin API returns are tens of MB per step, so
-    # they land in a small ring of PINNED buffers (a numpy view is returned, valid until the
-    # ring wraps) and the device copy is kept so that sample() on that very array skips the upload
-    self._pin_rings: Dict[torch.dtype, list] = {}   # dtype -> [buffers, next index]
+    # they land in PINNED buffers that the returned numpy arrays own (recycled once the caller has
+    # dropped the array), and the device copy is kept so that sample() on that very array skips the upload
+    self._pinned = _PinnedPool()
     self._last_logits = None   # (numpy view handed to the caller, device tensor it mirrors, request id)
     self.speculate_next = (env.get("XB_API_SPECULATE", "1") != "0") if speculate_next is None else bool(speculate_next)
     self.direct_host_logits = env.get("XB_API_DIRECT_LOGITS", "1") != "0"   # LM head stores the logits into pinned host memory itself
@@ -158,52 +215,33 @@ class B200ShardInferenceEngine(InferenceEngine):
       self.executor, functools.partial(self.tokenizer.decode, np.asarray(tokens).reshape(-1).tolist()))
 
   # ------------------------------------------------------------------ host staging
-  PIN_RING = 6
-
   def _to_host(self, dev: torch.Tensor) -> np.ndarray:
     arr, ev = self._to_host_async(dev)
     ev.synchronize()
     return arr
 
   def _to_host_async(self, dev: torch.Tensor):
-    """Device tensor -> numpy through a pinned ring buffer (one DMA, no pageable bounce).  The
-    returned array is a read-only view that stays valid for the next PIN_RING-1 results; its
-    contents are defined once the returned event has completed."""
-    buf = self._ring_buffer(dev.dtype, dev.shape)
+    """Device tensor -> numpy through a pinned buffer (one DMA, no pageable bounce).  The returned
+    read-only array OWNS its buffer (see _PinnedPool); its contents are defined once the returned
+    event has completed."""
+    buf, arr = self._pinned.take(dev.dtype, dev.shape)
     buf.copy_(dev, non_blocking=True)
     ev = torch.cuda.Event()
     ev.record(torch.cuda.current_stream(dev.device))
-    arr = buf.numpy()
-    arr.setflags(write=False)
     return arr, ev
-
-  def _ring_buffer(self, dtype: torch.dtype, shape) -> torch.Tensor:
-    """Next pinned host buffer of the ring for this dtype, viewed as ``shape``."""
-    n = 1
-    for d in shape:
-      n *= int(d)
-    ring = self._pin_rings.get(dtype)
-    if ring is None or ring[0][0].numel() < n:
-      ring = [[torch.empty(max(n, 1), dtype=dtype).pin_memory() for _ in range(self.PIN_RING)], 0]
-      self._pin_rings[dtype] = ring
-    buf = ring[0][ring[1]][:n].view(tuple(shape))
-    ring[1] = (ring[1] + 1) % self.PIN_RING
-    return buf
 
   def _forward_logits(self, st: StageRuntime, slots, q_lens, positions, **inp):
     """One native forward on a last shard whose logits go to the host: (device logits, numpy
-    view, event).  With ``direct_host_logits`` the LM-head kernel stores them into the pinned ring
+    view, event).  With ``direct_host_logits`` the LM-head kernel stores them into the pinned
     buffer itself (xb_forward_host_logits); otherwise a device-to-host copy follows the forward."""
     if not self.direct_host_logits:
       out = st.forward(slots, q_lens, positions, **inp)
       host, ev = self._to_host_async(out)
       return out, host, ev
-    buf = self._ring_buffer(torch.float32, (len(slots), st.vocab))
+    buf, arr = self._pinned.take(torch.float32, (len(slots), st.vocab))
     out = st.forward(slots, q_lens, positions, host_logits=buf, **inp)
     ev = torch.cuda.Event()
     ev.record(torch.cuda.current_stream(st.device))
-    arr = buf.numpy()
-    arr.setflags(write=False)
     return out, arr, ev
 
   # ------------------------------------------------------------------ sampling
@@ -259,7 +297,7 @@ class B200ShardInferenceEngine(InferenceEngine):
     if req is None or len(req.slots) != toks.numel() or req.pos + 1 > st.max_tokens_per_seq or len(req.slots) > st.max_batch_tokens:
       return
     try:
-      out, host, ev = self._forward_logits(st, req.slots, [1] * len(req.slots), [req.pos] * len(req.slots), tokens=toks)
+      out, host, ev = self._forward_logits(st, req.slots, [1] * len(req.slots), self._positions(req, req.pos), tokens=toks)
     except RuntimeError:
       return   # e.g. KV pool exhausted: the real call will report it
     self._spec = {"request_id": request_id, "pos": req.pos, "toks": None, "out": out, "host": host, "event": ev}   # "toks": filled by sample()
@@ -309,6 +347,18 @@ class B200ShardInferenceEngine(InferenceEngine):
         self.stage.release_slot(s)
         self.free_slots.append(s)
 
+  def _pad_id(self) -> int:
+    """The id the reference treats as padding (sharded_inference_engine.py:153-163): the tokenizer's
+    ``pad_id``, else its ``pad_token_id``, else -- also when that is None -- 0."""
+    tk = self.tokenizer
+    if hasattr(tk, "pad_id"):
+      return tk.pad_id
+    pid = getattr(tk, "pad_token_id", None)
+    return 0 if pid is None else pid
+
+  def _positions(self, req: _Request, pos: int) -> List[int]:
+    return [pos - k for k in req.skip]
+
   def _forward_chunked(self, st: StageRuntime, req: _Request, dev_in: torch.Tensor, bsz: int, s: int, pos: int,
                        is_tokens: bool, to_host: bool = True):
     """One logical forward over [bsz, s] rows, split so that no native call carries more
@@ -316,12 +366,13 @@ class B200ShardInferenceEngine(InferenceEngine):
     sequence (chunked prefill) when a single sequence is longer than that."""
     cap = st.max_batch_tokens
     last = self.shard.is_last_layer()
+    positions = self._positions(req, pos)
     if bsz * s <= cap:
       flat = dev_in.reshape(-1) if is_tokens else dev_in.reshape(bsz * s, -1)
       inp = {"tokens": flat} if is_tokens else {"hidden": flat}
       if last and to_host:
-        return self._forward_logits(st, req.slots, [s] * bsz, [pos] * bsz, **inp)   # (device logits, host view, event)
-      return st.forward(req.slots, [s] * bsz, [pos] * bsz, **inp)
+        return self._forward_logits(st, req.slots, [s] * bsz, positions, **inp)   # (device logits, host view, event)
+      return st.forward(req.slots, [s] * bsz, positions, **inp)
     outs = []
     if s <= cap:
       per = max(1, cap // s)
@@ -329,19 +380,70 @@ class B200ShardInferenceEngine(InferenceEngine):
         b1 = min(bsz, b0 + per)
         part = dev_in[b0:b1]
         flat = part.reshape(-1) if is_tokens else part.reshape((b1 - b0) * s, -1)
-        outs.append(st.forward(req.slots[b0:b1], [s] * (b1 - b0), [pos] * (b1 - b0),
+        outs.append(st.forward(req.slots[b0:b1], [s] * (b1 - b0), positions[b0:b1],
                                **({"tokens": flat} if is_tokens else {"hidden": flat})))
       return torch.cat(outs, dim=0)
     for b in range(bsz):
-      seq_out = []
-      for c0 in range(0, s, cap):
-        c1 = min(s, c0 + cap)
-        part = dev_in[b, c0:c1]
-        flat = part.reshape(-1) if is_tokens else part.reshape(c1 - c0, -1)
-        o = st.forward([req.slots[b]], [c1 - c0], [pos + c0], **({"tokens": flat} if is_tokens else {"hidden": flat}))
-        seq_out.append(o)
-      outs.append(seq_out[-1] if last else torch.cat(seq_out, dim=0))
+      outs.append(self._forward_one_sequence(st, req.slots[b], dev_in[b], positions[b], is_tokens))
     return torch.cat(outs, dim=0)
+
+  def _forward_one_sequence(self, st: StageRuntime, slot: int, rows: torch.Tensor, pos: int, is_tokens: bool) -> torch.Tensor:
+    """rows: ids [n] or hidden [n, D] of ONE sequence, run in position chunks of at most max_batch_tokens.
+    Returns hidden [n, D] (non-last shard) or the logits [1, V] of the last row."""
+    cap, n = st.max_batch_tokens, rows.shape[0]
+    seq_out = []
+    for c0 in range(0, n, cap):
+      c1 = min(n, c0 + cap)
+      part = rows[c0:c1].contiguous()
+      flat = part.reshape(-1) if is_tokens else part.reshape(c1 - c0, -1)
+      seq_out.append(st.forward([slot], [c1 - c0], [pos + c0], **({"tokens": flat} if is_tokens else {"hidden": flat})))
+    return seq_out[-1] if self.shard.is_last_layer() else torch.cat(seq_out, dim=0)
+
+  def _forward_padded_prompt(self, st: StageRuntime, req: _Request, dev_in: torch.Tensor, keep: np.ndarray, is_tokens: bool):
+    """Prompt holding the pad id (the reference's padded branch, sharded_inference_engine.py:165-177:
+    positions from the padding mask, padded keys never attended).  Real tokens never see a padded
+    key and their positions are the running count of real tokens, so running ONLY the real tokens,
+    compacted, gives them exactly the reference's result; the padded slots get no KV entry here.
+    Differences, by construction invisible to real tokens: rows of padded slots in a returned hidden
+    state are zero (the reference computes a row that attends itself), and the logits come from the
+    last REAL prompt token (the reference takes row -1 even when that slot is padding)."""
+    bsz, s = keep.shape
+    last = self.shard.is_last_layer()
+    outs = []
+    for b in range(bsz):
+      kb = keep[b].copy()
+      if not kb.any():
+        kb[-1] = True   # a row of nothing but padding: its last slot stands for the row (position 0, attends itself)
+      idx = torch.as_tensor(np.nonzero(kb)[0], device=dev_in.device)
+      req.skip[b] = int(s - idx.numel())
+      o = self._forward_one_sequence(st, req.slots[b], dev_in[b].index_select(0, idx), 0, is_tokens)
+      if last:
+        outs.append(o)
+      else:
+        full = torch.zeros((s, o.shape[-1]), dtype=o.dtype, device=o.device)
+        full.index_copy_(0, idx, o)
+        outs.append(full)
+    return torch.cat(outs, dim=0)
+
+  def _prompt_keep_mask(self, x: np.ndarray, inference_state: Optional[dict], bsz: int, s: int, pos: int) -> Optional[np.ndarray]:
+    """bool [bsz, s] of the prompt slots that are NOT padding, or None when the prompt holds no pad
+    id (the usual case: the reference's ``tril`` branch).  Only a prompt (multi-token input at
+    position 0) is examined -- a generated id equal to the pad id is an ordinary token, as in the
+    reference, whose padding mask is extended with True over the generated slots.  A later shard
+    sees hidden rows, not ids: it finds the ids in the ``tokens`` entry of the travelling state."""
+    if pos != 0 or s <= 1:
+      return None
+    if x.ndim == 2:
+      ids = x
+    else:
+      hist = (inference_state or {}).get("tokens")
+      if hist is None:
+        return None
+      ids = np.asarray(hist)
+      if ids.ndim != 2 or ids.shape != (bsz, s):
+        return None
+    keep = ids != self._pad_id()
+    return None if keep.all() else keep
 
   async def infer_tensor(self, request_id: str, shard: Shard, input_data: np.ndarray,
                          inference_state: Optional[dict] = None) -> tuple[np.ndarray, Optional[dict]]:
@@ -360,7 +462,7 @@ class B200ShardInferenceEngine(InferenceEngine):
         bsz, s = x.shape[0], x.shape[1]
       else:
         raise ValueError(f"input_data must be 2-D token ids or 3-D hidden states, got ndim={x.ndim}")
-      state_pos = None if not inference_state else inference_state.get("curr_pos")
+      state_pos = state_position(inference_state)
       req = self.requests.get(request_id)
       # a new request starts with a multi-token input at position 0 (encode() resets the
       # reference's state the same way, sharded_inference_engine.py:131-147)
@@ -374,22 +476,28 @@ class B200ShardInferenceEngine(InferenceEngine):
         else:
           for row, t in zip(req.tokens, x[:, 0].tolist()):
             row.append(int(t))
+      elif inference_state and inference_state.get("tokens") is not None:
+        # a later shard: the history arrives with the state (ShardInferenceState.from_dict, llm_utils.py:489-495)
+        # and is handed on unchanged
+        req.tokens = inference_state["tokens"]
       if x.ndim == 2:   # the caller's ids always go to the device, also when the step below is already in flight
         dev_in = torch.as_tensor(np.ascontiguousarray(x, dtype=np.int32)).to(st.device, non_blocking=True)
       if sp is not None:   # this very step was enqueued by sample() on the same ids (checked on the host)
         return finish(req, sp["out"], sp["host"], sp["event"], bsz, s, pos)
       if x.ndim == 3:
         dev_in = torch.as_tensor(np.ascontiguousarray(x, dtype=np.float32)).to(st.device, non_blocking=True).to(torch.bfloat16)
-      out = self._forward_chunked(st, req, dev_in, bsz, s, pos, x.ndim == 2)
+      keep = self._prompt_keep_mask(x, inference_state, bsz, s, pos)
+      if keep is not None:
+        out = self._forward_padded_prompt(st, req, dev_in, keep, x.ndim == 2)
+      else:
+        out = self._forward_chunked(st, req, dev_in, bsz, s, pos, x.ndim == 2)
       if isinstance(out, tuple):
         return finish(req, out[0], out[1], out[2], bsz, s, pos)
       return finish(req, out, None, None, bsz, s, pos)
 
     def finish(req, out, host, ev, bsz, s, pos):
       req.pos = pos + s
-      new_state = {"curr_pos": pos if not shard.is_last_layer() else pos + s}
-      if req.tokens is not None:
-        new_state["tokens"] = [row[:] for row in req.tokens]   # snapshot, like ShardInferenceState.to_dict (llm_utils.py:497-503)
+      new_state = state_to_dict(req.tokens, pos if not shard.is_last_layer() else pos + s)
       if shard.is_last_layer():
         if host is None:
           host, ev = self._to_host_async(out)          # fp32 [B, V]
@@ -437,7 +545,7 @@ class B200ShardInferenceEngine(InferenceEngine):
       if x.ndim != 2:
         raise ValueError(f"generate() takes 2-D token ids, got ndim={x.ndim}")
       bsz, s = x.shape
-      state_pos = None if not inference_state else inference_state.get("curr_pos")
+      state_pos = state_position(inference_state)
       req = self.requests.get(request_id)
       if req is None or (state_pos == 0) or (state_pos is None and s > 1) or len(req.slots) != bsz:
         req = self._start_request(request_id, bsz)
@@ -449,7 +557,11 @@ class B200ShardInferenceEngine(InferenceEngine):
         for row, t in zip(req.tokens, x[:, 0].tolist()):
           row.append(int(t))
       dev_in = torch.as_tensor(np.ascontiguousarray(x, dtype=np.int32)).to(st.device, non_blocking=True)
-      logits = self._forward_chunked(st, req, dev_in, bsz, s, pos, True, to_host=False)
+      keep = self._prompt_keep_mask(x, inference_state, bsz, s, pos)
+      if keep is not None:
+        logits = self._forward_padded_prompt(st, req, dev_in, keep, True)
+      else:
+        logits = self._forward_chunked(st, req, dev_in, bsz, s, pos, True, to_host=False)
       pos += s
       # id n is drawn from the forward at position pos+n-2, which must exist in the KV slot
       cap = max(1, min(int(max_generate_tokens), st.max_tokens_per_seq - pos + 1))
@@ -476,7 +588,7 @@ class B200ShardInferenceEngine(InferenceEngine):
           rewind.append((self.rng.get_state() if q is not None else None, self.sample_calls))
           n_enq += 1
           if n_enq < cap:   # id number n_enq enters the KV slot at position pos + n_enq - 1
-            logits = st.forward(req.slots, [1] * bsz, [pos + n_enq - 1] * bsz, tokens=toks)
+            logits = st.forward(req.slots, [1] * bsz, self._positions(req, pos + n_enq - 1), tokens=toks)
         events[n_acc].synchronize()
         ids = table_np[n_acc]
         n_acc += 1
@@ -494,7 +606,7 @@ class B200ShardInferenceEngine(InferenceEngine):
       for row, fed in zip(req.tokens, out_ids[:, :n_acc - 1].tolist()):        # all but the last id went through the model
         row.extend(fed)
       req.pos = pos + n_acc - 1
-      return out_ids, {"curr_pos": req.pos, "tokens": [row[:] for row in req.tokens]}
+      return out_ids, state_to_dict(req.tokens, req.pos)
 
     return await loop.run_in_executor(self.executor, gen_wrapper)
 
