@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define XB_ABI_VERSION 2
+#define XB_ABI_VERSION 3
 
 typedef struct xb_engine xb_engine;
 
@@ -41,6 +41,8 @@ enum {
  * load_model_config (xotorch/inference/torch/models/llm_utils.py:30-77) plus the Shard key
  * (xotorch/inference/shard.py:4-39: start_layer/end_layer inclusive). */
 typedef struct xb_model_desc {
+  uint32_t struct_size;      /* = sizeof(xb_model_desc) of the header the CALLER was built against; xb_engine_create
+                                refuses a descriptor whose size differs from the library's (stale binding) */
   int32_t n_layers, start_layer, end_layer;
   int32_t dim, n_heads, n_kv_heads, head_dim, inter_dim, vocab;
   float norm_eps;
@@ -173,6 +175,17 @@ int xb_handoff_create(xb_engine* e, int n_slots, int rows, void* landing_handle,
 int xb_handoff_connect(xb_engine* e, const void* next_landing_handle, const void* next_flag_handle);
 int xb_forward_handoff(xb_engine* e, const xb_batch* batch, int slot_in, int wait_value, int slot_out, int signal_value,
                        void* out, void* stream);
+/* xb_handoff_connect for two stages that live in ONE process (an in-process ring of per-GPU nodes, or two
+ * stages on one GPU in a test): `e` stores straight into `next`'s landing buffers through their device
+ * addresses, no CUDA IPC handle involved (xb_handoff_create may then be given NULL for both handle
+ * buffers); peer access from e's device to next's is enabled when they differ.  Both stages must have
+ * called xb_handoff_create with the same geometry.  `next` must outlive the connection. */
+int xb_handoff_connect_local(xb_engine* e, xb_engine* next);
+/* A consumer stage whose producer never signalled does not kill the CUDA context: after the time-out
+ * (XB_HANDOFF_TIMEOUT_S, default 30 s) the waiting kernel records the slot in a host-visible error word
+ * and lets the step finish on whatever the landing buffer holds; every later xb_forward* call on that
+ * engine fails with the recorded message until xb_handoff_clear_error is called. */
+int xb_handoff_clear_error(xb_engine* e);
 
 /* Replaces TorchDynamicShardInferenceEngine.sample + torchtune.generation.sample
  * (sharded_inference_engine.py:208-228).  logits: device fp32 [n, vocab].

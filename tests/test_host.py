@@ -127,9 +127,14 @@ def test_cabi_exports_every_declared_symbol(built_lib):
   raw = ctypes.CDLL(str(_cabi.lib_path()))
   for name in declared:
     assert hasattr(raw, name), f"libxb200.so does not export {name}"
-  assert built_lib.xb_abi_version() == 2
-  # struct layouts the Python side mirrors
-  assert ctypes.sizeof(_cabi.ModelDesc) == 19 * 4 and ctypes.sizeof(_cabi.Counters) == 6 * 8
+  assert built_lib.xb_abi_version() == _cabi.ABI_VERSION == int(re.search(r"#define XB_ABI_VERSION (\d+)", header).group(1))
+  # struct layouts the Python side mirrors: every xb_model_desc field of the header, in order
+  body = re.search(r"typedef struct xb_model_desc \{(.*?)\} xb_model_desc;", header, flags=re.S).group(1)
+  body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+  fields = [n.strip() for decl in re.findall(r"(?:u?int32_t|float)\s+([^;]+);", body) for n in decl.split(",")]
+  assert fields == [n for n, _ in _cabi.ModelDesc._fields_]
+  assert ctypes.sizeof(_cabi.ModelDesc) == 20 * 4 and ctypes.sizeof(_cabi.Counters) == 6 * 8
+  assert _cabi.model_desc(n_layers=1).struct_size == 80
 
 
 @pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
@@ -140,7 +145,7 @@ def test_compute_path_fails_loudly_without_gpu(built_lib):
   from xotorch_support_jetson_b200.shard import Shard
   from xotorch_support_jetson_b200.stage import StageRuntime
   from oracle.torch_oracle import model_config_from_hf
-  d = _cabi.ModelDesc(n_layers=4, start_layer=0, end_layer=3, dim=256, n_heads=8, n_kv_heads=2, head_dim=64, inter_dim=512,
+  d = _cabi.model_desc(n_layers=4, start_layer=0, end_layer=3, dim=256, n_heads=8, n_kv_heads=2, head_dim=64, inter_dim=512,
                       vocab=1024, norm_eps=1e-5, max_positions=64, max_batch_tokens=16, max_seqs=2)
   h = ctypes.c_void_p()
   rc = built_lib.xb_engine_create(ctypes.byref(d), 0, ctypes.byref(h))

@@ -41,6 +41,26 @@ def test_noalloc_linear_matches_existing_entry_point_on_consecutive_calls(built_
     assert (y - fp32).abs().max().item() <= 1e-4 * scale, (i, T, N, K)
 
 
+def test_noalloc_linear_allocates_nothing(built_lib):
+  """The point of the entry point: once it has run on a device, a call changes neither the
+  driver's free-memory figure nor the framework allocator's counters."""
+  from xotorch_support_jetson_b200.stage import linear_noalloc
+  x, w = _pair(32, 4096, 4096, seed=1)
+  y = torch.empty((32, 4096), dtype=torch.float32, device="cuda")
+  linear_noalloc(x, w, y)            # first call on the device: resolves the built-in array's address
+  torch.cuda.synchronize()
+  free0, _ = torch.cuda.mem_get_info()
+  stats0 = torch.cuda.memory_stats()
+  for _ in range(3):
+    linear_noalloc(x, w, y)
+  torch.cuda.synchronize()
+  free1, _ = torch.cuda.mem_get_info()
+  stats1 = torch.cuda.memory_stats()
+  assert free1 == free0
+  for k in ("allocation.all.allocated", "segment.all.allocated", "allocated_bytes.all.current", "reserved_bytes.all.current"):
+    assert stats1.get(k) == stats0.get(k), k
+
+
 def test_noalloc_linear_rounding_mode_and_rejections(built_lib):
   from xotorch_support_jetson_b200.stage import debug_linear, linear_noalloc
   x, w = _pair(16, 768, 512, seed=7)

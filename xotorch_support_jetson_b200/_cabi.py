@@ -12,7 +12,7 @@ SYMBOLS = (
   "xb_last_error", "xb_abi_version", "xb_engine_create", "xb_engine_destroy", "xb_load_weight",
   "xb_load_safetensors", "xb_weights_missing", "xb_safetensors_list",
   "xb_kv_reserve", "xb_kv_release_slot", "xb_kv_slot_len", "xb_forward", "xb_forward_host_logits", "xb_sample",
-  "xb_handoff_create", "xb_handoff_connect", "xb_forward_handoff",
+  "xb_handoff_create", "xb_handoff_connect", "xb_forward_handoff", "xb_handoff_connect_local", "xb_handoff_clear_error",
   "xb_get_counters", "xb_debug_linear", "xb_bench_linears", "xb_bench_attention", "xb_linear_noalloc",
 )
 
@@ -25,6 +25,7 @@ ROPE_INTERLEAVED, ROPE_HALF_SPLIT = 0, 1
 
 class ModelDesc(C.Structure):
   _fields_ = [
+    ("struct_size", C.c_uint32),   # sizeof(xb_model_desc) as this binding knows it (filled in by model_desc())
     ("n_layers", C.c_int32), ("start_layer", C.c_int32), ("end_layer", C.c_int32),
     ("dim", C.c_int32), ("n_heads", C.c_int32), ("n_kv_heads", C.c_int32), ("head_dim", C.c_int32),
     ("inter_dim", C.c_int32), ("vocab", C.c_int32),
@@ -33,6 +34,14 @@ class ModelDesc(C.Structure):
     ("max_positions", C.c_int32), ("max_batch_tokens", C.c_int32), ("max_seqs", C.c_int32),
     ("first_from_mlp", C.c_int32), ("last_to_attn", C.c_int32),
   ]
+
+
+ABI_VERSION = 3
+
+
+def model_desc(**fields) -> ModelDesc:
+  """ModelDesc with ``struct_size`` set: xb_engine_create rejects a descriptor laid out by another header."""
+  return ModelDesc(struct_size=C.sizeof(ModelDesc), **fields)
 
 
 class Batch(C.Structure):
@@ -83,6 +92,8 @@ def load():
   lib.xb_forward_host_logits.argtypes = [C.c_void_p, C.POINTER(Batch), C.c_void_p, C.c_void_p, C.c_void_p]
   lib.xb_handoff_create.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
   lib.xb_handoff_connect.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+  lib.xb_handoff_connect_local.argtypes = [C.c_void_p, C.c_void_p]
+  lib.xb_handoff_clear_error.argtypes = [C.c_void_p]
   lib.xb_forward_handoff.argtypes = [C.c_void_p, C.POINTER(Batch), C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
   lib.xb_sample.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_float, C.c_void_p, C.c_uint64,
                             C.c_void_p, C.c_void_p]
@@ -96,6 +107,8 @@ def load():
     fn = getattr(lib, name)
     if name not in ("xb_last_error",):
       fn.restype = C.c_int
+  if lib.xb_abi_version() != ABI_VERSION:
+    raise RuntimeError(f"{p} exports ABI v{lib.xb_abi_version()}, this binding is for v{ABI_VERSION}: rebuild the library")
   _lib = lib
   return lib
 

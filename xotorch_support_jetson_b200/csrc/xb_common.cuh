@@ -9,6 +9,8 @@
 
 typedef __nv_bfloat16 bf16;
 
+#define XB_MAX_DEVICES 64   // per-device caches (kernel attributes, built-in scratch address) are indexed by device ordinal
+
 // ----------------------------------------------------------------------------- errors
 // Thread-local message returned by xb_last_error(); no C++ exception crosses the C ABI.
 extern thread_local std::string g_xb_err;

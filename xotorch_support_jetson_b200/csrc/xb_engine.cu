@@ -78,6 +78,10 @@ struct xb_engine {
   bf16* peer_landing = nullptr;
   uint32_t* peer_flags = nullptr;
   int ho_slots = 0, ho_rows = 0;
+  bool peer_is_local = false;       // peer_landing / peer_flags are plain device pointers of an engine in this process
+  long long ho_timeout_cycles = 0;  // consumer-side wait budget (XB_HANDOFF_TIMEOUT_S)
+  int* ho_err = nullptr;            // mapped host memory {slot + 1, wait value}: written by the waiting kernel on time-out
+  int* ho_err_dev = nullptr;        // its device address
   HandoffCtl* d_ctl = nullptr;
   // workspaces
   bf16 *h = nullptr, *hn = nullptr, *q = nullptr, *attn = nullptr, *act = nullptr, *last_rows = nullptr;
@@ -96,6 +100,19 @@ struct xb_engine {
 };
 
 #define LAUNCH_COUNT(e) ((e)->c.launches++)
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is per DEVICE: one flag per device and call site, so a
+// second engine on another GPU of the same process sets it again.
+#define XB_SMEM_ATTR_ONCE(kernel, bytes)                                                                  \
+  do {                                                                                                    \
+    static bool _done[XB_MAX_DEVICES] = {false};                                                          \
+    int _dev = 0;                                                                                         \
+    XB_CUDA(cudaGetDevice(&_dev));                                                                        \
+    if (_dev < 0 || _dev >= XB_MAX_DEVICES || !_done[_dev]) {                                             \
+      XB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes)));   \
+      if (_dev >= 0 && _dev < XB_MAX_DEVICES) _done[_dev] = true;                                         \
+    }                                                                                                     \
+  } while (0)
 
 // a stage that begins at the MLP block of layer 0 does not hold the embedding; one that stops after the
 // attention block of the last layer does not hold the final norm / LM head
@@ -181,6 +198,9 @@ extern "C" int xb_engine_create(const xb_model_desc* desc, int device, xb_engine
   cudaDeviceProp prop;
   XB_CUDA(cudaGetDeviceProperties(&prop, device));
   XB_CHECK(prop.major == 10, "libxb200 is built for sm_100a only; device %d is sm_%d%d", device, prop.major, prop.minor);
+  XB_CHECK(desc->struct_size == sizeof(xb_model_desc),
+           "xb_model_desc.struct_size is %u but this library (ABI v%d) expects %zu: the caller was built against another "
+           "xb200.h", desc->struct_size, XB_ABI_VERSION, sizeof(xb_model_desc));
   const xb_model_desc& d = *desc;
   XB_CHECK(d.start_layer >= 0 && d.end_layer >= d.start_layer && d.end_layer < d.n_layers, "bad layer range [%d,%d] of %d",
            d.start_layer, d.end_layer, d.n_layers);
@@ -203,19 +223,24 @@ extern "C" int xb_engine_create(const xb_model_desc* desc, int device, xb_engine
   uint64_t wbytes = 0;
   for (int l = 0; l < e->nl; ++l) {
     LayerW& w = e->L[l];
-    XB_TRY(alloc_tiled(&w.wqkv, e->NQKV, D));
-    XB_TRY(alloc_tiled(&w.wo, D, e->NQ));
-    XB_TRY(alloc_tiled(&w.wgu, 2 * I, D));
-    XB_TRY(alloc_tiled(&w.wdown, D, I));
-    XB_TRY(dmalloc((void**)&w.sa_norm, D * 2));
-    XB_TRY(dmalloc((void**)&w.mlp_norm, D * 2));
-    if (d.qkv_bias) {
-      XB_TRY(dmalloc((void**)&w.bqkv, (size_t)e->NQKV * 2));
-      XB_CUDA(cudaMemset(w.bqkv, 0, (size_t)e->NQKV * 2));
-    }
+    // a boundary layer of a half-layer stage holds only the block that runs here (436 MB per cut at 8B)
     const bool has_attn = !(l == 0 && d.first_from_mlp), has_mlp = !(l + 1 == e->nl && d.last_to_attn);
-    if (has_attn) wbytes += ((size_t)e->NQKV * D + D * e->NQ) * 2;
-    if (has_mlp) wbytes += (size_t)3 * I * D * 2;
+    if (has_attn) {
+      XB_TRY(alloc_tiled(&w.wqkv, e->NQKV, D));
+      XB_TRY(alloc_tiled(&w.wo, D, e->NQ));
+      XB_TRY(dmalloc((void**)&w.sa_norm, D * 2));
+      if (d.qkv_bias) {
+        XB_TRY(dmalloc((void**)&w.bqkv, (size_t)e->NQKV * 2));
+        XB_CUDA(cudaMemset(w.bqkv, 0, (size_t)e->NQKV * 2));
+      }
+      wbytes += ((size_t)e->NQKV * D + D * e->NQ) * 2;
+    }
+    if (has_mlp) {
+      XB_TRY(alloc_tiled(&w.wgu, 2 * I, D));
+      XB_TRY(alloc_tiled(&w.wdown, D, I));
+      XB_TRY(dmalloc((void**)&w.mlp_norm, D * 2));
+      wbytes += (size_t)3 * I * D * 2;
+    }
   }
   const bool first = shard_is_first(d), last = shard_is_last(d);
   // the embedding table stays row-major (row gather); the LM head is tile-major like every
@@ -296,9 +321,10 @@ extern "C" int xb_engine_destroy(xb_engine* e) {
   }
   cudaFree(e->embed); cudaFree(e->final_norm); cudaFree(e->lm_head); cudaFree(e->rope);
   cudaFree(e->d_page_table); cudaFree(e->d_meta); cudaFree(e->in_tokens); cudaFree(e->logits);
-  if (e->peer_landing) cudaIpcCloseMemHandle(e->peer_landing);
-  if (e->peer_flags) cudaIpcCloseMemHandle(e->peer_flags);
+  if (e->peer_landing && !e->peer_is_local) cudaIpcCloseMemHandle(e->peer_landing);
+  if (e->peer_flags && !e->peer_is_local) cudaIpcCloseMemHandle(e->peer_flags);
   cudaFree(e->landing); cudaFree(e->flags); cudaFree(e->done_cnt);
+  if (e->ho_err) cudaFreeHost(e->ho_err);
   for (int i = 0; i < xb_engine::META_RING; ++i) {
     if (e->h_meta_ring[i]) cudaFreeHost(e->h_meta_ring[i]);
     if (e->meta_ev[i]) cudaEventDestroy(e->meta_ev[i]);
@@ -328,6 +354,12 @@ static int resolve_target(xb_engine* e, int layer, int kind, WTarget* t) {
     XB_CHECK(layer >= d.start_layer && layer <= d.end_layer, "layer %d outside this shard [%d,%d]", layer, d.start_layer,
              d.end_layer);
     LayerW& w = e->L[layer - d.start_layer];
+    {
+      const bool attn_kind = kind == XB_W_Q || kind == XB_W_K || kind == XB_W_V || kind == XB_W_O || kind == XB_W_SA_NORM ||
+                             kind == XB_W_Q_BIAS || kind == XB_W_K_BIAS || kind == XB_W_V_BIAS;
+      XB_CHECK(!(attn_kind && w.wqkv == nullptr), "layer %d: the attention block of this layer runs on the previous stage", layer);
+      XB_CHECK(!(!attn_kind && kind <= XB_W_MLP_NORM && w.wgu == nullptr), "layer %d: the MLP block of this layer runs on the next stage", layer);
+    }
     switch (kind) {
       case XB_W_Q: t->tdst = w.wqkv; t->row0 = 0; t->rows = e->NQ; t->K = D; break;
       case XB_W_K: t->tdst = w.wqkv; t->row0 = e->NQ; t->rows = e->NKV; t->K = D; break;
@@ -609,6 +641,7 @@ extern "C" int xb_kv_reserve(xb_engine* e, int n_slots, int max_tokens_per_slot,
   const size_t pool_bytes = (size_t)e->n_pages * e->NKV * page_tokens * 2;
   const long long pool_rows = (long long)e->n_pages * e->d.n_kv_heads * page_tokens;
   for (LayerW& w : e->L) {
+    if (w.wqkv == nullptr) continue;   // boundary layer whose attention block runs on the previous stage: no cache here
     XB_TRY(dmalloc((void**)&w.k_pool, pool_bytes));
     XB_TRY(dmalloc((void**)&w.v_pool, pool_bytes));
     // zeroed ONCE here (never per prompt): rows of a page beyond a sequence's length are
@@ -712,12 +745,7 @@ static int launch_attn_g(xb_engine* e, const LayerW& w, const BatchMeta& m, int 
   if (n_tiles == 0) {
     // decode: one block per (token, kv head, kv split)
     using Cfg = AttDecCfg<HD, G, NST>;
-    static bool attr_set = false;
-    if (!attr_set) {
-      XB_CUDA(cudaFuncSetAttribute(xb_attn_decode_mma_kernel<HD, G, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   Cfg::SMEM_BYTES));
-      attr_set = true;
-    }
+    XB_SMEM_ATTR_ONCE((xb_attn_decode_mma_kernel<HD, G, NST>), Cfg::SMEM_BYTES);
     dim3 grid(T, d.n_kv_heads, n_splits);
     XB_TRY(launch_k(e, xb_attn_decode_mma_kernel<HD, G, NST>, dim3(grid), dim3(160), Cfg::SMEM_BYTES, st, 1, w.tmK, w.tmV, e->q, m, e->o_part, e->ml_part,
                                                                               e->attn, d.n_heads, d.n_kv_heads, n_splits,
@@ -729,12 +757,7 @@ static int launch_attn_g(xb_engine* e, const LayerW& w, const BatchMeta& m, int 
   } else {
     // prefill: one block per (query tile, kv head), tcgen05 flash attention
     using Cfg = AttTcCfg<HD>;
-    static bool attr_set = false;
-    if (!attr_set) {
-      XB_CUDA(cudaFuncSetAttribute(xb_attn_prefill_tc_kernel<HD, G>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   Cfg::SMEM_BYTES));
-      attr_set = true;
-    }
+    XB_SMEM_ATTR_ONCE((xb_attn_prefill_tc_kernel<HD, G>), Cfg::SMEM_BYTES);
     XB_TRY(launch_k(e, xb_attn_prefill_tc_kernel<HD, G>, dim3(n_tiles, d.n_kv_heads), dim3(192), Cfg::SMEM_BYTES, st, 1, w.tmK,
                     w.tmV, e->q, m, m.tile_start, m.tile_len, e->attn, d.n_heads, d.n_kv_heads, scale_log2));
   }
@@ -847,7 +870,7 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
     // stage input arrives in the landing buffer, stored there by the previous GPU's last kernel
     XB_TRY(launch_k(e, xb_recv_norm_kernel<256>, dim3(T), dim3(256), norm_smem, st, 1, (const bf16*)e->landing,
                     (const uint32_t*)e->flags, (const HandoffCtl*)e->d_ctl, (long long)e->ho_rows * D, e->h, norm0, e->hn, D,
-                    d.norm_eps, d.rmsnorm_two_round));
+                    d.norm_eps, d.rmsnorm_two_round, e->ho_timeout_cycles, e->ho_err_dev));
   } else {
     XB_TRY(launch_k(e, xb_resid_norm_kernel<256, 2>, dim3(T), dim3(256), norm_smem, st, 1, nullptr, SplitInfo{1, 0, 1}, 0, nullptr, e->h, norm0, e->hn, D,
                                                              d.norm_eps, d.rmsnorm_two_round));
@@ -939,6 +962,28 @@ static int forward_impl(xb_engine* e, const xb_batch* b, void* out, void* const*
     if (pos + ql > max_ctx) max_ctx = pos + ql;
   }
   XB_CHECK(T <= d.max_batch_tokens, "batch carries %d token rows, engine was created for %d", T, d.max_batch_tokens);
+  if (e->ho_err != nullptr && *reinterpret_cast<volatile int*>(e->ho_err) != 0)
+    return xb_fail(3, "an earlier hand-off step timed out waiting for landing slot %d to reach %d (producer stage absent or stuck); "
+                      "its result is invalid -- xb_handoff_clear_error() to go on", e->ho_err[0] - 1, e->ho_err[1]);
+  {
+    // every check comes before the first change of slot_len / the page lists: a batch that cannot be
+    // served leaves the engine exactly as it found it
+    size_t need_new = 0;
+    for (int i = 0; i < b->n_seqs; ++i) {
+      const int need_pages = (b->positions[i] + b->q_lens[i] + e->page_tokens - 1) / e->page_tokens;
+      const size_t have = e->slot_pages[b->slot_ids[i]].size();
+      if ((size_t)need_pages > have) need_new += (size_t)need_pages - have;
+    }
+    XB_CHECK(need_new <= e->free_pages.size(), "KV page pool exhausted: the batch needs %zu more pages, %zu are free", need_new,
+             e->free_pages.size());
+  }
+  if (ctl != nullptr) {
+    XB_CHECK(decode_only, "the peer hand-off carries decode steps only");
+    XB_CHECK(!ho_in || (!first && e->landing != nullptr && ctl[0] < e->ho_slots && T <= e->ho_rows),
+             "hand-off input: needs a non-first shard with xb_handoff_create done, slot < %d, rows <= %d", e->ho_slots, e->ho_rows);
+    XB_CHECK(!ho_out || (!last && e->peer_landing != nullptr && e->done_cnt != nullptr && ctl[2] < e->ho_slots && T <= e->ho_rows),
+             "hand-off output: needs a non-last shard with xb_handoff_create + connect done, slot < %d, rows <= %d", e->ho_slots, e->ho_rows);
+  }
   // pinned staging buffer from the ring (wait until its previous upload has been consumed)
   const int ring = e->meta_next;
   e->meta_next = (e->meta_next + 1) % xb_engine::META_RING;
@@ -961,7 +1006,6 @@ static int forward_impl(xb_engine* e, const xb_batch* b, void* out, void* const*
     if ((int)pages.size() < need_pages) {
       const int old = (int)pages.size();
       while ((int)pages.size() < need_pages) {
-        XB_CHECK(!e->free_pages.empty(), "KV page pool exhausted");
         const int p = e->free_pages.back();
         e->free_pages.pop_back();
         e->h_page_table[(size_t)slot * e->max_pages + pages.size()] = p;
@@ -999,11 +1043,6 @@ static int forward_impl(xb_engine* e, const xb_batch* b, void* out, void* const*
   }
   e->meta_T = T;
   if (ctl != nullptr) {
-    XB_CHECK(decode_only, "the peer hand-off carries decode steps only");
-    XB_CHECK(!ho_in || (!first && e->landing != nullptr && ctl[0] < e->ho_slots && T <= e->ho_rows),
-             "hand-off input: needs a non-first shard with xb_handoff_create done, slot < %d, rows <= %d", e->ho_slots, e->ho_rows);
-    XB_CHECK(!ho_out || (!last && e->peer_landing != nullptr && ctl[2] < e->ho_slots && T <= e->ho_rows),
-             "hand-off output: needs a non-last shard with xb_handoff_connect done, slot < %d, rows <= %d", e->ho_slots, e->ho_rows);
     int* hc = hm + e->meta_ints - 4;
     hc[0] = ctl[0]; hc[1] = ctl[1]; hc[2] = ctl[2]; hc[3] = ctl[3];
     XB_CUDA(cudaMemcpyAsync(e->d_ctl, hc, 16, cudaMemcpyHostToDevice, st));
@@ -1083,7 +1122,8 @@ extern "C" int xb_forward_handoff(xb_engine* e, const xb_batch* b, int slot_in, 
 }
 
 extern "C" int xb_handoff_create(xb_engine* e, int n_slots, int rows, void* landing_handle, void* flag_handle) {
-  XB_CHECK(e != nullptr && n_slots > 0 && rows > 0 && rows <= 128 && landing_handle && flag_handle, "bad argument");
+  XB_CHECK(e != nullptr && n_slots > 0 && rows > 0 && rows <= 128, "bad argument");
+  XB_CHECK((landing_handle == nullptr) == (flag_handle == nullptr), "pass both IPC handle buffers, or neither (in-process ring)");
   XB_CUDA(cudaSetDevice(e->device));
   XB_CHECK(e->landing == nullptr, "hand-off buffers already created");
   const size_t bytes = (size_t)n_slots * rows * e->d.dim * 2;
@@ -1095,9 +1135,55 @@ extern "C" int xb_handoff_create(xb_engine* e, int n_slots, int rows, void* land
   XB_CUDA(cudaMemset(e->done_cnt, 0, (size_t)n_slots * 4));
   e->ho_slots = n_slots;
   e->ho_rows = rows;
-  XB_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(landing_handle), e->landing));
-  XB_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(flag_handle), e->flags));
+  if (landing_handle != nullptr) {
+    XB_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(landing_handle), e->landing));
+    XB_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(flag_handle), e->flags));
+  }
+  // consumer-side wait budget and the host-visible word a timed-out wait reports through
+  {
+    const char* tv = getenv("XB_HANDOFF_TIMEOUT_S");
+    double secs = tv != nullptr ? atof(tv) : 30.0;
+    if (!(secs > 0.0)) secs = 30.0;
+    int khz = 0;
+    XB_CUDA(cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, e->device));
+    e->ho_timeout_cycles = (long long)(secs * (double)khz * 1000.0);
+    XB_CUDA(cudaHostAlloc((void**)&e->ho_err, 2 * sizeof(int), cudaHostAllocMapped));
+    e->ho_err[0] = e->ho_err[1] = 0;
+    XB_CUDA(cudaHostGetDevicePointer((void**)&e->ho_err_dev, e->ho_err, 0));
+  }
   XB_CUDA(cudaDeviceSynchronize());
+  return 0;
+}
+
+extern "C" int xb_handoff_clear_error(xb_engine* e) {
+  XB_CHECK(e != nullptr, "null engine");
+  if (e->ho_err != nullptr) {
+    XB_CUDA(cudaSetDevice(e->device));
+    XB_CUDA(cudaDeviceSynchronize());
+    e->ho_err[0] = e->ho_err[1] = 0;
+  }
+  return 0;
+}
+
+extern "C" int xb_handoff_connect_local(xb_engine* e, xb_engine* next) {
+  XB_CHECK(e != nullptr && next != nullptr && e != next, "bad argument");
+  XB_CHECK(e->ho_slots > 0 && next->landing != nullptr, "both stages must call xb_handoff_create first");
+  XB_CHECK(e->ho_slots == next->ho_slots && e->ho_rows == next->ho_rows && e->d.dim == next->d.dim,
+           "hand-off geometry differs between the stages (%d x %d x %d vs %d x %d x %d)", e->ho_slots, e->ho_rows, e->d.dim,
+           next->ho_slots, next->ho_rows, next->d.dim);
+  XB_CHECK(e->peer_landing == nullptr, "this stage is already connected");
+  XB_CUDA(cudaSetDevice(e->device));
+  if (e->device != next->device) {
+    int can = 0;
+    XB_CUDA(cudaDeviceCanAccessPeer(&can, e->device, next->device));
+    XB_CHECK(can, "device %d cannot address the memory of device %d", e->device, next->device);
+    cudaError_t ce = cudaDeviceEnablePeerAccess(next->device, 0);
+    if (ce == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+    else XB_CUDA(ce);
+  }
+  e->peer_landing = next->landing;
+  e->peer_flags = next->flags;
+  e->peer_is_local = true;
   return 0;
 }
 
@@ -1138,22 +1224,23 @@ extern "C" int xb_bench_linears(xb_engine* e, int T, int iters, int* n_launches,
     for (int l = 0; l < e->nl; ++l) {
       const LayerW& w = e->L[l];
       const GemmPlan* gp;
-      if (only < 0 || only == SITE_QKV) {
+      const bool has_attn = w.wqkv != nullptr, has_mlp = w.wgu != nullptr;
+      if (has_attn && (only < 0 || only == SITE_QKV)) {
         XB_TRY(get_plan(e, SITE_QKV, l, e->hn, D, w.wqkv, T, e->NQKV, D, e->gemm_out, e->NQKV, w.bqkv, 0, &gp));
         XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
         ++n;
       }
-      if (only < 0 || only == SITE_O) {
+      if (has_attn && (only < 0 || only == SITE_O)) {
         XB_TRY(get_plan(e, SITE_O, l, e->attn, e->NQ, w.wo, T, D, e->NQ, e->gemm_out, D, nullptr, 0, &gp));
         XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
         ++n;
       }
-      if (only < 0 || only == SITE_GU) {
+      if (has_mlp && (only < 0 || only == SITE_GU)) {
         XB_TRY(get_plan(e, SITE_GU, l, e->hn, D, w.wgu, T, 2 * I, D, e->gemm_out, 2 * I, nullptr, 0, &gp));
         XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
         ++n;
       }
-      if (only < 0 || only == SITE_DOWN) {
+      if (has_mlp && (only < 0 || only == SITE_DOWN)) {
         XB_TRY(get_plan(e, SITE_DOWN, l, e->act, I, w.wdown, T, D, I, e->gemm_out, D, nullptr, 0, &gp));
         XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
         ++n;
@@ -1188,8 +1275,10 @@ extern "C" int xb_bench_attention(xb_engine* e, int n_seqs, int max_ctx, int n_s
   if (n_splits <= 0) n_splits = choose_kv_splits(e, n_seqs, max_ctx);
   XB_CHECK(n_splits <= e->max_attn_splits, "n_splits %d above the workspace limit %d", n_splits, e->max_attn_splits);
   for (int it = 0; it < iters; ++it) {
-    if (d.head_dim == 128) XB_TRY(launch_attn<128>(e, e->L[0], m, n_seqs, n_splits, 0, st));
-    else XB_TRY(launch_attn<64>(e, e->L[0], m, n_seqs, n_splits, 0, st));
+    XB_CHECK(e->L[0].wqkv != nullptr || e->nl > 1, "this stage runs no attention block");
+    const LayerW& w0 = e->L[e->L[0].wqkv != nullptr ? 0 : 1];   // first layer whose attention block runs here
+    if (d.head_dim == 128) XB_TRY(launch_attn<128>(e, w0, m, n_seqs, n_splits, 0, st));
+    else XB_TRY(launch_attn<64>(e, w0, m, n_seqs, n_splits, 0, st));
   }
   if (splits_used) *splits_used = n_splits;
   return 0;
@@ -1212,11 +1301,7 @@ extern "C" int xb_sample(xb_engine* e, const float* logits, int n, float temp, i
     const char* cv = getenv("XB_SAMPLE_CLUSTER");
     const bool use_cluster = !(cv != nullptr && cv[0] == '0');
     if (use_cluster && (size_t)chunk * 4 <= (size_t)200 * 1024) {
-      static bool attr_set = false;
-      if (!attr_set) {
-        XB_CUDA(cudaFuncSetAttribute(xb_sample_cluster_kernel<1024, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_set = true;
-      }
+      XB_SMEM_ATTR_ONCE((xb_sample_cluster_kernel<1024, CL>), 200 * 1024);
       cudaLaunchConfig_t cfg = {};
       cfg.gridDim = dim3(n * CL);
       cfg.blockDim = dim3(1024);
@@ -1295,7 +1380,7 @@ static __device__ __align__(256) float g_xb_noalloc_scratch[XB_NOALLOC_SCRATCH_F
 // Per-device DEVICE address of the array above.  In host code `g_xb_noalloc_scratch` is only a
 // host-side handle for the symbol -- handing it to a kernel would make the kernel write through
 // a host address -- so the real address is looked up once per device and cached here.
-#define XB_NOALLOC_MAX_DEVICES 64
+#define XB_NOALLOC_MAX_DEVICES XB_MAX_DEVICES
 static float* g_xb_noalloc_ptr[XB_NOALLOC_MAX_DEVICES] = {nullptr};
 
 // y[T,N] = x[T,K] * w[N,K]^T with the engine's split-K tcgen05 Linear, for callers that must
@@ -1324,6 +1409,15 @@ extern "C" int xb_linear_noalloc(const void* x, const void* w, int T, int N, int
   int dev = 0, sms = 148;
   XB_CUDA(cudaGetDevice(&dev));
   XB_CHECK(dev >= 0 && dev < XB_NOALLOC_MAX_DEVICES, "device index %d not supported", dev);
+  {
+    // the scratch array used is the CURRENT device's copy: the operands must live there too
+    cudaPointerAttributes pa;
+    XB_CUDA(cudaPointerGetAttributes(&pa, x));
+    XB_CHECK(pa.type == cudaMemoryTypeDevice || pa.type == cudaMemoryTypeManaged, "x must be device memory");
+    XB_CHECK(pa.type == cudaMemoryTypeManaged || pa.device == dev,
+             "xb_linear_noalloc: x lives on device %d but device %d is current; make the operands' device current "
+             "(cudaSetDevice) before the call", pa.device, dev);
+  }
   if (g_xb_noalloc_ptr[dev] == nullptr) {
     float* p = nullptr;
     XB_CUDA(cudaGetSymbolAddress((void**)&p, g_xb_noalloc_scratch));

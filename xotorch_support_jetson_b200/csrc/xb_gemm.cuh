@@ -649,11 +649,16 @@ template <int BN, int STAGES>
 static int xb_gemm_launch_t(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, int grid, cudaStream_t st,
                             int pdl) {
   using Cfg = GemmCfg<BN, STAGES>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    XB_CUDA(cudaFuncSetAttribute(xb_gemm_tcgen05_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 Cfg::SMEM_BYTES));
-    attr_set = true;
+  {
+    // per device: the attribute does not carry over to another GPU of the same process
+    static bool done[XB_MAX_DEVICES] = {false};
+    int dev = 0;
+    XB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= XB_MAX_DEVICES || !done[dev]) {
+      XB_CUDA(cudaFuncSetAttribute(xb_gemm_tcgen05_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   Cfg::SMEM_BYTES));
+      if (dev >= 0 && dev < XB_MAX_DEVICES) done[dev] = true;
+    }
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid, 1, 1);

@@ -215,7 +215,8 @@ template <int NT>
 __global__ void __launch_bounds__(NT) xb_recv_norm_kernel(const bf16* __restrict__ landing, const uint32_t* __restrict__ flags,
                                                           const HandoffCtl* __restrict__ ctl, long long slot_elems,
                                                           bf16* __restrict__ h, const bf16* __restrict__ nw,
-                                                          bf16* __restrict__ hn, int D, float eps, int two_round) {
+                                                          bf16* __restrict__ hn, int D, float eps, int two_round,
+                                                          long long timeout_cycles, int* __restrict__ err_word) {
   pdl_launch_dependents();
   pdl_wait();
   __shared__ float red[32];
@@ -224,11 +225,18 @@ __global__ void __launch_bounds__(NT) xb_recv_norm_kernel(const bf16* __restrict
   const int slot = ctl->slot_in;
   const uint32_t want = (uint32_t)ctl->wait_value;
   if (threadIdx.x == 0) {
+    // A producer that is merely slow (its first call of a shape captures a graph, a long prefill chunk is
+    // queued ahead of it) must not cost the consumer its CUDA context: on time-out the slot is recorded in
+    // a host-visible word (checked by the next xb_forward* call) and the step runs on to completion.
     long long t0 = clock64();
     while ((int32_t)(ld_acquire_sys(flags + slot) - want) < 0) {
-      if (clock64() - t0 > 4000000000LL) {
-        printf("xb200: hand-off flag wait timed out (slot %d want %u)\n", slot, want);
-        __trap();
+      if (clock64() - t0 > timeout_cycles) {
+        if (t == 0) {
+          err_word[1] = (int)want;
+          __threadfence_system();
+          *reinterpret_cast<volatile int*>(err_word) = slot + 1;
+        }
+        break;
       }
     }
   }

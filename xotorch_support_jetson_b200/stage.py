@@ -72,7 +72,7 @@ class StageRuntime:
     if max_positions is None:
       max_positions = min(config["max_seq_len"], max(max_tokens_per_seq, 8))
     self.max_positions = max_positions
-    d = _cabi.ModelDesc(
+    d = _cabi.model_desc(
       n_layers=shard.n_layers, start_layer=shard.start_layer, end_layer=shard.end_layer,
       dim=config["embed_dim"], n_heads=config["num_heads"], n_kv_heads=config["num_kv_heads"],
       head_dim=config["head_dim"], inter_dim=config["intermediate_dim"], vocab=config["vocab_size"],
@@ -228,11 +228,24 @@ class StageRuntime:
     _cabi.check(self.lib.xb_forward(self._h, C.byref(b), optr, tap_ptrs, C.c_void_p(stream)))
     return out
 
-  def handoff_create(self, n_slots: int, rows: int) -> tuple:
-    """Allocate this stage's landing buffers; returns the two CUDA IPC handles (bytes)."""
+  def handoff_create(self, n_slots: int, rows: int, ipc: bool = True) -> Optional[tuple]:
+    """Allocate this stage's landing buffers; returns the two CUDA IPC handles (bytes) for stages in
+    other processes, or None with ipc=False (stages of one process connect with handoff_connect_local)."""
+    if not ipc:
+      _cabi.check(self.lib.xb_handoff_create(self._h, int(n_slots), int(rows), None, None))
+      return None
     hl, hf = C.create_string_buffer(64), C.create_string_buffer(64)
     _cabi.check(self.lib.xb_handoff_create(self._h, int(n_slots), int(rows), hl, hf))
     return bytes(hl.raw), bytes(hf.raw)
+
+  def handoff_connect_local(self, next_stage: "StageRuntime"):
+    """The NEXT stage lives in this process (another GPU, or the same one): store into its landing
+    buffers through their device addresses (xb_handoff_connect_local)."""
+    _cabi.check(self.lib.xb_handoff_connect_local(self._h, next_stage._h))
+    self._next_stage = next_stage   # keeps the consumer's buffers alive as long as this producer
+
+  def handoff_clear_error(self):
+    _cabi.check(self.lib.xb_handoff_clear_error(self._h))
 
   def handoff_connect(self, landing_handle: bytes, flag_handle: bytes):
     """Map the NEXT stage's landing buffers (handles from its handoff_create)."""
@@ -317,7 +330,9 @@ def linear_noalloc(x: torch.Tensor, w: torch.Tensor, y: torch.Tensor, round_bf16
   N = w.shape[0]
   assert x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and y.dtype == torch.float32
   assert y.shape == (T, N) and x.is_contiguous() and w.is_contiguous() and y.is_contiguous()
-  stream = torch.cuda.current_stream(x.device).cuda_stream
-  _cabi.check(lib.xb_linear_noalloc(C.c_void_p(x.data_ptr()), C.c_void_p(w.data_ptr()), T, N, K, C.c_void_p(y.data_ptr()),
-                                    int(round_bf16), C.c_void_p(stream)))
+  assert w.device == x.device and y.device == x.device
+  with torch.cuda.device(x.device):   # the library uses the CURRENT device's copy of its built-in workspace
+    stream = torch.cuda.current_stream(x.device).cuda_stream
+    _cabi.check(lib.xb_linear_noalloc(C.c_void_p(x.data_ptr()), C.c_void_p(w.data_ptr()), T, N, K, C.c_void_p(y.data_ptr()),
+                                      int(round_bf16), C.c_void_p(stream)))
   return y
