@@ -164,8 +164,9 @@ def run_reference(args):
     steps = max(2, int(budget / per_step))
   times = smp.steps(steps)
   val, per_step = sb * steps / sum(times), sum(times) / steps
-  sample = (f"{steps} decode steps of {sb} of the {args.batch * args.gpus} sequences at context {args.prompt_len} "
-            f"(synthetic KV cache, no CPU prefill), oracle port in reference-exact mode")
+  sample = (f"{steps} decode steps of {sb} sequences (one micro-batch of {args.batch}"
+            + (f"; the {args.gpus}-GPU arm keeps {args.gpus} such micro-batches in flight" if args.gpus > 1 else "")
+            + f") at context {args.prompt_len} (synthetic KV cache, no CPU prefill), oracle port in reference-exact mode")
   line = {
     "impl": "reference", "metric": "decode_tok_s", "value": val, "unit": "tok/s", "n_gpus": args.gpus, "steps": steps,
     "warmup": warm, "ms_per_step": per_step * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -222,7 +223,8 @@ def run_b200(args):
   B, M, L = args.batch, world, args.prompt_len
   K, W = args.steps, args.warmup
   peaks = measured_peaks()
-  max_ctx = L + 2 * (K + W) + 80
+  R = max(1, args.reps)
+  max_ctx = L + W + 2 * R * K + 16 + 80
   runner = PipelineRunner(args.model, hf_cfg, cfg, rank, world, local, B, M, max_ctx, max_batch_tokens=args.max_batch_tokens,
                           dist=dist if world > 1 else None, seed=0, ret_group=ret_group)
   dev = runner.device
@@ -235,7 +237,7 @@ def run_b200(args):
       dist.barrier()
     torch.cuda.synchronize()
 
-  def timed(fn):
+  def timed(fn, reduce_max=True):
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(runner.stream)
@@ -243,14 +245,25 @@ def run_b200(args):
     e1.record(runner.stream)
     barrier()
     ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
-    if world > 1:
+    if world > 1 and reduce_max:
       dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     return float(ms.item())
 
+  def timed_median(fn, reps):
+    """The K-step region timed `reps` times (each bracketed by barrier + synchronize, max over ranks);
+    a 0.1 s region on a freshly started box is not at steady state, the median of several is."""
+    ts = [timed(fn) for _ in range(max(1, reps))]
+    return statistics.median(ts), ts
+
   c0 = runner.stage.counters()
-  # ---- prefill: one untimed pass (builds launch plans), then a timed pass on fresh slots
-  runner.prefill(prompts)
-  runner.drain()
+  # ---- prefill: one untimed pass (builds launch plans), then a timed pass on fresh slots.  At N > 1 the
+  # untimed pass is also the correctness check: the pipeline's greedy ids against a one-GPU full-shard run
+  tokens_check = None
+  if world > 1:
+    tokens_check = pipeline_token_check(runner, args.model, hf_cfg, cfg, prompts, 8, local, dist)
+  else:
+    runner.prefill(prompts)
+    runner.drain()
   barrier()
   runner.reset()
   prefill_ms = timed(lambda: runner.prefill(prompts))
@@ -262,18 +275,18 @@ def run_b200(args):
   if rank == 0:
     clocks.start()
   l0 = runner.stage.counters()["launches"]
-  decode_ms = timed(lambda: runner.decode(K))
-  launches = runner.stage.counters()["launches"] - l0
+  decode_ms, decode_all = timed_median(lambda: runner.decode(K), R)
+  launches = (runner.stage.counters()["launches"] - l0) // R
   clk = clocks.stop() if rank == 0 else None
   value = B * M * K / (decode_ms * 1e-3)
-  ctx_avg = L + W + (K - 1) / 2.0
+  ctx_avg = L + W + (R * K - 1) / 2.0
 
   # ---- end-to-end leg with host buffers
   e2e = None
   if world > 1:
     host_in = [torch.zeros(B, dtype=torch.int32).pin_memory() for _ in range(M)]
     host_out = [torch.zeros(B, dtype=torch.int32).pin_memory() for _ in range(M)]
-    e2e_ms = timed(lambda: runner.decode(K, host_tokens=host_in, host_out=host_out))
+    e2e_ms, _ = timed_median(lambda: runner.decode(K, host_tokens=host_in, host_out=host_out), R)
     e2e = {"value": B * M * K / (e2e_ms * 1e-3), "unit": "tok/s", "h2d_bytes_per_step": 4 * B * M, "d2h_bytes_per_step": 2 * 4 * B * M,
            "api": "PipelineRunner.decode with pinned host id buffers (ids D2H+H2D on rank 0, sampled ids D2H on the last rank, every step)"}
   runner.drain()
@@ -290,27 +303,44 @@ def run_b200(args):
     with torch.cuda.stream(runner.stream):
       nl_box[0] = st.bench_linears(B, iters)
 
-  lin_ms = timed(lin)
+  lin_ms = timed(lin, reduce_max=False)     # THIS rank's time: the fraction is per stage (stages hold different matrices)
   n_lin = nl_box[0]
   wbytes = cnt["weight_bytes"]
-  lin_launch_us = lin_ms * 1e3 / n_lin
-  achieved = wbytes * iters / (lin_ms * 1e-3) / 1e9
+  per_rank = [(lin_ms, wbytes, n_lin, cnt["kv_bytes_per_pos"])]
+  if world > 1:
+    per_rank = [None] * world
+    dist.all_gather_object(per_rank, (lin_ms, wbytes, n_lin, cnt["kv_bytes_per_pos"]))
+  fracs = [(wb * iters / (ms * 1e-3) / 1e9) / peaks["hbm_gbs"] for ms, wb, _, _ in per_rank]
+  # the stage whose Linears take longest per step governs the pipeline: report that one, list the others
+  br = max(range(world), key=lambda r: per_rank[r][0])
+  lin_ms_b, wbytes_b, n_lin_b, _ = per_rank[br]
+  achieved = wbytes_b * iters / (lin_ms_b * 1e-3) / 1e9
   roofline = {"bound": "hbm", "kernel": "xb_gemm_tcgen05_kernel (skinny weight-streaming Linear)", "achieved": achieved,
               "peak": peaks["hbm_gbs"], "peak_source": peaks["source"] + " (MEASURED_PEAKS.json hbm_gbs)" if peaks["source"] == "measured" else "fallback",
               "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": None,
-              "bytes_per_launch": wbytes / (n_lin / iters), "launch_us": lin_launch_us,
-              "launches_per_step": n_lin // iters}
-  prof = ROOT / "profiles" / "r01_ncu_traffic.json"
-  if prof.exists():
-    try:
-      roofline["traffic"] = json.loads(prof.read_text()).get("gemm_dram_bytes_per_launch")
-    except Exception:
-      pass
+              "bytes_per_launch": wbytes_b / (n_lin_b / iters), "launch_us": lin_ms_b * 1e3 / n_lin_b,
+              "launches_per_step": n_lin_b // iters}
+  if world > 1:
+    roofline["rank"] = br
+    roofline["frac_per_rank"] = fracs
+  else:
+    # DRAM bytes per launch of this kernel from the committed `ncu --set full` capture of the N=1 bs=32 step
+    # (evidence from a profile run, not re-measured here; stages of an N>1 pipeline hold other matrices: null)
+    for name in ("r02_ncu_traffic.json", "r01_ncu_traffic.json"):
+      prof = ROOT / "profiles" / name
+      if prof.exists():
+        try:
+          roofline["traffic"] = json.loads(prof.read_text()).get("gemm_dram_bytes_per_launch")
+          roofline["traffic_source"] = f"ncu --set full capture at N=1, committed as profiles/{name} (not measured in this run)"
+          break
+        except Exception:
+          pass
   # whole decode step against the HBM roofline (weights once per micro-batch + KV of every sequence)
-  step_bytes = M * wbytes + B * M * ctx_avg * cnt["kv_bytes_per_pos"]
+  # (per GPU: the stage that streams most bytes per step)
+  step_bytes = max(M * wb + B * M * ctx_avg * kvb for _, wb, _, kvb in per_rank)
   step_frac = (step_bytes / (decode_ms * 1e-3 / K) / 1e9) / peaks["hbm_gbs"]
 
-  extra = {"prefill_tok_s": prefill_tok_s, "prefill_ms": prefill_ms,
+  extra = {"decode_ms_per_step_all_reps": [t / K for t in decode_all], "prefill_tok_s": prefill_tok_s, "prefill_ms": prefill_ms,
            "decode_step_hbm_frac": step_frac, "decode_step_bytes_per_gpu": step_bytes,
            "decode_ctx_avg": ctx_avg}
   # prefill against the tensor roofline (algorithmic FLOPs)
@@ -320,6 +350,8 @@ def run_b200(args):
   flops = 2.0 * T_all * nl_total * (2 * D * H * hd + 2 * D * KV * hd + 3 * D * I) + 2.0 * B * M * L * L * H * hd * nl_total + 2.0 * B * M * V * D
   extra["prefill_tflops_per_gpu"] = flops / world / (prefill_ms * 1e-3) / 1e12
   extra["prefill_tensor_frac"] = extra["prefill_tflops_per_gpu"] / peaks["bf16_tflops_sustained"]
+  if tokens_check is not None:
+    extra.update(tokens_check)
 
   # ---- decode bs=1 (latency-bound single stream), same pipeline
   runner.reset()
@@ -340,7 +372,7 @@ def run_b200(args):
       t0 = time.perf_counter()
       val, per_step = cpu_decode_sample(hf_cfg, args.model, args.ref_batch, L, args.cpu_steps, 1)
       cpu_base = {"value": val, "unit": "tok/s", "cores": os.cpu_count() or 1, "kind": "port",
-                  "sample": f"{args.cpu_steps} decode steps of {args.ref_batch} sequences at context {L} (synthetic KV cache), "
+                  "sample": f"{args.cpu_steps} decode steps of {args.ref_batch} sequences (the named batch) at context {L} (synthetic KV cache), "
                             f"oracle port in reference-exact mode, {time.perf_counter() - t0:.0f}s incl. weight init"}
 
   if rank == 0:
@@ -354,6 +386,65 @@ def run_b200(args):
   runner.close()
   if world > 1:
     dist.destroy_process_group()
+
+
+def pipeline_token_check(runner, model_id, hf_cfg, cfg, prompts, n_steps, local, dist):
+  """N > 1: `n_steps` greedy decode steps of every micro-batch through the pipeline (whatever hand-off
+  and stage partition the run uses: peer stores / NCCL, half-layer / whole-layer stages) compared, id for
+  id, with a ONE-GPU full-shard engine on the same seeded weights and prompts (built on the last rank,
+  same micro-batch shape, so both run the same kernels).  Leaves the runner reset.  Returns the `extra`
+  entries {tokens_equal_n1, tokens_crc, tokens_crc_n1, tokens_checked} on every rank."""
+  import zlib
+  import torch
+  from xotorch_support_jetson_b200.pipeline import gpu_random_getter
+  from xotorch_support_jetson_b200.shard import Shard
+  from xotorch_support_jetson_b200.stage import StageRuntime
+  B, M, world, rank = runner.B, runner.M, runner.world, runner.rank
+  L = prompts[0].shape[1]
+  runner.reset()
+  runner.prefill(prompts)
+  hist = []
+  for k in range(n_steps + 1):
+    runner.drain()
+    torch.cuda.synchronize()
+    if rank == world - 1:
+      hist.append(torch.stack([t.clone() for t in runner.tok]).cpu())   # ids sampled after k decode steps, [M, B]
+    if k < n_steps:
+      runner.decode(1)
+  res = [None]
+  if rank == world - 1:
+    got = torch.stack(hist)                                              # [n_steps + 1, M, B]
+    nl = cfg["num_layers"]
+    st = StageRuntime(Shard(model_id, 0, nl - 1, nl), cfg, device=local, max_batch_tokens=runner.max_batch_tokens, max_seqs=B,
+                      max_tokens_per_seq=L + n_steps + 8)
+    st.load_hf_tensors(*gpu_random_getter(hf_cfg, 0, 0.02, runner.device))
+    per = max(1, runner.max_batch_tokens // L)
+    want = torch.zeros_like(got)
+    with torch.cuda.stream(torch.cuda.Stream(device=runner.device)):
+      for m in range(M):
+        tok = torch.zeros(B, dtype=torch.int32, device=runner.device)
+        for c0 in range(0, B, per):                                      # same prefill chunking as PipelineRunner.prefill
+          c1 = min(B, c0 + per)
+          lg = st.forward(list(range(c0, c1)), [L] * (c1 - c0), [0] * (c1 - c0), tokens=prompts[m][c0:c1].reshape(-1))
+          st.sample(lg, temp=0.0, out=tok[c0:c1])
+        want[0, m] = tok.cpu()
+        for k in range(n_steps):
+          lg = st.forward(list(range(B)), [1] * B, [L + k] * B, tokens=tok)
+          tok = st.sample(lg, temp=0.0)
+          want[k + 1, m] = tok.cpu()
+        for b in range(B):
+          st.release_slot(b)
+    torch.cuda.synchronize()
+    st.close()
+    del st
+    torch.cuda.empty_cache()
+    crc = lambda t: zlib.crc32(t.to(torch.int32).numpy().tobytes())
+    res = [{"tokens_equal_n1": bool(torch.equal(got, want)), "tokens_crc": crc(got), "tokens_crc_n1": crc(want),
+            "tokens_checked": f"{n_steps + 1} greedy ids x {M} micro-batches x {B} sequences (first id after the prefill + {n_steps} decode steps), "
+                              f"pipeline vs one-GPU full shard; mismatching ids: {int((got != want).sum())}"}]
+  dist.broadcast_object_list(res, src=world - 1)
+  runner.reset()
+  return res[0]
 
 
 class PipelineRunnerView:
@@ -461,8 +552,9 @@ def main():
   ap.add_argument("--batch", type=int, default=BATCH)
   ap.add_argument("--prompt-len", type=int, default=PROMPT_LEN)
   ap.add_argument("--max-batch-tokens", type=int, default=8192)
-  ap.add_argument("--ref-batch", type=int, default=4, help="sequences per step in the CPU sample")
-  ap.add_argument("--cpu-steps", type=int, default=6)
+  ap.add_argument("--ref-batch", type=int, default=BATCH, help="sequences per step of the CPU arm (the named batch)")
+  ap.add_argument("--cpu-steps", type=int, default=3)
+  ap.add_argument("--reps", type=int, default=5, help="the K-step timed region is repeated this often; the median is reported")
   ap.add_argument("--no-cpu-baseline", action="store_true")
   args = ap.parse_args()
   if args.warmup < 3 and args.impl == "b200":

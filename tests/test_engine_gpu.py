@@ -11,6 +11,10 @@ pytestmark = pytest.mark.gpu
 # different orders, so values differ by a few bf16 ulps (2^-8 relative) that compound over
 # layers.  Hidden states / logits must agree within REL_TOL of the tensor's max-abs.
 REL_TOL = 0.04
+# The same bound per model at about twice the worst case measured on the B200 over prefill + decode, every layer
+# (llama-3.2-tiny 0.012, llama-3.1-tiny 0.023 -- head_dim 128, 6 layers --, qwen-2.5-tiny 0.018): a regression
+# that doubles the error fails.  REL_TOL itself stays the ceiling for the checks that mix models.
+MODEL_TOL = {"llama-3.2-tiny": 0.025, "llama-3.1-tiny": 0.04, "qwen-2.5-tiny": 0.035}
 
 
 def _setup(mid, seed=0, std=0.05, jitter=0.1):
@@ -85,7 +89,7 @@ def test_prefill_decode_parity(built_lib, mid, splits):
     x = torch.tensor([int(ref_toks[0, step])], dtype=torch.int32, device="cuda")
     q_len = 1
   print(f"{mid} {splits}: hidden rel err {worst_h:.4f}, logits rel err {worst_l:.4f}, tokens {got_toks} vs {ref_toks[0].tolist()}")
-  assert worst_h < REL_TOL and worst_l < REL_TOL
+  assert worst_h < MODEL_TOL[mid] and worst_l < MODEL_TOL[mid]
   agree = sum(int(a == b) for a, b in zip(got_toks, ref_toks[0].tolist()))
   assert agree >= n_dec - 1
   for s in stages:

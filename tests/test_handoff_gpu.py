@@ -39,8 +39,9 @@ def _move(t, dev):
   if t.device == dev:
     return t
   out = t.to(dev)
-  torch.cuda.synchronize(t.device)
-  torch.cuda.synchronize(dev)
+  for d in (t.device, dev):
+    if d.type == "cuda":
+      torch.cuda.synchronize(d)
   return out
 
 

@@ -211,7 +211,7 @@ class StageRuntime:
         out = torch.empty((T, self.dim), dtype=torch.bfloat16, device=self.device)
     tap_ptrs = None
     if taps is not None:
-      tap_ptrs = (C.c_void_p * len(taps))(*[t.data_ptr() for t in taps])
+      tap_ptrs = (C.c_void_p * len(taps))(*[t.data_ptr() if t is not None else None for t in taps])   # None: layer not tapped
     stream = torch.cuda.current_stream(self.device).cuda_stream
     optr = C.c_void_p(out.data_ptr()) if out is not None else None
     if handoff is not None:
