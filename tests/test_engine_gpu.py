@@ -548,3 +548,62 @@ def test_half_layer_stage_boundaries_are_exact(built_lib, mid, tmp_path):
     for st in stages:
       st.close()
   full.close()
+
+
+@pytest.mark.parametrize("mid,page_tokens", [("llama-3.1-tiny", 16), ("qwen-2.5-tiny", 64), ("llama-3.2-tiny", 32)])
+def test_decode_attention_variants_are_bit_identical(built_lib, monkeypatch, mid, page_tokens):
+  """The decode step with the q/k/v finalize folded into the attention kernel (default) and the kv splits
+  merged inside a thread-block cluster (default) against the same step through the stand-alone
+  xb_qkv_finalize_kernel / xb_attn_combine2_kernel: every variant must produce identical logits -- ragged
+  contexts on both sides of a 64-key tile boundary, interleaved and half-split RoPE, q/k/v bias, 2-4 query
+  heads per kv head, pages smaller than / equal to a tile, graph replays included."""
+  from xotorch_support_jetson_b200.shard import Shard
+  from xotorch_support_jetson_b200.stage import StageRuntime
+  O, cfg, state = _setup(mid)
+  nl = cfg["num_layers"]
+  lens = [5, 61, 130]
+  g = torch.Generator().manual_seed(77)
+  prompts = [torch.randint(1, cfg["vocab_size"], (n,), generator=g, dtype=torch.int32).cuda() for n in lens]
+  steps = 6
+
+  def run(fuse, cluster, splits=None):
+    monkeypatch.setenv("XB_FUSE_QKV", str(fuse))
+    monkeypatch.setenv("XB_ATTN_CLUSTER", str(cluster))
+    if splits is None:
+      monkeypatch.delenv("XB_ATTN_SPLITS", raising=False)
+    else:
+      monkeypatch.setenv("XB_ATTN_SPLITS", str(splits))
+    st = StageRuntime(Shard(mid, 0, nl - 1, nl), cfg, device=0, max_batch_tokens=256, max_seqs=3, max_tokens_per_seq=192,
+                      page_tokens=page_tokens)
+    st.load_state(state)
+    outs = []
+    with torch.cuda.stream(torch.cuda.Stream()):
+      lg = st.forward([0, 1, 2], lens, [0, 0, 0], tokens=torch.cat(prompts))
+      outs.append(lg.clone())
+      tok = st.sample(lg, temp=0.0)
+      for k in range(steps):
+        lg = st.forward([0, 1, 2], [1, 1, 1], [n + k for n in lens], tokens=tok)
+        outs.append(lg.clone())
+        tok = st.sample(lg, temp=0.0)
+    torch.cuda.synchronize()
+    launches = st.counters()["launches"]
+    st.close()
+    return [o.cpu() for o in outs], launches
+
+  base, n_base = run(0, 0)
+  for fuse, cluster, splits in [(1, 0, None), (0, 1, None), (1, 1, None), (1, 16, None), (1, 1, 3), (0, 0, 3), (1, 1, 1)]:
+    got, n = run(fuse, cluster, splits)
+    if splits is None:
+      for a, b in zip(got, base):
+        assert torch.equal(a, b), (fuse, cluster, splits)
+      if fuse and cluster:
+        assert n < n_base      # fewer kernels per step
+    else:
+      # another split count changes the fp32 merge order: same result within rounding noise, and the two
+      # plumbing variants still agree with each other at equal split count (checked through the next entry)
+      for a, b in zip(got, base):
+        assert _rel(a.numpy(), b.numpy()) < 0.01, (fuse, cluster, splits)
+  a3, _ = run(1, 1, 3)
+  b3, _ = run(0, 0, 3)
+  for a, b in zip(a3, b3):
+    assert torch.equal(a, b)

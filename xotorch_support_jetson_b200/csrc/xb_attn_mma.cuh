@@ -147,28 +147,54 @@ __device__ __forceinline__ void att_issue_tile(const CUtensorMap* tmK, const CUt
 }
 
 // ----------------------------------------------------------------------------- decode
+#include <cooperative_groups.h>
+
 template <int HD, int G, int NST>
 struct AttDecCfg {
   static constexpr int TILE_BYTES = XB_ATT_TILE * HD * 2;
   static constexpr int STAGE_BYTES = 2 * TILE_BYTES;
   static constexpr int MERGE_BYTES = 4 * G * HD * 4 + 4 * 16 * 2 * 4;   // aliases the K/V ring after the key loop
-  static_assert(MERGE_BYTES <= NST * STAGE_BYTES, "merge buffers must fit in the K/V ring");
-  static constexpr int SMEM_BYTES = NST * STAGE_BYTES + 1024 + 128;
+  static constexpr int XCHG_OFF = (MERGE_BYTES + 1023) & ~1023;         // cluster exchange area (also in the ring), past the merge buffers
+  static constexpr int XCHG_BYTES = G * HD * 4 + G * 2 * 4;
+  static_assert(MERGE_BYTES <= XCHG_OFF && XCHG_OFF + XCHG_BYTES <= NST * STAGE_BYTES, "merge / exchange buffers must fit in the K/V ring");
+  static constexpr int ROWS_OFF = NST * STAGE_BYTES + 128;               // after the barriers: q of the group + the step's own k / v row
+  static constexpr int ROWS_BYTES = (G + 2) * HD * 2;
+  static constexpr int SMEM_BYTES = NST * STAGE_BYTES + 128 + ((ROWS_BYTES + 127) & ~127) + 1024;
 };
 
-template <int HD, int G, int NST>
+// FUSED: the q/k/v projection of the step, still in the split-K partial planes its Linear left behind.  The
+// attention block finishes the q rows of its own head group and -- in the block that holds the newest tile --
+// the step's k / v row (bias, bf16 rounding, RoPE; arithmetic of xb_qkv_finalize_kernel), appends that row to
+// the paged cache and uses it from shared memory: one launch and one dependency hop less per layer.
+struct QkvFin {
+  const float* part;
+  SplitInfo si;
+  long long split_stride;
+  const bf16* bias;
+  const float* rope;
+  bf16 *k_pool, *v_pool;
+  int rope_kind;
+};
+
+template <int HD, int G, int NST, bool FUSED>
 __global__ void __launch_bounds__(160) xb_attn_decode_mma_kernel(
     const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV, const bf16* __restrict__ q,
     BatchMeta m, float* __restrict__ o_part, float* __restrict__ ml_part, bf16* __restrict__ out, int H, int KV,
-    int n_splits, float scale_log2) {
+    int n_splits, float scale_log2, QkvFin f, int cluster_merge) {
+  namespace cg = cooperative_groups;
   using Cfg = AttDecCfg<HD, G, NST>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* stages = smem;
   float* mg_o = reinterpret_cast<float*>(smem);                            // [4 warps][G][HD], reuses the ring
   float* mg_ml = mg_o + 4 * G * HD;                                       // [4 warps][16][2]
+  float* xc_o = reinterpret_cast<float*>(smem + Cfg::XCHG_OFF);            // [G][HD] this split's merged accumulator
+  float* xc_ml = xc_o + G * HD;                                           // [G][2]  (max, sum)
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + NST * Cfg::STAGE_BYTES);
   uint64_t* empty_bar = full_bar + NST;
+  bf16* sQ = reinterpret_cast<bf16*>(smem + Cfg::ROWS_OFF);                // [G][HD]
+  bf16* sKrow = sQ + G * HD;                                              // [HD]
+  bf16* sVrow = sKrow + HD;                                               // [HD]
 
   const int t = blockIdx.x, kvh = blockIdx.y, sp = blockIdx.z;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -176,10 +202,11 @@ __global__ void __launch_bounds__(160) xb_attn_decode_mma_kernel(
   // The batch metadata and page table were uploaded before the step's first kernel started, and
   // every K/V row below position `pos` was written by an EARLIER step: only q and the row at `pos`
   // come from the kernel just upstream.  So the producer streams the older tiles before
-  // griddepcontrol.wait -- the K/V reads overlap the q/k/v Linear and its finalize kernel.
+  // griddepcontrol.wait -- the K/V reads overlap the q/k/v Linear.
   // (Safe because every forward call begins with the metadata H2D copy, a full stream dependency:
-  // no kernel of an earlier call can still be running, and within a call only the kernel just
-  // upstream writes this layer's pool, at row `pos`.)
+  // no kernel of an earlier call can still be running, and within a call nothing else writes this
+  // layer's pool.)  FUSED: the row at `pos` is made by THIS block and patched into the staged tile,
+  // so the producer never waits at all -- what the TMA reads for that one row does not matter.
   const int pos = m.tok_pos[t];
   const int slot = m.seq_slot[m.tok_seq[t]];
   const int* pt = m.page_table + (long long)slot * m.max_pages;
@@ -203,7 +230,7 @@ __global__ void __launch_bounds__(160) xb_attn_decode_mma_kernel(
       tma_prefetch_desc(&tmV);
       int stage = 0;
       uint32_t phase = 0;
-      bool waited = false;
+      bool waited = FUSED;
       for (int kt = kt0; kt < kt1; ++kt) {
         if (!waited && (kt - kt0 >= NST || kt >= n_tiles - 1)) {   // ring full, or the tile holding row `pos`
           pdl_wait();
@@ -215,86 +242,180 @@ __global__ void __launch_bounds__(160) xb_attn_decode_mma_kernel(
         if (++stage == NST) { stage = 0; phase ^= 1; }
       }
     }
-    return;
-  }
-  pdl_wait();   // compute warps: q, and (through the last tile) the newest K/V row
+  } else {
+    pdl_wait();   // compute warps: q (or the projection's partial planes), and the newest K/V row
 
-  // ===================== 4 compute warps: each takes 16 keys of every tile =====================
-  constexpr int KS = HD / 16, DT = HD / 8;
-  uint32_t qf[KS][4];
-  {
-    // A fragment rows: r0 = lane/4 (a head of the group when < G), r1 = r0 + 8 (always padding)
-    const int r0 = lane >> 2;
-    const bf16* qrow = q + ((long long)t * H + (kvh * G + (r0 < G ? r0 : 0))) * HD + ((lane & 3) << 1);
+    constexpr int KS = HD / 16, DT = HD / 8;
+    if (FUSED) {
+      // ---- finish q of this head group (every split needs it) and, where the newest tile lives, the k / v row
+      const int heads = H + 2 * KV, half = HD >> 1;
+      const long long base = (long long)t * heads * HD;
+      const float* rope_row = f.rope + (long long)pos * half * 2;
+      const int iph = f.rope_kind == 0 ? HD / 4 : HD / 8;
+      const bool owns_last = kt1 == n_tiles && kt1 > kt0;
+      const int n_items = (G + (owns_last ? 2 : 0)) * iph;
+      const int page = pt[pos / m.page_tokens], off = pos % m.page_tokens;
+      const long long grow = (((long long)page * KV + kvh) * m.page_tokens + off) * HD;
+      for (int it = threadIdx.x; it < n_items; it += 128) {
+        const int hsel = it / iph, c = (it % iph) * 4;
+        int head;
+        bf16 *sdst, *gdst = nullptr;
+        if (hsel < G) { head = kvh * G + hsel; sdst = sQ + hsel * HD; }
+        else if (hsel == G) { head = H + kvh; sdst = sKrow; gdst = f.k_pool + grow; }
+        else { head = H + KV + kvh; sdst = sVrow; gdst = f.v_pool + grow; }
+        float x[4], y[4];
+        qkv_item(f.part, f.si, f.split_stride, base, head, c, HD, head < H + KV, f.bias, rope_row, f.rope_kind, x, y);
+        qkv_store4(sdst + c, x);
+        if (gdst != nullptr) qkv_store4(gdst + c, x);        // KVCache.update: later steps read it from the pool
+        if (f.rope_kind != 0) {
+          qkv_store4(sdst + half + c, y);
+          if (gdst != nullptr) qkv_store4(gdst + half + c, y);
+        }
+      }
+      named_bar_sync(1, 128);
+    }
+
+    // ===================== 4 compute warps: each takes 16 keys of every tile =====================
+    uint32_t qf[KS][4];
+    {
+      // A fragment rows: r0 = lane/4 (a head of the group when < G), r1 = r0 + 8 (always padding)
+      const int r0 = lane >> 2;
+      const bf16* qrow = FUSED ? sQ + (r0 < G ? r0 : 0) * HD + ((lane & 3) << 1)
+                               : q + ((long long)t * H + (kvh * G + (r0 < G ? r0 : 0))) * HD + ((lane & 3) << 1);
 #pragma unroll
-    for (int ks = 0; ks < KS; ++ks) {
-      uint32_t lo = 0, hi = 0;
+      for (int ks = 0; ks < KS; ++ks) {
+        uint32_t lo = 0, hi = 0;
+        if (r0 < G) {
+          lo = *reinterpret_cast<const uint32_t*>(qrow + ks * 16);
+          hi = *reinterpret_cast<const uint32_t*>(qrow + ks * 16 + 8);
+        }
+        qf[ks][0] = lo; qf[ks][1] = 0u; qf[ks][2] = hi; qf[ks][3] = 0u;
+      }
+    }
+    float mrow[2] = {-INFINITY, -INFINITY}, lrow[2] = {0.f, 0.f};
+    float o[DT][4];
+#pragma unroll
+    for (int d = 0; d < DT; ++d) o[d][0] = o[d][1] = o[d][2] = o[d][3] = 0.f;
+
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kt = kt0; kt < kt1; ++kt) {
+      mbar_wait(&full_bar[stage], phase);
+      const int key_abs0 = kt * XB_ATT_TILE;
+      if (FUSED && kt == n_tiles - 1 && warp == ((pos & (XB_ATT_TILE - 1)) >> 4)) {
+        // the step's own row: only this warp reads it (its 16 keys of the tile) -- overwrite what the TMA staged
+        const int r = pos & (XB_ATT_TILE - 1);
+        uint8_t* sKt = stages + stage * Cfg::STAGE_BYTES;
+        constexpr int CH = HD / 8;   // 16-byte chunks per row
+        for (int i = lane; i < 2 * CH; i += 32) {
+          const int which = i / CH, c16 = i % CH;
+          const uint4 v = *reinterpret_cast<const uint4*>((which ? sVrow : sKrow) + c16 * 8);
+          *reinterpret_cast<uint4*>(sKt + which * Cfg::TILE_BYTES + att_tile_off(r, c16)) = v;
+        }
+        __syncwarp();
+      }
+      if (key_abs0 + warp * 16 <= pos) {
+        const uint32_t sK = smem_u32(stages + stage * Cfg::STAGE_BYTES);
+        att_warp_block<HD, 1>(qf, sK, sK + Cfg::TILE_BYTES, warp * 16, key_abs0, pos, pos, scale_log2, mrow, lrow, o);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty_bar[stage]);
+      if (++stage == NST) { stage = 0; phase ^= 1; }
+    }
+
+    // ---- merge the 4 warps (each saw a disjoint key subset); only rows < G are real
+    named_bar_sync(1, 128);   // every warp is done reading the ring: its memory now holds the merge buffers
+    lrow[0] += __shfl_xor_sync(0xffffffffu, lrow[0], 1);
+    lrow[0] += __shfl_xor_sync(0xffffffffu, lrow[0], 2);
+    {
+      const int r0 = lane >> 2;
       if (r0 < G) {
-        lo = *reinterpret_cast<const uint32_t*>(qrow + ks * 16);
-        hi = *reinterpret_cast<const uint32_t*>(qrow + ks * 16 + 8);
+        if ((lane & 3) == 0) {
+          mg_ml[(warp * 16 + r0) * 2] = mrow[0];
+          mg_ml[(warp * 16 + r0) * 2 + 1] = lrow[0];
+        }
+#pragma unroll
+        for (int d = 0; d < DT; ++d)
+          *reinterpret_cast<float2*>(&mg_o[(warp * G + r0) * HD + d * 8 + ((lane & 3) << 1)]) = make_float2(o[d][0], o[d][1]);
       }
-      qf[ks][0] = lo; qf[ks][1] = 0u; qf[ks][2] = hi; qf[ks][3] = 0u;
+    }
+    named_bar_sync(1, 128);
+    for (int idx = threadIdx.x; idx < G * HD; idx += 128) {
+      const int g = idx / HD, d = idx % HD;
+      float M = -INFINITY;
+#pragma unroll
+      for (int w = 0; w < 4; ++w) M = fmaxf(M, mg_ml[(w * 16 + g) * 2]);
+      float L = 0.f, A = 0.f;
+      if (M > -INFINITY) {
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+          const float mw = mg_ml[(w * 16 + g) * 2];
+          const float wt = mw == -INFINITY ? 0.f : exp2f(mw - M);
+          L += mg_ml[(w * 16 + g) * 2 + 1] * wt;
+          A += mg_o[(w * G + g) * HD + d] * wt;
+        }
+      }
+      const int hh = kvh * G + g;
+      if (n_splits == 1) {
+        out[((long long)t * H + hh) * HD + d] = f2bf(L > 0.f ? A / L : 0.f);
+      } else if (cluster_merge) {
+        xc_o[idx] = A;
+        if (d == 0) { xc_ml[g * 2] = M; xc_ml[g * 2 + 1] = L; }       // M in log2 units
+      } else {
+        const long long oo = ((long long)t * H + hh) * n_splits + sp;
+        o_part[oo * HD + d] = A;
+        if (d == 0) { ml_part[oo * 2] = M; ml_part[oo * 2 + 1] = L; }   // M in log2 units
+      }
     }
   }
-  float mrow[2] = {-INFINITY, -INFINITY}, lrow[2] = {0.f, 0.f};
-  float o[DT][4];
-#pragma unroll
-  for (int d = 0; d < DT; ++d) o[d][0] = o[d][1] = o[d][2] = o[d][3] = 0.f;
 
-  int stage = 0;
-  uint32_t phase = 0;
-  for (int kt = kt0; kt < kt1; ++kt) {
-    mbar_wait(&full_bar[stage], phase);
-    const int key_abs0 = kt * XB_ATT_TILE;
-    if (key_abs0 + warp * 16 <= pos) {
-      const uint32_t sK = smem_u32(stages + stage * Cfg::STAGE_BYTES);
-      att_warp_block<HD, 1>(qf, sK, sK + Cfg::TILE_BYTES, warp * 16, key_abs0, pos, pos, scale_log2, mrow, lrow, o);
-    }
-    __syncwarp();
-    if (lane == 0) mbar_arrive(&empty_bar[stage]);
-    if (++stage == NST) { stage = 0; phase ^= 1; }
-  }
-
-  // ---- merge the 4 warps (each saw a disjoint key subset); only rows < G are real
-  named_bar_sync(1, 128);   // every warp is done reading the ring: its memory now holds the merge buffers
-  lrow[0] += __shfl_xor_sync(0xffffffffu, lrow[0], 1);
-  lrow[0] += __shfl_xor_sync(0xffffffffu, lrow[0], 2);
-  {
-    const int r0 = lane >> 2;
-    if (r0 < G) {
-      if ((lane & 3) == 0) {
-        mg_ml[(warp * 16 + r0) * 2] = mrow[0];
-        mg_ml[(warp * 16 + r0) * 2 + 1] = lrow[0];
+  if (cluster_merge && n_splits > 1) {
+    // ---- the kv splits of one (token, kv head) form a thread-block cluster (rank = split): the first block
+    // merges all partials straight out of its peers' shared memory -- the arithmetic, in the order, of
+    // xb_attn_combine2_kernel, without that kernel's launch or the round trip through global memory
+    cg::cluster_group cluster = cg::this_cluster();
+    cluster.sync();
+    if (sp == 0 && warp < 4) {
+      for (int g = warp; g < G; g += 4) {
+        float ms = -INFINITY, ls = 0.f;
+        if (lane < n_splits) {
+          const float* pml = cluster.map_shared_rank(xc_ml, lane);
+          ms = pml[g * 2];
+          ls = pml[g * 2 + 1];
+        }
+        const float M = warp_max(ms);
+        const float w = (ms == -INFINITY) ? 0.f : exp2f(ms - M);
+        const float L = warp_sum(ls * w);
+        constexpr int VPL = HD / 32;
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int s0 = 0; s0 < n_splits; s0 += 8) {
+          float4 v[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (s0 + u < n_splits) {
+              const float* src = cluster.map_shared_rank(xc_o, s0 + u) + g * HD + lane * VPL;
+              if (VPL == 4) v[u] = *reinterpret_cast<const float4*>(src);
+              else { const float2 t2 = *reinterpret_cast<const float2*>(src); v[u].x = t2.x; v[u].y = t2.y; }
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const float ws = __shfl_sync(0xffffffffu, w, (s0 + u) & 31);
+            if (s0 + u < n_splits) {
+              acc[0] = fmaf(ws, v[u].x, acc[0]); acc[1] = fmaf(ws, v[u].y, acc[1]);
+              acc[2] = fmaf(ws, v[u].z, acc[2]); acc[3] = fmaf(ws, v[u].w, acc[3]);
+            }
+          }
+        }
+        const float invL = L > 0.f ? 1.0f / L : 0.f;
+        bf16* dst = out + ((long long)t * H + kvh * G + g) * HD + lane * VPL;
+#pragma unroll
+        for (int j = 0; j < VPL; j += 2)
+          *reinterpret_cast<uint32_t*>(dst + j) = f2_to_bf2(acc[j] * invL, acc[j + 1] * invL);
       }
-#pragma unroll
-      for (int d = 0; d < DT; ++d)
-        *reinterpret_cast<float2*>(&mg_o[(warp * G + r0) * HD + d * 8 + ((lane & 3) << 1)]) = make_float2(o[d][0], o[d][1]);
     }
-  }
-  named_bar_sync(1, 128);
-  for (int idx = threadIdx.x; idx < G * HD; idx += 128) {
-    const int g = idx / HD, d = idx % HD;
-    float M = -INFINITY;
-#pragma unroll
-    for (int w = 0; w < 4; ++w) M = fmaxf(M, mg_ml[(w * 16 + g) * 2]);
-    float L = 0.f, A = 0.f;
-    if (M > -INFINITY) {
-#pragma unroll
-      for (int w = 0; w < 4; ++w) {
-        const float mw = mg_ml[(w * 16 + g) * 2];
-        const float wt = mw == -INFINITY ? 0.f : exp2f(mw - M);
-        L += mg_ml[(w * 16 + g) * 2 + 1] * wt;
-        A += mg_o[(w * G + g) * HD + d] * wt;
-      }
-    }
-    const int hh = kvh * G + g;
-    if (n_splits == 1) {
-      out[((long long)t * H + hh) * HD + d] = f2bf(L > 0.f ? A / L : 0.f);
-    } else {
-      const long long oo = ((long long)t * H + hh) * n_splits + sp;
-      o_part[oo * HD + d] = A;
-      if (d == 0) { ml_part[oo * 2] = M; ml_part[oo * 2 + 1] = L; }   // M in log2 units
-    }
+    cluster.sync();   // the peers' shared memory must outlive the first block's reads
   }
 }
 

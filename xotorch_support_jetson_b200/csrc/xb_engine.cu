@@ -91,6 +91,8 @@ struct xb_engine {
   int max_attn_splits = 32;
   // decode Linears with a fused reduction (xb_gemm.cuh skinny_finish): arrival counters per 128-feature tile
   int* tile_ctr = nullptr;
+  int fuse_qkv = 1;       // XB_FUSE_QKV=0: q/k/v finalize as its own kernel instead of the decode attention's prologue
+  int attn_cluster = 1;   // XB_ATTN_CLUSTER=0: kv splits merged by xb_attn_combine2_kernel instead of a cluster + DSMEM; 16: clusters of up to 16
   int fuse_epi = 0;       // XB_FUSE_EPI=1: reduce + q/k/v / SiLU epilogue inside the decode Linear (measured slower, see xb_gemm.cuh)
   int meta_T = 0;         // token rows the device metadata currently describes
   std::map<long long, GemmPlan> plans;
@@ -122,8 +124,8 @@ static inline bool shard_is_last(const xb_model_desc& d) { return d.end_layer ==
 // Launch one kernel of the forward: programmatic dependent launch (the kernel calls
 // griddepcontrol.wait before touching upstream data) and an optional cluster dimension.
 template <typename... KArgs, typename... Args>
-static int launch_k(xb_engine* e, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, int cluster_x,
-                    Args... args) {
+static int launch_kc(xb_engine* e, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, dim3 cluster,
+                     Args... args) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = block;
@@ -136,11 +138,11 @@ static int launch_k(xb_engine* e, void (*kern)(KArgs...), dim3 grid, dim3 block,
     attr[na].val.programmaticStreamSerializationAllowed = 1;
     ++na;
   }
-  if (cluster_x > 1) {
+  if (cluster.x * cluster.y * cluster.z > 1) {
     attr[na].id = cudaLaunchAttributeClusterDimension;
-    attr[na].val.clusterDim.x = cluster_x;
-    attr[na].val.clusterDim.y = 1;
-    attr[na].val.clusterDim.z = 1;
+    attr[na].val.clusterDim.x = cluster.x;
+    attr[na].val.clusterDim.y = cluster.y;
+    attr[na].val.clusterDim.z = cluster.z;
     ++na;
   }
   cfg.attrs = attr;
@@ -148,6 +150,12 @@ static int launch_k(xb_engine* e, void (*kern)(KArgs...), dim3 grid, dim3 block,
   XB_CUDA(cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...));
   e->c.launches++;
   return 0;
+}
+
+template <typename... KArgs, typename... Args>
+static int launch_k(xb_engine* e, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, int cluster_x,
+                    Args... args) {
+  return launch_kc(e, kern, grid, block, smem, st, dim3(cluster_x > 1 ? cluster_x : 1, 1, 1), args...);
 }
 
 static int dmalloc(void** p, size_t bytes) {
@@ -301,6 +309,10 @@ extern "C" int xb_engine_create(const xb_model_desc* desc, int device, xb_engine
     if (g != nullptr && g[0] == '0') e->use_pdl = 0;
     g = getenv("XB_FUSE_EPI");
     if (g != nullptr) e->fuse_epi = g[0] == '1';
+    g = getenv("XB_FUSE_QKV");
+    if (g != nullptr) e->fuse_qkv = g[0] != '0';
+    g = getenv("XB_ATTN_CLUSTER");
+    if (g != nullptr) e->attn_cluster = atoi(g);
   }
   *out = e;
   return 0;
@@ -733,27 +745,48 @@ static int get_plan(xb_engine* e, int site, int layer, const bf16* x, long long 
   return 0;
 }
 
-template <int HD, int G>
-static int launch_attn_g(xb_engine* e, const LayerW& w, const BatchMeta& m, int T, int n_splits, int n_tiles,
-                         cudaStream_t st) {
+template <int HD, int G, bool FUSED>
+static int launch_attn_decode(xb_engine* e, const LayerW& w, const BatchMeta& m, int T, int n_splits, cudaStream_t st,
+                              const QkvFin& fin) {
   const xb_model_desc& d = e->d;
   const float scale_log2 = (1.0f / sqrtf((float)d.head_dim)) * 1.4426950408889634f;
 #ifndef XB_ATT_DEC_NST
 #define XB_ATT_DEC_NST 3
 #endif
   constexpr int NST = XB_ATT_DEC_NST;
-  if (n_tiles == 0) {
-    // decode: one block per (token, kv head, kv split)
-    using Cfg = AttDecCfg<HD, G, NST>;
-    XB_SMEM_ATTR_ONCE((xb_attn_decode_mma_kernel<HD, G, NST>), Cfg::SMEM_BYTES);
-    dim3 grid(T, d.n_kv_heads, n_splits);
-    XB_TRY(launch_k(e, xb_attn_decode_mma_kernel<HD, G, NST>, dim3(grid), dim3(160), Cfg::SMEM_BYTES, st, 1, w.tmK, w.tmV, e->q, m, e->o_part, e->ml_part,
-                                                                              e->attn, d.n_heads, d.n_kv_heads, n_splits,
-                                                                              scale_log2));
-    if (n_splits > 1) {
-      const int rows = T * d.n_heads;
-      XB_TRY(launch_k(e, xb_attn_combine2_kernel<HD>, dim3((rows + 3) / 4), dim3(128), 0, st, 1, e->o_part, e->ml_part, e->attn, n_splits, rows));
+  // decode: one block per (token, kv head, kv split); the splits of one (token, kv head) are a cluster
+  using Cfg = AttDecCfg<HD, G, NST>;
+  auto kern = xb_attn_decode_mma_kernel<HD, G, NST, FUSED>;
+  XB_SMEM_ATTR_ONCE(kern, Cfg::SMEM_BYTES);
+  const int cl = (e->attn_cluster && n_splits > 1) ? 1 : 0;
+  if (cl && n_splits > 8) {
+    static bool np_done[XB_MAX_DEVICES] = {false};
+    int dev = 0;
+    XB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= XB_MAX_DEVICES || !np_done[dev]) {
+      XB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+      if (dev >= 0 && dev < XB_MAX_DEVICES) np_done[dev] = true;
     }
+  }
+  dim3 grid(T, d.n_kv_heads, n_splits);
+  XB_TRY(launch_kc(e, kern, grid, dim3(160), Cfg::SMEM_BYTES, st, dim3(1, 1, cl ? n_splits : 1), w.tmK, w.tmV, e->q, m, e->o_part,
+                   e->ml_part, e->attn, d.n_heads, d.n_kv_heads, n_splits, scale_log2, fin, cl));
+  if (n_splits > 1 && !cl) {
+    const int rows = T * d.n_heads;
+    XB_TRY(launch_k(e, xb_attn_combine2_kernel<HD>, dim3((rows + 3) / 4), dim3(128), 0, st, 1, e->o_part, e->ml_part, e->attn, n_splits, rows));
+  }
+  return 0;
+}
+
+// fin != nullptr: decode with the q/k/v finalize folded into the attention kernel (see QkvFin)
+template <int HD, int G>
+static int launch_attn_g(xb_engine* e, const LayerW& w, const BatchMeta& m, int T, int n_splits, int n_tiles,
+                         cudaStream_t st, const QkvFin* fin) {
+  const xb_model_desc& d = e->d;
+  const float scale_log2 = (1.0f / sqrtf((float)d.head_dim)) * 1.4426950408889634f;
+  if (n_tiles == 0) {
+    if (fin != nullptr) return launch_attn_decode<HD, G, true>(e, w, m, T, n_splits, st, *fin);
+    return launch_attn_decode<HD, G, false>(e, w, m, T, n_splits, st, QkvFin{});
   } else {
     // prefill: one block per (query tile, kv head), tcgen05 flash attention
     using Cfg = AttTcCfg<HD>;
@@ -765,16 +798,17 @@ static int launch_attn_g(xb_engine* e, const LayerW& w, const BatchMeta& m, int 
 }
 
 template <int HD>
-static int launch_attn(xb_engine* e, const LayerW& w, const BatchMeta& m, int T, int n_splits, int n_tiles, cudaStream_t st) {
+static int launch_attn(xb_engine* e, const LayerW& w, const BatchMeta& m, int T, int n_splits, int n_tiles, cudaStream_t st,
+                       const QkvFin* fin = nullptr) {
   switch (e->d.n_heads / e->d.n_kv_heads) {
-    case 1: return launch_attn_g<HD, 1>(e, w, m, T, n_splits, n_tiles, st);
-    case 2: return launch_attn_g<HD, 2>(e, w, m, T, n_splits, n_tiles, st);
-    case 3: return launch_attn_g<HD, 3>(e, w, m, T, n_splits, n_tiles, st);
-    case 4: return launch_attn_g<HD, 4>(e, w, m, T, n_splits, n_tiles, st);
-    case 5: return launch_attn_g<HD, 5>(e, w, m, T, n_splits, n_tiles, st);
-    case 6: return launch_attn_g<HD, 6>(e, w, m, T, n_splits, n_tiles, st);
-    case 7: return launch_attn_g<HD, 7>(e, w, m, T, n_splits, n_tiles, st);
-    case 8: return launch_attn_g<HD, 8>(e, w, m, T, n_splits, n_tiles, st);
+    case 1: return launch_attn_g<HD, 1>(e, w, m, T, n_splits, n_tiles, st, fin);
+    case 2: return launch_attn_g<HD, 2>(e, w, m, T, n_splits, n_tiles, st, fin);
+    case 3: return launch_attn_g<HD, 3>(e, w, m, T, n_splits, n_tiles, st, fin);
+    case 4: return launch_attn_g<HD, 4>(e, w, m, T, n_splits, n_tiles, st, fin);
+    case 5: return launch_attn_g<HD, 5>(e, w, m, T, n_splits, n_tiles, st, fin);
+    case 6: return launch_attn_g<HD, 6>(e, w, m, T, n_splits, n_tiles, st, fin);
+    case 7: return launch_attn_g<HD, 7>(e, w, m, T, n_splits, n_tiles, st, fin);
+    case 8: return launch_attn_g<HD, 8>(e, w, m, T, n_splits, n_tiles, st, fin);
   }
   return xb_fail(1, "GQA group size %d not supported (1..8)", e->d.n_heads / e->d.n_kv_heads);
 }
@@ -812,6 +846,8 @@ static int choose_kv_splits(xb_engine* e, int T, int max_ctx) {
   if (n > 16) n = 16;
   if (ov != nullptr && atoi(ov) > 0) n = atoi(ov);
   if (n > tiles) n = tiles;
+  // the splits of a (token, kv head) are merged inside one thread-block cluster: 8 blocks portable, 16 with XB_ATTN_CLUSTER=16
+  if (e->attn_cluster && n > (e->attn_cluster >= 16 ? 16 : 8)) n = e->attn_cluster >= 16 ? 16 : 8;
   if (n > e->max_attn_splits) n = e->max_attn_splits;
   if (n < 1) n = 1;
   return n;
@@ -886,14 +922,22 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
     XB_TRY(get_plan(e, SITE_QKV, l, e->hn, D, w.wqkv, T, e->NQKV, D, e->gemm_out, e->NQKV, w.bqkv, 0, &gp));
     XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
     LAUNCH_COUNT(e);
+    QkvFin fin{};
+    const QkvFin* finp = nullptr;
     if (gp->args.mode == XB_GEMM_SKINNY && gp->args.epi == XB_EPI_PLAIN) {
-      const int qkv_items = (d.n_heads + 2 * d.n_kv_heads) * (d.rope_kind == 0 ? hd / 4 : hd / 8);
-      XB_TRY(launch_k(e, xb_qkv_finalize_kernel, dim3(T, (qkv_items + 255) / 256), dim3(256), 0, st, 1, (const float*)e->gemm_out, gp->split,
-                      (long long)T * e->NQKV, w.bqkv, e->rope, e->q, w.k_pool, w.v_pool, m, d.n_heads, d.n_kv_heads, hd,
-                      d.rope_kind));
+      if (e->fuse_qkv && n_tiles == 0) {
+        // decode: the attention blocks reduce the planes, apply bias + RoPE and append the k / v row themselves
+        fin = QkvFin{(const float*)e->gemm_out, gp->split, (long long)T * e->NQKV, w.bqkv, e->rope, w.k_pool, w.v_pool, d.rope_kind};
+        finp = &fin;
+      } else {
+        const int qkv_items = (d.n_heads + 2 * d.n_kv_heads) * (d.rope_kind == 0 ? hd / 4 : hd / 8);
+        XB_TRY(launch_k(e, xb_qkv_finalize_kernel, dim3(T, (qkv_items + 255) / 256), dim3(256), 0, st, 1, (const float*)e->gemm_out, gp->split,
+                        (long long)T * e->NQKV, w.bqkv, e->rope, e->q, w.k_pool, w.v_pool, m, d.n_heads, d.n_kv_heads, hd,
+                        d.rope_kind));
+      }
     }
-    if (hd == 128) XB_TRY(launch_attn<128>(e, w, m, T, n_splits, n_tiles, st));
-    else XB_TRY(launch_attn<64>(e, w, m, T, n_splits, n_tiles, st));
+    if (hd == 128) XB_TRY(launch_attn<128>(e, w, m, T, n_splits, n_tiles, st, finp));
+    else XB_TRY(launch_attn<64>(e, w, m, T, n_splits, n_tiles, st, finp));
     // output projection + residual + mlp_norm
     XB_TRY(get_plan(e, SITE_O, l, e->attn, e->NQ, w.wo, T, D, e->NQ, e->gemm_out, D, nullptr, 0, &gp));
     XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));

@@ -328,6 +328,45 @@ __device__ __forceinline__ void qkv_load4(const float* __restrict__ part, const 
   x[0] = rbf(a.x); x[1] = rbf(a.y); x[2] = rbf(a.z); x[3] = rbf(a.w);
 }
 
+// One work item of the finalize: 4 consecutive elements [c, c+4) of fused-projection head `head` (interleaved
+// RoPE: two pairs) or, for half-split RoPE, those 4 plus their partners [half+c, half+c+4).  x (and y) receive the
+// finished bf16-representable values.  Shared by the stand-alone kernel below and by the decode attention kernel,
+// which does this work in its prologue (xb_attn_mma.cuh) -- one arithmetic, bit-identical results.
+__device__ __forceinline__ void qkv_item(const float* __restrict__ part, const SplitInfo& si, long long split_stride,
+                                         long long base, int head, int c, int hd, bool rot, const bf16* __restrict__ bias,
+                                         const float* __restrict__ rope_row, int rope_kind, float* x, float* y) {
+  const int half = hd >> 1;
+  qkv_load4(part, si, split_stride, base, head * hd + c, bias, x);
+  if (rope_kind == 0) {
+    if (rot) {
+      const float4 cs = *reinterpret_cast<const float4*>(rope_row + c);   // (cos,sin) of pairs c/2, c/2+1
+      const float a0 = x[0], b0 = x[1], a1 = x[2], b1 = x[3];
+      x[0] = __fsub_rn(__fmul_rn(a0, cs.x), __fmul_rn(b0, cs.y));
+      x[1] = __fadd_rn(__fmul_rn(b0, cs.x), __fmul_rn(a0, cs.y));
+      x[2] = __fsub_rn(__fmul_rn(a1, cs.z), __fmul_rn(b1, cs.w));
+      x[3] = __fadd_rn(__fmul_rn(b1, cs.z), __fmul_rn(a1, cs.w));
+    }
+  } else {
+    qkv_load4(part, si, split_stride, base, head * hd + half + c, bias, y);
+    if (rot) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 cs = *reinterpret_cast<const float2*>(rope_row + (c + j) * 2);
+        const float cc = rbf(cs.x), ss = rbf(cs.y);
+        const float a = x[j], b = y[j];
+        x[j] = __fadd_rn(rbf(__fmul_rn(a, cc)), rbf(__fmul_rn(-b, ss)));
+        y[j] = __fadd_rn(rbf(__fmul_rn(b, cc)), rbf(__fmul_rn(a, ss)));
+      }
+    }
+  }
+}
+__device__ __forceinline__ void qkv_store4(bf16* dst, const float* x) {
+  uint2 o;
+  o.x = f2_to_bf2(x[0], x[1]);
+  o.y = f2_to_bf2(x[2], x[3]);
+  *reinterpret_cast<uint2*>(dst) = o;
+}
+
 __global__ void __launch_bounds__(256) xb_qkv_finalize_kernel(const float* __restrict__ part, SplitInfo si, long long split_stride,
                                                               const bf16* __restrict__ bias, const float* __restrict__ rope,
                                                               bf16* __restrict__ q_out, bf16* __restrict__ k_pool,
@@ -359,42 +398,10 @@ __global__ void __launch_bounds__(256) xb_qkv_finalize_kernel(const float* __res
       bf16* pool = (head < H + KV) ? k_pool : v_pool;
       dst = pool + (((long long)page * KV + kvh) * m.page_tokens + off) * hd;
     }
-    float x[4];
-    qkv_load4(part, si, split_stride, base, head * hd + c, bias, x);
-    if (rope_kind == 0) {
-      if (head < H + KV) {
-        const float4 cs = *reinterpret_cast<const float4*>(rope_row + c);   // (cos,sin) of pairs c/2, c/2+1
-        const float a0 = x[0], b0 = x[1], a1 = x[2], b1 = x[3];
-        x[0] = __fsub_rn(__fmul_rn(a0, cs.x), __fmul_rn(b0, cs.y));
-        x[1] = __fadd_rn(__fmul_rn(b0, cs.x), __fmul_rn(a0, cs.y));
-        x[2] = __fsub_rn(__fmul_rn(a1, cs.z), __fmul_rn(b1, cs.w));
-        x[3] = __fadd_rn(__fmul_rn(b1, cs.z), __fmul_rn(a1, cs.w));
-      }
-      uint2 o;
-      o.x = f2_to_bf2(x[0], x[1]);
-      o.y = f2_to_bf2(x[2], x[3]);
-      *reinterpret_cast<uint2*>(dst + c) = o;
-    } else {
-      float y[4];
-      qkv_load4(part, si, split_stride, base, head * hd + half + c, bias, y);
-      if (head < H + KV) {
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const float2 cs = *reinterpret_cast<const float2*>(rope_row + (c + j) * 2);
-          const float cc = rbf(cs.x), ss = rbf(cs.y);
-          const float a = x[j], b = y[j];
-          x[j] = __fadd_rn(rbf(__fmul_rn(a, cc)), rbf(__fmul_rn(-b, ss)));
-          y[j] = __fadd_rn(rbf(__fmul_rn(b, cc)), rbf(__fmul_rn(a, ss)));
-        }
-      }
-      uint2 o;
-      o.x = f2_to_bf2(x[0], x[1]);
-      o.y = f2_to_bf2(x[2], x[3]);
-      *reinterpret_cast<uint2*>(dst + c) = o;
-      o.x = f2_to_bf2(y[0], y[1]);
-      o.y = f2_to_bf2(y[2], y[3]);
-      *reinterpret_cast<uint2*>(dst + half + c) = o;
-    }
+    float x[4], y[4];
+    qkv_item(part, si, split_stride, base, head, c, hd, head < H + KV, bias, rope_row, rope_kind, x, y);
+    qkv_store4(dst + c, x);
+    if (rope_kind != 0) qkv_store4(dst + half + c, y);
   }
 }
 
