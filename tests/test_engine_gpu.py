@@ -565,6 +565,7 @@ def test_decode_attention_variants_are_bit_identical(built_lib, monkeypatch, mid
   g = torch.Generator().manual_seed(77)
   prompts = [torch.randint(1, cfg["vocab_size"], (n,), generator=g, dtype=torch.int32).cuda() for n in lens]
   steps = 6
+  feed = [torch.randint(1, cfg["vocab_size"], (3,), generator=g, dtype=torch.int32).cuda() for _ in range(steps)]
 
   def run(fuse, cluster, splits=None):
     monkeypatch.setenv("XB_FUSE_QKV", str(fuse))
@@ -580,11 +581,9 @@ def test_decode_attention_variants_are_bit_identical(built_lib, monkeypatch, mid
     with torch.cuda.stream(torch.cuda.Stream()):
       lg = st.forward([0, 1, 2], lens, [0, 0, 0], tokens=torch.cat(prompts))
       outs.append(lg.clone())
-      tok = st.sample(lg, temp=0.0)
-      for k in range(steps):
-        lg = st.forward([0, 1, 2], [1, 1, 1], [n + k for n in lens], tokens=tok)
+      for k in range(steps):    # fixed ids, so that a near-tie in one variant cannot send the runs down different paths
+        lg = st.forward([0, 1, 2], [1, 1, 1], [n + k for n in lens], tokens=feed[k])
         outs.append(lg.clone())
-        tok = st.sample(lg, temp=0.0)
     torch.cuda.synchronize()
     launches = st.counters()["launches"]
     st.close()
@@ -602,7 +601,7 @@ def test_decode_attention_variants_are_bit_identical(built_lib, monkeypatch, mid
       # another split count changes the fp32 merge order: same result within rounding noise, and the two
       # plumbing variants still agree with each other at equal split count (checked through the next entry)
       for a, b in zip(got, base):
-        assert _rel(a.numpy(), b.numpy()) < 0.01, (fuse, cluster, splits)
+        assert _rel(a.numpy(), b.numpy()) < REL_TOL / 2, (fuse, cluster, splits)
   a3, _ = run(1, 1, 3)
   b3, _ = run(0, 0, 3)
   for a, b in zip(a3, b3):
