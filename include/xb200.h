@@ -210,8 +210,7 @@ int xb_debug_linear(const void* x, const void* w, int T, int N, int K, float* y,
  * llm_utils.py:513-522) and the LM head on a last shard (llm_utils.py:425-435) -- `iters`
  * times back to back on `stream`, on the engine's own weights.  The caller brackets the
  * call with CUDA events; *n_launches receives the number of kernels enqueued.
- * With XB_FUSE_EPI=1 (decode Linears reduce and apply their epilogue themselves) T must equal the
- * token-row count of the last xb_forward and the hook OVERWRITES the KV entries that call wrote. */
+ */
 int xb_bench_linears(xb_engine* e, int T, int iters, int* n_launches, void* stream);
 
 /* Measurement hook: the decode attention kernel(s) of this shard's first layer
@@ -219,6 +218,13 @@ int xb_bench_linears(xb_engine* e, int T, int iters, int* n_launches, void* stre
  * the last xb_forward call, `iters` times back to back, with `n_splits` kv splits (0 = the
  * engine's choice, returned in *splits_used). */
 int xb_bench_attention(xb_engine* e, int n_seqs, int max_ctx, int n_splits, int iters, int* splits_used, void* stream);
+
+/* Measurement hook: per-block timeline of the Linear launches (llm_utils.py:513-522 / general_mha.py:83-102 sites) of
+ * an engine created with XB_GEMM_TS=1 (eager launches; every Linear then records %globaltimer stamps per block:
+ * entry, weight prefetch issued, dependency resolved, first / last MMA, epilogue start / end, exit).  Copies
+ * [n_launches][blocks][16] uint64 nanosecond stamps recorded since the previous call into host_out (may be NULL to
+ * just reset) and starts a new recording. */
+int xb_debug_timeline(xb_engine* e, unsigned long long* host_out, size_t cap_u64, int* n_launches, int* blocks);
 
 /* Allocation-free Linear (no counterpart in the reference, which never manages device memory
  * itself): y[T,N] (fp32) = x[T,K] * w[N,K]^T on device buffers through the engine's split-K

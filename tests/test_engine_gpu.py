@@ -382,11 +382,11 @@ def test_sampler_edge_cases(built_lib):
   ("qwen-2.5-tiny", None),                   # head_dim 64, half-split pairs + q/k/v bias
   ("qwen-2.5-hd128", dict(hidden=512, heads=4, kv=2, inter=1024, layers=3, vocab=1536)),   # half-split pairs 64 lanes apart
 ])
-def test_fused_decode_reduction_is_bit_identical(built_lib, mid, hf_override, monkeypatch):
-  """Decode Linears: the block that completes a 128-feature tile last sums the split-K planes
-  and applies the q/k/v (bias, RoPE, KV append) or SiLU*up epilogue itself (xb_gemm.cuh
-  skinny_finish).  Must equal the separate reduce kernels (XB_FUSE_EPI=0) bit for bit --
-  same plane order, same rounding points -- over ragged batches, several steps, graph replays."""
+def test_bulk_store_epilogue_is_bit_identical(built_lib, mid, hf_override, monkeypatch):
+  """Decode Linears: the last work unit of every block leaves through shared memory + bulk stores
+  (xb_gemm.cuh, the block's tail) instead of per-token strided stores (XB_BULK_EPI=0).  Same values in the
+  same places: identical logits over ragged batches, 7 / 33 / 99 token rows (BN 16 / 64 / 128 plans), several
+  steps, graph replays; interleaved and half-split RoPE models."""
   from oracle import torch_oracle as O
   from xotorch_support_jetson_b200 import models
   from xotorch_support_jetson_b200.shard import Shard
@@ -398,48 +398,45 @@ def test_fused_decode_reduction_is_bit_identical(built_lib, mid, hf_override, mo
     o = hf_override
     hf_cfg = models._qwen(o["hidden"], o["heads"], o["kv"], o["inter"], o["layers"], vocab=o["vocab"], max_pos=4096)
   cfg = O.model_config_from_hf(hf_cfg)
-  assert 128 % cfg["head_dim"] == 0
   state = random_hf_state(hf_cfg, seed=3, std=0.05, norm_jitter=0.1)
   nl = cfg["num_layers"]
+  lens = [5, 33, 17, 64, 1, 48, 9]
 
-  def make(fuse):
-    monkeypatch.setenv("XB_FUSE_EPI", "1" if fuse else "0")
+  def run(bulk):
+    monkeypatch.setenv("XB_BULK_EPI", "1" if bulk else "0")     # read when a Linear is planned (first use of a shape)
     st = StageRuntime(Shard(mid, 0, nl - 1, nl), cfg, device=0, max_batch_tokens=128, max_seqs=40, max_tokens_per_seq=96, page_tokens=16)
     st.load_state(state)
-    return st
-
-  a, b = make(True), make(False)
-  g = torch.Generator().manual_seed(7)
-  lens = [5, 33, 17, 64, 1, 48, 9]
-  outs = {0: [], 1: []}
-  with torch.cuda.stream(torch.cuda.Stream()):
-    for k, st in enumerate((a, b)):
-      g.manual_seed(7)
+    g = torch.Generator().manual_seed(7)
+    outs = []
+    with torch.cuda.stream(torch.cuda.Stream()):
       for i, L in enumerate(lens):
         p = torch.randint(1, cfg["vocab_size"], (L,), generator=g).to(torch.int32).cuda()
-        outs[k].append(st.forward([i], [L], [0], tokens=p))
+        outs.append(st.forward([i], [L], [0], tokens=p))
       pos = list(lens)
       # ragged decode, 7 rows (BN=16 plan), 5 steps (step 2 onwards replays the graph)
-      tok = torch.stack([o.argmax(-1).to(torch.int32).reshape(()) for o in outs[k][:len(lens)]])
+      tok = torch.stack([o.argmax(-1).to(torch.int32).reshape(()) for o in outs[:len(lens)]])
       for step in range(5):
         lg = st.forward(list(range(len(lens))), [1] * len(lens), pos, tokens=tok)
-        outs[k].append(lg)
+        outs.append(lg)
         tok = lg.argmax(-1).to(torch.int32)
         pos = [x + 1 for x in pos]
-      # a 33-row decode batch (BN=64 plan) and a 100-row mixed call that still takes the T <= 128 path
+      # a 33-row decode batch (BN=64 plan) and a 99-row mixed call that still takes the T <= 128 path
       for i in range(33):
         st.release_slot(i)
       p = torch.randint(1, cfg["vocab_size"], (33 * 3,), generator=g).to(torch.int32).cuda()
-      outs[k].append(st.forward(list(range(33)), [3] * 33, [0] * 33, tokens=p))
-      tok = outs[k][-1].argmax(-1).to(torch.int32)
-      outs[k].append(st.forward(list(range(33)), [1] * 33, [3] * 33, tokens=tok))
-  torch.cuda.synchronize()
-  assert len(outs[0]) == len(outs[1])
-  for i, (x, y) in enumerate(zip(outs[0], outs[1])):
+      outs.append(st.forward(list(range(33)), [3] * 33, [0] * 33, tokens=p))
+      tok = outs[-1].argmax(-1).to(torch.int32)
+      outs.append(st.forward(list(range(33)), [1] * 33, [3] * 33, tokens=tok))
+    torch.cuda.synchronize()
+    res = [o.cpu() for o in outs]
+    st.close()
+    return res
+
+  x_all, y_all = run(True), run(False)
+  assert len(x_all) == len(y_all)
+  for i, (x, y) in enumerate(zip(x_all, y_all)):
     assert torch.isfinite(x).all()
-    assert torch.equal(x, y), f"output {i}: fused and separate reductions differ by {float((x - y).abs().max())}"
-  a.close()
-  b.close()
+    assert torch.equal(x, y), f"output {i}: bulk-store and per-token epilogues differ by {float((x - y).abs().max())}"
 
 
 @pytest.mark.parametrize("V", [128256, 152064, 50257, 1000])

@@ -13,7 +13,7 @@ SYMBOLS = (
   "xb_load_safetensors", "xb_weights_missing", "xb_safetensors_list",
   "xb_kv_reserve", "xb_kv_release_slot", "xb_kv_slot_len", "xb_forward", "xb_forward_host_logits", "xb_sample",
   "xb_handoff_create", "xb_handoff_connect", "xb_forward_handoff", "xb_handoff_connect_local", "xb_handoff_clear_error",
-  "xb_get_counters", "xb_debug_linear", "xb_bench_linears", "xb_bench_attention", "xb_linear_noalloc",
+  "xb_get_counters", "xb_debug_linear", "xb_bench_linears", "xb_bench_attention", "xb_linear_noalloc", "xb_debug_timeline",
 )
 
 # weight kinds (enum in xb200.h)
@@ -102,6 +102,7 @@ def load():
                                   C.c_int, C.c_int, C.c_void_p]
   lib.xb_linear_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p]
   lib.xb_bench_attention.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_void_p]
+  lib.xb_debug_timeline.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int)]
   lib.xb_bench_linears.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_void_p]
   for name in SYMBOLS:
     fn = getattr(lib, name)

@@ -89,11 +89,11 @@ struct xb_engine {
   size_t gemm_out_bytes = 0;
   float *o_part = nullptr, *ml_part = nullptr;
   int max_attn_splits = 32;
-  // decode Linears with a fused reduction (xb_gemm.cuh skinny_finish): arrival counters per 128-feature tile
-  int* tile_ctr = nullptr;
   int fuse_qkv = 1;       // XB_FUSE_QKV=0: q/k/v finalize as its own kernel instead of the decode attention's prologue
   int attn_cluster = 1;   // XB_ATTN_CLUSTER=0: kv splits merged by xb_attn_combine2_kernel instead of a cluster + DSMEM; 16: clusters of up to 16
-  int fuse_epi = 0;       // XB_FUSE_EPI=1: reduce + q/k/v / SiLU epilogue inside the decode Linear (measured slower, see xb_gemm.cuh)
+  // timeline instrumentation (XB_GEMM_TS=1; eager launches only): globaltimer stamps of every Linear launch
+  unsigned long long* ts_buf = nullptr;
+  int ts_cap = 0, ts_next = 0, ts_blocks = 160;
   int meta_T = 0;         // token rows the device metadata currently describes
   std::map<long long, GemmPlan> plans;
   xb_counters c{};
@@ -276,11 +276,6 @@ extern "C" int xb_engine_create(const xb_model_desc* desc, int device, xb_engine
   e->gemm_out_bytes = T * maxN * 2;
   if (e->gemm_out_bytes < ((size_t)64 << 20)) e->gemm_out_bytes = (size_t)64 << 20;
   XB_TRY(dmalloc(&e->gemm_out, e->gemm_out_bytes));
-  {
-    const size_t n_ctr = (maxN + 127) / 128;
-    XB_TRY(dmalloc((void**)&e->tile_ctr, n_ctr * sizeof(int)));
-    XB_CUDA(cudaMemset(e->tile_ctr, 0, n_ctr * sizeof(int)));
-  }
   // kv splits > 1 are only used while T * n_kv_heads < 2 * num_sms (see xb_forward)
   const size_t Tsplit = T < (size_t)2 * e->num_sms ? T : (size_t)2 * e->num_sms;
   XB_TRY(dmalloc((void**)&e->o_part, Tsplit * d.n_heads * e->max_attn_splits * d.head_dim * sizeof(float)));
@@ -307,8 +302,13 @@ extern "C" int xb_engine_create(const xb_model_desc* desc, int device, xb_engine
     if (g != nullptr && g[0] == '0') e->use_graphs = 0;
     g = getenv("XB_PDL");
     if (g != nullptr && g[0] == '0') e->use_pdl = 0;
-    g = getenv("XB_FUSE_EPI");
-    if (g != nullptr) e->fuse_epi = g[0] == '1';
+    g = getenv("XB_GEMM_TS");
+    if (g != nullptr && g[0] == '1') {
+      e->ts_cap = 1024;
+      e->use_graphs = 0;
+      XB_TRY(dmalloc((void**)&e->ts_buf, (size_t)e->ts_cap * e->ts_blocks * XB_TS_SLOTS * 8));
+      XB_CUDA(cudaMemset(e->ts_buf, 0, (size_t)e->ts_cap * e->ts_blocks * XB_TS_SLOTS * 8));
+    }
     g = getenv("XB_FUSE_QKV");
     if (g != nullptr) e->fuse_qkv = g[0] != '0';
     g = getenv("XB_ATTN_CLUSTER");
@@ -344,7 +344,8 @@ extern "C" int xb_engine_destroy(xb_engine* e) {
   for (auto& kv : e->graphs)
     if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
   cudaFree(e->h); cudaFree(e->hn); cudaFree(e->q); cudaFree(e->attn); cudaFree(e->act);
-  cudaFree(e->last_rows); cudaFree(e->gemm_out); cudaFree(e->tile_ctr); cudaFree(e->o_part); cudaFree(e->ml_part);
+  cudaFree(e->ts_buf);
+  cudaFree(e->last_rows); cudaFree(e->gemm_out); cudaFree(e->o_part); cudaFree(e->ml_part);
   delete e;
   return 0;
 }
@@ -692,6 +693,17 @@ extern "C" int xb_kv_slot_len(xb_engine* e, int slot, int* len) {
 }
 
 // ----------------------------------------------------------------------------- forward
+// every Linear of the engine goes through here (timeline instrumentation hooks in when enabled)
+static int run_gemm(xb_engine* e, const GemmPlan& gp, cudaStream_t st) {
+  if (e->ts_buf != nullptr && e->ts_next < e->ts_cap && gp.grid <= e->ts_blocks) {
+    GemmPlan p = gp;
+    p.args.ts = e->ts_buf + (size_t)e->ts_next * e->ts_blocks * XB_TS_SLOTS;
+    ++e->ts_next;
+    return xb_gemm_run(p, st, e->use_pdl);
+  }
+  return xb_gemm_run(gp, st, e->use_pdl);
+}
+
 static int get_plan(xb_engine* e, int site, int layer, const bf16* x, long long ldx, const bf16* w, int T, int N, int K,
                     void* out, long long ld_out, const bf16* bias, int round_bf16, const GemmPlan** pp) {
   const long long key = (((long long)site * 4096 + layer) << 32) | (unsigned)T;
@@ -699,14 +711,11 @@ static int get_plan(xb_engine* e, int site, int layer, const bf16* x, long long 
   if (it == e->plans.end()) {
     GemmPlan p;
     XB_TRY(xb_gemm_plan(&p, x, ldx, w, 1, T, N, K, out, ld_out, bias, round_bf16, e->num_sms, 0));
-    const bool fuse = e->fuse_epi && p.args.mode == XB_GEMM_SKINNY && 128 % e->d.head_dim == 0 && N % 128 == 0;
-    if ((p.args.mode == XB_GEMM_WIDE || fuse) && site == SITE_QKV) {
-      // bias + RoPE + q store + paged-KV append happen in the GEMM epilogue (decode: in the block
-      // that completes a tile last)
+    if (p.args.mode == XB_GEMM_WIDE && site == SITE_QKV) {
+      // prefill: bias + RoPE + q store + paged-KV append happen in the GEMM epilogue
       const xb_model_desc& d = e->d;
       GemmArgs& g = p.args;
       g.epi = XB_EPI_QKV;
-      g.tile_ctr = e->tile_ctr;
       g.rope = e->rope;
       g.q_out = e->q;
       g.k_pool = e->L[layer].k_pool;
@@ -726,11 +735,6 @@ static int get_plan(xb_engine* e, int site, int layer, const bf16* x, long long 
       p.args.epi = XB_EPI_SILU;
       p.args.out = e->act;
       p.args.ld_out = e->d.inter_dim;
-    } else if (fuse && site == SITE_GU) {
-      p.args.epi = XB_EPI_SILU;
-      p.args.tile_ctr = e->tile_ctr;
-      p.args.fin_out = e->act;
-      p.args.fin_ld = e->d.inter_dim;
     }
     if (p.args.mode == XB_GEMM_SKINNY && out == e->gemm_out) {
       const size_t need = (size_t)p.split.splits * T * N * 4;
@@ -871,9 +875,9 @@ static int run_head(xb_engine* e, int n_seqs, cudaStream_t st, float* host_logit
   if (host_logits != nullptr) {
     GemmPlan p = *gp;
     p.args.out2 = host_logits;
-    XB_TRY(xb_gemm_run(p, st, e->use_pdl));
+    XB_TRY(run_gemm(e, p, st));
   } else {
-    XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
+    XB_TRY(run_gemm(e, *gp, st));
   }
   LAUNCH_COUNT(e);
   return 0;
@@ -920,7 +924,7 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
     if (do_attn) {
     // q/k/v projections as one GEMM (general_mha.py:83-97)
     XB_TRY(get_plan(e, SITE_QKV, l, e->hn, D, w.wqkv, T, e->NQKV, D, e->gemm_out, e->NQKV, w.bqkv, 0, &gp));
-    XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
+    XB_TRY(run_gemm(e, *gp, st));
     LAUNCH_COUNT(e);
     QkvFin fin{};
     const QkvFin* finp = nullptr;
@@ -940,14 +944,14 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
     else XB_TRY(launch_attn<64>(e, w, m, T, n_splits, n_tiles, st, finp));
     // output projection + residual + mlp_norm
     XB_TRY(get_plan(e, SITE_O, l, e->attn, e->NQ, w.wo, T, D, e->NQ, e->gemm_out, D, nullptr, 0, &gp));
-    XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
+    XB_TRY(run_gemm(e, *gp, st));
     LAUNCH_COUNT(e);
     if (do_mlp) XB_TRY(launch_resid_norm(e, gp, T, w.mlp_norm, st));
     }
     if (do_mlp) {
     // gate/up as one GEMM, SiLU*up, down projection (llm_utils.py:513-522)
     XB_TRY(get_plan(e, SITE_GU, l, e->hn, D, w.wgu, T, 2 * I, D, e->gemm_out, 2 * I, nullptr, 0, &gp));
-    XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
+    XB_TRY(run_gemm(e, *gp, st));
     LAUNCH_COUNT(e);
     if (gp->args.mode == XB_GEMM_SKINNY && gp->args.epi == XB_EPI_PLAIN) {
       const long long n = (long long)T * (I / 4);
@@ -955,7 +959,7 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
                       gp->split, (long long)T * 2 * I, e->act, T, I));
     }
     XB_TRY(get_plan(e, SITE_DOWN, l, e->act, I, w.wdown, T, D, I, e->gemm_out, D, nullptr, 0, &gp));
-    XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
+    XB_TRY(run_gemm(e, *gp, st));
     LAUNCH_COUNT(e);
     }
     // `gp` is the block's last Linear (down, or the output projection of a stage that stops after attention)
@@ -1252,9 +1256,6 @@ extern "C" int xb_handoff_connect(xb_engine* e, const void* next_landing_handle,
 // the call with CUDA events; the launch count is returned in *n_launches.
 extern "C" int xb_bench_linears(xb_engine* e, int T, int iters, int* n_launches, void* stream) {
   XB_CHECK(e != nullptr && T > 0 && T <= e->d.max_batch_tokens && iters > 0, "bad argument");
-  // with XB_FUSE_EPI=1 the q/k/v epilogue stores through the batch metadata of the last forward
-  XB_CHECK(!e->fuse_epi || T == e->meta_T, "xb_bench_linears: T=%d must equal the row count of the last xb_forward (%d)", T,
-           e->meta_T);
   const xb_model_desc& d = e->d;
   cudaStream_t st = (cudaStream_t)stream;
   XB_CUDA(cudaSetDevice(e->device));
@@ -1271,22 +1272,22 @@ extern "C" int xb_bench_linears(xb_engine* e, int T, int iters, int* n_launches,
       const bool has_attn = w.wqkv != nullptr, has_mlp = w.wgu != nullptr;
       if (has_attn && (only < 0 || only == SITE_QKV)) {
         XB_TRY(get_plan(e, SITE_QKV, l, e->hn, D, w.wqkv, T, e->NQKV, D, e->gemm_out, e->NQKV, w.bqkv, 0, &gp));
-        XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
+        XB_TRY(run_gemm(e, *gp, st));
         ++n;
       }
       if (has_attn && (only < 0 || only == SITE_O)) {
         XB_TRY(get_plan(e, SITE_O, l, e->attn, e->NQ, w.wo, T, D, e->NQ, e->gemm_out, D, nullptr, 0, &gp));
-        XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
+        XB_TRY(run_gemm(e, *gp, st));
         ++n;
       }
       if (has_mlp && (only < 0 || only == SITE_GU)) {
         XB_TRY(get_plan(e, SITE_GU, l, e->hn, D, w.wgu, T, 2 * I, D, e->gemm_out, 2 * I, nullptr, 0, &gp));
-        XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
+        XB_TRY(run_gemm(e, *gp, st));
         ++n;
       }
       if (has_mlp && (only < 0 || only == SITE_DOWN)) {
         XB_TRY(get_plan(e, SITE_DOWN, l, e->act, I, w.wdown, T, D, I, e->gemm_out, D, nullptr, 0, &gp));
-        XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
+        XB_TRY(run_gemm(e, *gp, st));
         ++n;
       }
     }
@@ -1294,7 +1295,7 @@ extern "C" int xb_bench_linears(xb_engine* e, int T, int iters, int* n_launches,
       const bf16* head = e->lm_head;
       const GemmPlan* gp;
       XB_TRY(get_plan(e, SITE_HEAD, 0, e->last_rows, D, head, T, d.vocab, D, e->logits, d.vocab, nullptr, 1, &gp));
-      XB_TRY(xb_gemm_run(*gp, st, e->use_pdl));
+      XB_TRY(run_gemm(e, *gp, st));
       n += 1;
     }
   }
@@ -1366,6 +1367,27 @@ extern "C" int xb_sample(xb_engine* e, const float* logits, int n, float temp, i
   }
   XB_CUDA(cudaGetLastError());
   LAUNCH_COUNT(e);
+  return 0;
+}
+
+// Timeline instrumentation read-out (engine created with XB_GEMM_TS=1): copies the stamps of the Linear launches
+// recorded since the last call -- [n_launches][blocks][XB_TS_SLOTS] nanosecond globaltimer values, 0 = not reached -- and
+// starts a new recording.  Synchronises the device.
+extern "C" int xb_debug_timeline(xb_engine* e, unsigned long long* host_out, size_t cap_u64, int* n_launches, int* blocks) {
+  XB_CHECK(e != nullptr && n_launches != nullptr && blocks != nullptr, "null argument");
+  XB_CHECK(e->ts_buf != nullptr, "create the engine with XB_GEMM_TS=1 to record a timeline");
+  XB_CUDA(cudaSetDevice(e->device));
+  XB_CUDA(cudaDeviceSynchronize());
+  const size_t per = (size_t)e->ts_blocks * XB_TS_SLOTS;
+  int n = e->ts_next;
+  if (host_out != nullptr) {
+    if ((size_t)n * per > cap_u64) n = (int)(cap_u64 / per);
+    XB_CUDA(cudaMemcpy(host_out, e->ts_buf, (size_t)n * per * 8, cudaMemcpyDeviceToHost));
+  }
+  XB_CUDA(cudaMemset(e->ts_buf, 0, (size_t)e->ts_cap * per * 8));
+  e->ts_next = 0;
+  *n_launches = n;
+  *blocks = e->ts_blocks;
   return 0;
 }
 

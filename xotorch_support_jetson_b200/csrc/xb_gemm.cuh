@@ -52,13 +52,17 @@ struct GemmArgs {
   bf16 *q_out, *k_pool, *v_pool;
   const int *tok_seq, *tok_pos, *seq_slot, *page_table;
   int max_pages, page_tokens, n_heads, n_kv_heads, head_dim, rope_kind;
-  // SKINNY with epi != PLAIN: the block that completes a 128-feature tile LAST (tile_ctr) sums the
-  // partial planes in plane order and applies the epilogue itself -- no separate reduce kernel
-  int* tile_ctr;           // [a_tiles], zero between launches (the last arriver resets its entry)
-  void* fin_out;           // XB_EPI_SILU: bf16 act[t][fin_ld]
-  long long fin_ld;
+  int bulk_epi;            // SKINNY: the block's LAST unit leaves through shared memory + bulk stores (see the epilogue)
   float* out2;             // SKINNY: second copy of the result (same layout as `out`), e.g. pinned host memory
+  unsigned long long* ts;  // timeline instrumentation (XB_GEMM_TS=1): [gridDim.x][XB_TS_SLOTS] globaltimer stamps, else nullptr
 };
+// stamps: 0 block entry, 1 producer: first stages issued (before the dependency wait), 2 producer: dependency resolved,
+// 3 first MMA issued, 4 last MMA committed, 5 (not a time) %smid of the block, 6 epilogue: last unit stored, 7 block exit,
+// 8 epilogue: accumulator of the last unit complete, 9 producer: last load issued, 10 MMA thread: last stage landed
+#define XB_TS(g, slot)                                                                   \
+  do {                                                                                   \
+    if ((g).ts != nullptr) (g).ts[(size_t)blockIdx.x * XB_TS_SLOTS + (slot)] = xb_gtimer(); \
+  } while (0)
 enum { XB_EPI_PLAIN = 0, XB_EPI_QKV = 1, XB_EPI_SILU = 2 };
 
 // TMA coordinates (innermost, row) of the [128 x 64] weight box holding rows 128*wt.. of k-block kb
@@ -234,113 +238,10 @@ __device__ __forceinline__ void epi_wide_silu(const GemmArgs& g, uint32_t t_addr
   }
 }
 
-// ---- SKINNY fused reduction (XB_FUSE_EPI=1, off by default): runs in the four epilogue warps after the
-// unit's partial plane is stored.  Measured on B200, Llama-3.1-8B: bit-identical to the separate
-// reduce kernels but SLOWER -- decode bs=32 6.16 ms/step against 4.95 ms, Linear kernel 0.53 of the
-// HBM peak against 0.81, bs=1 285.8 against 287.7 tok/s: the device-wide fence + atomic + two
-// block barriers per unit cost as much as the kernel boundary they replace (which programmatic
-// dependent launch already overlaps), and the 128 epilogue threads of ONE block then do a reduction
-// that the separate kernel spreads over every SM; on a block's last unit all of it is tail.
-// thread = output feature n = ta*128 + row_in_tile.  Sums are taken over ALL planes of the tile in
-// plane order (its own included, re-read from L2), so the result does not depend on which block
-// happens to arrive last and equals what xb_qkv_finalize_kernel / xb_silu_mul_kernel compute.
-__device__ __forceinline__ void skinny_sum8(const float* part, long long plane_stride, int nseg, long long ld, int n, int t0,
-                                            int T, float* acc) {
-#pragma unroll
-  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
-  for (int s = 0; s < nseg; ++s) {
-    float v[8];
-    const float* p = part + s * plane_stride + (long long)t0 * ld + n;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] = (t0 + j < T) ? __ldcg(p + j * ld) : 0.f;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] += v[j];
-  }
-}
-
-__device__ __forceinline__ void skinny_finish(const GemmArgs& g, int ta, int row_in_tile, int lane, volatile uint32_t* flag) {
-  const int nseg = xb_n_segments(SplitInfo{g.k_blocks, g.sk_q, g.splits}, ta * 128);
-  __threadfence();                                   // this thread's plane stores are visible device-wide
-  asm volatile("bar.sync 1, 128;" ::: "memory");     // ... and so are those of the other 127 epilogue threads
-  if (row_in_tile == 0) {
-    const int old = atomicAdd(g.tile_ctr + ta, 1);
-    const bool last = old == nseg - 1;
-    if (last) g.tile_ctr[ta] = 0;                    // every arrival is in: ready for the next launch
-    *flag = last ? 1u : 0u;
-  }
-  asm volatile("bar.sync 1, 128;" ::: "memory");
-  if (*flag == 0u) return;
-  __threadfence();
-  const float* part = reinterpret_cast<const float*>(g.out);
-  const int T = g.b_rows;
-  const long long ld = g.ld_out, ps = (long long)T * ld;
-  const int n = ta * 128 + row_in_tile;
-  const bool valid = n < g.a_rows;
-  const int nn = valid ? n : 0;
-  if (g.epi == XB_EPI_SILU) {
-    // lanes 0..15 hold gate, 16..31 up of the same 16 features (interleave of xb_tile_weight_kernel)
-    bf16* act = reinterpret_cast<bf16*>(g.fin_out);
-    const int feat = ta * 64 + (row_in_tile >> 5) * 16 + (lane & 15);
-#pragma unroll 1
-    for (int t0 = 0; t0 < T; t0 += 8) {
-      float acc[8];
-      skinny_sum8(part, ps, valid ? nseg : 0, ld, nn, t0, T, acc);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float x = rbf(acc[j]);
-        const float o = __shfl_xor_sync(0xffffffffu, x, 16);
-        if (lane < 16 && valid && t0 + j < T)
-          act[(long long)(t0 + j) * g.fin_ld + feat] = f2bf(rbf(x / (1.0f + expf(-x))) * o);
-      }
-    }
-  } else {
-    const int hd = g.head_dim, half = hd >> 1, H = g.n_heads, KV = g.n_kv_heads;
-    const int head = nn / hd, e = nn % hd;
-    const bool rot = head < H + KV;
-    const bool split_pairs = g.rope_kind != 0 && rot;   // partner hd/2 features away: other warp, so re-read it
-    const int np = split_pairs ? (e < half ? nn + half : nn - half) : nn;
-    const float bias_n = g.bias != nullptr ? bf2f(g.bias[nn]) : 0.f;
-    const float bias_p = g.bias != nullptr ? bf2f(g.bias[np]) : 0.f;
-#pragma unroll 1
-    for (int t0 = 0; t0 < T; t0 += 8) {
-      float own[8], par[8];
-      skinny_sum8(part, ps, valid ? nseg : 0, ld, nn, t0, T, own);
-      if (split_pairs) skinny_sum8(part, ps, valid ? nseg : 0, ld, np, t0, T, par);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const int t = t0 + j;
-        const bool ok = valid && t < T;
-        float x = own[j];
-        if (g.bias != nullptr) x += bias_n;
-        x = rbf(x);
-        float y = __shfl_xor_sync(0xffffffffu, x, 1);   // interleaved pairs: neighbour lane
-        float r = x;
-        const int pos = ok ? g.tok_pos[t] : 0;
-        if (rot && ok) {
-          const float* rope_row = g.rope + (long long)pos * half * 2;
-          if (g.rope_kind == 0) {
-            const float2 cs = *reinterpret_cast<const float2*>(rope_row + (e >> 1) * 2);
-            r = (e & 1) == 0 ? __fsub_rn(__fmul_rn(x, cs.x), __fmul_rn(y, cs.y))
-                             : __fadd_rn(__fmul_rn(x, cs.x), __fmul_rn(y, cs.y));
-          } else {
-            y = par[j];
-            if (g.bias != nullptr) y += bias_p;
-            y = rbf(y);
-            const float2 cs = *reinterpret_cast<const float2*>(rope_row + (e % half) * 2);
-            const float cc = rbf(cs.x), sn = rbf(cs.y);
-            r = e < half ? __fadd_rn(rbf(__fmul_rn(x, cc)), rbf(__fmul_rn(-y, sn)))
-                         : __fadd_rn(rbf(__fmul_rn(x, cc)), rbf(__fmul_rn(y, sn)));
-          }
-        }
-        if (ok) *epi_qkv_dst(g, t, pos, head, e) = f2bf(r);
-      }
-    }
-  }
-}
-
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(192, 1)
-xb_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmArgs g) {
+xb_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                       const __grid_constant__ CUtensorMap tmC, GemmArgs g) {
   using Cfg = GemmCfg<BN, STAGES>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -351,14 +252,15 @@ xb_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   uint64_t* tfull_bar = empty_bar + STAGES;
   uint64_t* tempty_bar = tfull_bar + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
-  volatile uint32_t* last_flag = tmem_slot + 1;   // skinny_finish: "this block completed the tile"
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
   if (warp == 0 && lane == 0) {
+    XB_TS(g, 0);
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    if (g.bulk_epi) tma_prefetch_desc(&tmC);
   }
   if (warp == 1) {
     if (lane == 0) {
@@ -415,7 +317,9 @@ xb_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               }
             }
           }
+          XB_TS(g, 1);
           pdl_wait();
+          XB_TS(g, 2);
           waited = true;
           pre = npre;
         }
@@ -451,6 +355,7 @@ xb_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
+      XB_TS(g, 9);
       if (!waited) pdl_wait();
     }
   } else if (warp == 1) {
@@ -459,6 +364,7 @@ xb_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       constexpr uint32_t idesc = umma_idesc_bf16(BN);
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
+      bool first_mma = true;
       while (walk.next(g, wu)) {
         const int kb0 = wu.kb0, kb1 = wu.kb1;
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);   // epilogue has drained this accumulator
@@ -466,6 +372,8 @@ xb_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&full_bar[stage], phase);         // TMA bytes have landed
+          if (first_mma) { XB_TS(g, 3); first_mma = false; }
+          if (kb + 1 == kb1) XB_TS(g, 10);
           tc_fence_after();
           const uint32_t a_addr = smem_u32(sA + stage * Cfg::A_BYTES);
           const uint32_t b_addr = smem_u32(sB + stage * Cfg::B_BYTES);
@@ -480,21 +388,68 @@ xb_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         tc_commit(&tfull_bar[acc]);                   // accumulator complete -> epilogue
         if (++acc == Cfg::ACC_STAGES) { acc = 0; acc_phase ^= 1; }
       }
+      XB_TS(g, 4);
     }
   } else {
     // ===================== epilogue warps 2..5: TMEM -> registers -> global =====================
     const int quad = warp & 3;                        // TMEM lane quadrant this warp may read
     const int row_in_tile = quad * 32 + lane;
     pdl_wait();                                       // `out` may still be read by the upstream grid
+    if (warp == 2 && lane == 0 && g.ts != nullptr) {   // slot 5: the SM this block runs on
+      unsigned int smid;
+      asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+      g.ts[(size_t)blockIdx.x * XB_TS_SLOTS + 5] = smid;
+    }
     int acc = 0;
     uint32_t acc_phase = 0;
     while (walk.next(g, wu)) {
       const int s = wu.slot, ta = wu.ta, tb = wu.tb;
       mbar_wait(&tfull_bar[acc], acc_phase);
+      if (warp == 2 && lane == 0) XB_TS(g, 8);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN);
       const int arow = ta * 128 + row_in_tile;
-      if (BN == 256 && g.mode == XB_GEMM_WIDE && g.epi == XB_EPI_QKV) {
+      bool last_unit = false;
+      if (BN <= 128 && g.mode == XB_GEMM_SKINNY && g.bulk_epi && g.out2 == nullptr) {
+        UnitWalker peek = walk;
+        GemmUnit nu;
+        last_unit = !peek.next(g, nu);
+      }
+      if (BN <= 128 && last_unit) {
+        // The block's LAST unit is pure tail: nothing overlaps its epilogue (earlier units drain while the next
+        // unit's MMAs run).  Measured on B200 with per-block timestamps (profiles/gemm_timeline.py): the per-token
+        // strided fp32 stores of the general path take 2.4 us per unit at 32 token rows -- more than the whole gap
+        // the weight prefetch of the next Linear can cover (32 separate 512-byte bulk copies, one per lane, were no
+        // faster: ~64 ns of issue time each).  All loads of the block have landed and all its MMAs have retired by
+        // now, so the operand ring is free: the [tokens x 128 features] block is transposed through it and leaves
+        // as ONE 2-D TMA store (a [T x 128] fp32 box of the partial plane; columns past N are clipped).
+        float* stg = reinterpret_cast<float*>(sA);          // [BN][128] fp32 <= STAGES * 16 KB
+#pragma unroll 1
+        for (int c = 0; c < BN; c += 16) {
+          uint32_t v[16];
+          tmem_ld16(t_addr + c, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            float x = __uint_as_float(v[j]);
+            if (g.round_bf16) x = rbf(x);
+            stg[(c + j) * 128 + row_in_tile] = x;
+          }
+        }
+        if (warp == 2 && lane == 0) XB_TS(g, 11);
+        tc_fence_before();
+        fence_proxy_async();                                // generic-proxy writes -> visible to the TMA engine
+        asm volatile("bar.sync 2, 128;" ::: "memory");
+        if (warp == 2 && lane == 0) {
+          XB_TS(g, 12);
+          asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                       ::"l"(&tmC), "r"(smem_u32(stg)), "r"(ta * 128), "r"(s * g.b_rows) : "memory");
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          XB_TS(g, 13);
+          asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // shared memory may be released at exit
+          XB_TS(g, 14);
+        }
+      } else if (BN == 256 && g.mode == XB_GEMM_WIDE && g.epi == XB_EPI_QKV) {
         epi_wide_qkv<BN>(g, t_addr, arow, tb);
       } else if (BN == 256 && g.mode == XB_GEMM_WIDE && g.epi == XB_EPI_SILU) {
         epi_wide_silu<BN>(g, t_addr, arow, tb);
@@ -553,8 +508,8 @@ xb_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       if (lane == 0) mbar_arrive(&tempty_bar[acc]);
       if (++acc == Cfg::ACC_STAGES) { acc = 0; acc_phase ^= 1; }
       // the accumulator is released: the next unit's MMAs run while the tile is reduced
-      if (BN <= 128 && g.mode == XB_GEMM_SKINNY && g.epi != XB_EPI_PLAIN) skinny_finish(g, ta, row_in_tile, lane, last_flag);
     }
+    if (warp == 2 && lane == 0) XB_TS(g, 6);
   }
 
   tc_fence_before();
@@ -563,6 +518,7 @@ xb_gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     tc_fence_after();
     tmem_dealloc(tmem_base, Cfg::TM_COLS);
   }
+  if (threadIdx.x == 0) XB_TS(g, 7);
 }
 
 // ----------------------------------------------------------------------------- CUDA-core checker
@@ -645,9 +601,25 @@ static int xb_make_tmap(CUtensorMap* m, const void* ptr, long long rows, long lo
   return 0;
 }
 
+// 2-D fp32 row-major [rows, cols] tensor, box = [box_rows, 128 cols], no swizzle (TMA store of partial planes)
+static int xb_make_tmap_f32(CUtensorMap* m, const void* ptr, long long rows, long long cols, long long ld_elems, int box_rows) {
+  PFN_encodeTiled fn = xb_get_encode_fn();
+  XB_CHECK(fn != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)ld_elems * 4};
+  cuuint32_t box[2] = {128, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  XB_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (fp32 store map) failed with CUresult %d (rows=%lld cols=%lld box_rows=%d)",
+           (int)r, rows, cols, box_rows);
+  return 0;
+}
+
 template <int BN, int STAGES>
-static int xb_gemm_launch_t(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, int grid, cudaStream_t st,
-                            int pdl) {
+static int xb_gemm_launch_t(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmArgs& g, int grid,
+                            cudaStream_t st, int pdl) {
   using Cfg = GemmCfg<BN, STAGES>;
   {
     // per device: the attribute does not carry over to another GPU of the same process
@@ -670,13 +642,14 @@ static int xb_gemm_launch_t(const CUtensorMap& tmA, const CUtensorMap& tmB, cons
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl ? 1 : 0;
-  XB_CUDA(cudaLaunchKernelEx(&cfg, xb_gemm_tcgen05_kernel<BN, STAGES>, tmA, tmB, g));
+  XB_CUDA(cudaLaunchKernelEx(&cfg, xb_gemm_tcgen05_kernel<BN, STAGES>, tmA, tmB, tmC, g));
   return 0;
 }
 
 // A planned Linear: tensor maps + unit decomposition, built once per (site, token count).
 struct GemmPlan {
   CUtensorMap tmA, tmB;
+  CUtensorMap tmC;   // SKINNY with bulk_epi: fp32 view [splits * T, N] of the partial planes (TMA store); else a copy of tmA
   GemmArgs args;
   SplitInfo split;   // how a consumer sums the fp32 partial planes (SKINNY)
   int bn;
@@ -698,10 +671,9 @@ static int xb_gemm_plan(GemmPlan* p, const bf16* x, long long ldx, const bf16* w
   g.round_bf16 = round_bf16;
   g.w_tiled = w_tiled;
   g.epi = XB_EPI_PLAIN;
-  g.tile_ctr = nullptr;
-  g.fin_out = nullptr;
-  g.fin_ld = 0;
+  g.bulk_epi = 0;
   g.out2 = nullptr;
+  g.ts = nullptr;
   const long long w_tiles = (N + 127) / 128;
   if (T <= 128) {
     const int bn = xb_pick_bn_skinny(T);
@@ -728,6 +700,7 @@ static int xb_gemm_plan(GemmPlan* p, const bf16* x, long long ldx, const bf16* w
     if (w_tiled) XB_TRY(xb_make_tmap(&p->tmA, w, w_tiles * g.k_blocks * 128, 64, 64, 128));
     else XB_TRY(xb_make_tmap(&p->tmA, w, N, K, K, 128));
     XB_TRY(xb_make_tmap(&p->tmB, x, T, K, ldx, bn));
+    p->tmC = p->tmA;
   } else {
     p->bn = 256;
     g.mode = XB_GEMM_WIDE;
@@ -750,6 +723,16 @@ static int xb_gemm_plan(GemmPlan* p, const bf16* x, long long ldx, const bf16* w
     const int units = g.a_tiles * g.b_tiles * g.splits;
     p->grid = units < num_sms ? units : num_sms;
   }
+  if (g.mode == XB_GEMM_SKINNY) {
+    // last-unit epilogue through a TMA store: 16-byte aligned base and row pitch (XB_BULK_EPI=0: per-token stores only)
+    const char* bv = getenv("XB_BULK_EPI");
+    if (!(bv != nullptr && bv[0] == '0') && ld_out % 4 == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
+      XB_TRY(xb_make_tmap_f32(&p->tmC, out, (long long)g.splits * T, N, ld_out, T));
+      g.bulk_epi = 1;
+    }
+  } else {
+    p->tmC = p->tmA;
+  }
   p->split.k_blocks = g.k_blocks;
   p->split.q = g.mode == XB_GEMM_SKINNY ? g.sk_q : 0;
   p->split.splits = g.mode == XB_GEMM_SKINNY ? g.splits : 1;
@@ -758,14 +741,14 @@ static int xb_gemm_plan(GemmPlan* p, const bf16* x, long long ldx, const bf16* w
 
 static int xb_gemm_run(const GemmPlan& p, cudaStream_t st, int pdl) {
   switch (p.bn) {
-    case 16:  return xb_gemm_launch_t<16, 5>(p.tmA, p.tmB, p.args, p.grid, st, pdl);
+    case 16:  return xb_gemm_launch_t<16, 5>(p.tmA, p.tmB, p.tmC, p.args, p.grid, st, pdl);
 #ifndef XB_G32_STAGES
 #define XB_G32_STAGES 5
 #endif
-    case 32:  return xb_gemm_launch_t<32, XB_G32_STAGES>(p.tmA, p.tmB, p.args, p.grid, st, pdl);
-    case 64:  return xb_gemm_launch_t<64, 4>(p.tmA, p.tmB, p.args, p.grid, st, pdl);
-    case 128: return xb_gemm_launch_t<128, 6>(p.tmA, p.tmB, p.args, p.grid, st, pdl);
-    case 256: return xb_gemm_launch_t<256, 4>(p.tmA, p.tmB, p.args, p.grid, st, pdl);
+    case 32:  return xb_gemm_launch_t<32, XB_G32_STAGES>(p.tmA, p.tmB, p.tmC, p.args, p.grid, st, pdl);
+    case 64:  return xb_gemm_launch_t<64, 4>(p.tmA, p.tmB, p.tmC, p.args, p.grid, st, pdl);
+    case 128: return xb_gemm_launch_t<128, 6>(p.tmA, p.tmB, p.tmC, p.args, p.grid, st, pdl);
+    case 256: return xb_gemm_launch_t<256, 4>(p.tmA, p.tmB, p.tmC, p.args, p.grid, st, pdl);
   }
   return xb_fail(1, "unsupported BN %d", p.bn);
 }

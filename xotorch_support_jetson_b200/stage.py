@@ -279,6 +279,17 @@ class StageRuntime:
                                             C.c_void_p(stream)))
     return used.value
 
+  def timeline(self):
+    """Stamps of the Linear launches since the last call (engine created with XB_GEMM_TS=1): uint64 numpy
+    array [n_launches, blocks, 16] of globaltimer nanoseconds (0 = stamp not reached)."""
+    import numpy as np
+    n, blocks = C.c_int(), C.c_int()
+    slots = 16
+    cap = 1024 * 160 * slots
+    buf = np.zeros(cap, dtype=np.uint64)
+    _cabi.check(self.lib.xb_debug_timeline(self._h, buf.ctypes.data_as(C.c_void_p), cap, C.byref(n), C.byref(blocks)))
+    return buf[: n.value * blocks.value * slots].reshape(n.value, blocks.value, slots)
+
   def release_slot(self, slot: int):
     _cabi.check(self.lib.xb_kv_release_slot(self._h, slot))
 
