@@ -18,6 +18,9 @@ says so).  What is pinned by the reference itself this way:
   and how ``curr_pos`` / the token history evolve, for a full shard, for a 2-shard ring walked
   the way ``Node`` walks it (orchestration/node.py:109-147,424-443), and for a prompt that holds
   the pad id (the padded branch, sharded_inference_engine.py:165-177).
+* ``Node`` itself (orchestration/node.py, unmodified) walking a request around rings of 1, 2 and 3 in-process
+  nodes over this package's peer handles with a scripted engine: engine call sequence, tokens published
+  through ``on_token``, stop by token cap and by eos, final bookkeeping (ref_node_trace.json).
 """
 import asyncio
 import json
@@ -276,6 +279,62 @@ def gen_engine_trace(LU, GM, SE, Shard, prompt: str, n_layers: int, splits, n_ne
           "max_generated_tokens": max_generated_tokens, "generated": out_ids, "calls": calls}
 
 
+# ----------------------------------------------------------------------------- 5: the reference's Node
+def gen_node_trace(n_nodes: int, prompt: str, n_layers: int, max_generate_tokens: int, eos_token_id: int):
+  """The reference's OWN ``Node`` (orchestration/node.py, unmodified) walking one request around a ring of
+  ``n_nodes`` in-process nodes.  Engines: the scripted engine; peers / discovery / server: this package's
+  ``NvlinkPeerHandle`` / ``BoxDiscovery`` / ``NullServer`` (they are what is being fitted to the reference's
+  plug-in points); partitioning: the reference's memory-weighted ring strategy."""
+  install_stubs()
+  cwd = os.getcwd()
+  os.chdir("/tmp")
+  try:
+    from xotorch.orchestration.node import Node
+    from xotorch.inference.shard import Shard as RefShard
+    from xotorch.topology.ring_memory_weighted_partitioning_strategy import RingMemoryWeightedPartitioningStrategy
+    from xotorch.topology.device_capabilities import DeviceCapabilities, DeviceFlops
+  finally:
+    os.chdir(cwd)
+  from oracle.scripted_engine import ScriptedEngine
+  from xotorch_support_jetson_b200.networking import BoxDiscovery, NullServer, NvlinkPeerHandle
+  log, tokens = [], []
+  ids = [f"gpu{n_nodes - 1 - i:02d}-rank{i}" for i in range(n_nodes)]
+  caps = DeviceCapabilities(model="Linux Box (NVIDIA B200)", chip="NVIDIA B200", memory=183359, flops=DeviceFlops(fp32=0, fp16=0, int8=0))
+
+  async def run():
+    nodes = [Node(ids[i], NullServer(), ScriptedEngine(ids[i], log, eos_token_id), BoxDiscovery(), None,
+                  RingMemoryWeightedPartitioningStrategy(), max_generate_tokens=max_generate_tokens) for i in range(n_nodes)]
+    for i, nd in enumerate(nodes):
+      nd.device_capabilities = caps
+      nd.discovery.handles = [NvlinkPeerHandle(nodes[j], j, caps) for j in range(n_nodes) if j != i]
+    for nd in nodes:
+      await nd.update_peers()
+    for nd in nodes:
+      await nd.collect_topology(set())
+    done = asyncio.Event()
+
+    def on_token(rid, toks, fin):
+      tokens.append({"request_id": rid, "tokens": [int(t) for t in toks], "is_finished": bool(fin)})
+      if fin:
+        done.set()
+
+    # the entry node hears about tokens through send_result from the last node (or directly when it is the last)
+    nodes[0].on_token.register("trace").on_next(on_token)
+    await nodes[0].process_prompt(RefShard("scripted", 0, 0, n_layers), prompt, "req-1")
+    await asyncio.wait_for(done.wait(), 30)
+    await asyncio.sleep(0.05)
+    shards = [nodes[i].get_current_shard(RefShard("scripted", 0, 0, n_layers)) for i in range(n_nodes)]
+    return {"buffered": {ids[i]: [int(t) for t in nodes[i].buffered_token_output.get("req-1", ([], False))[0]] for i in range(n_nodes)},
+            "finished": {ids[i]: bool(nodes[i].buffered_token_output.get("req-1", ([], False))[1]) for i in range(n_nodes)},
+            "outstanding": {ids[i]: dict(nodes[i].outstanding_requests) for i in range(n_nodes)},
+            "shards": [[s.start_layer, s.end_layer, s.n_layers] for s in shards],
+            "peer_graph": {k: sorted(c.to_id for c in v) for k, v in nodes[0].topology.peer_graph.items()}}
+
+  end = asyncio.run(run())
+  return {"n_nodes": n_nodes, "node_ids": ids, "prompt": prompt, "n_layers": n_layers, "max_generate_tokens": max_generate_tokens,
+          "eos_token_id": eos_token_id, "engine_log": log, "on_token": tokens, "end": end}
+
+
 def main():
   if not REF.exists():
     print("reference not mounted: nothing generated")
@@ -292,7 +351,15 @@ def main():
   (GOLD / "ref_engine_trace.json").write_text(json.dumps(traces, separators=(",", ":")))
   for k, v in traces.items():
     print(k, "generated", v["generated"], "calls", len(v["calls"]))
-  print("written: ref_config_permute_state.json, ref_engine_trace.json")
+  node_traces = {
+    "one_node_cap": gen_node_trace(1, "5 9 11 2 40", 4, 6, 96),
+    "two_nodes_cap": gen_node_trace(2, "5 9 11 2 40", 4, 6, 96),
+    "three_nodes_eos": gen_node_trace(3, "5 9 11 2 40", 6, 64, 83),     # 83 is the third id the toy model emits: stop by eos
+  }
+  (GOLD / "ref_node_trace.json").write_text(json.dumps(node_traces, separators=(",", ":")))
+  for k, v in node_traces.items():
+    print(k, "tokens", [t["tokens"] for t in v["on_token"]], "engine calls", len(v["engine_log"]))
+  print("written: ref_config_permute_state.json, ref_engine_trace.json, ref_node_trace.json")
 
 
 if __name__ == "__main__":

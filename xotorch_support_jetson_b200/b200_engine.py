@@ -36,6 +36,7 @@ import torch
 
 from .inference_engine import InferenceEngine
 from .model_config import load_model_config
+from .networking import DeviceTensorRef
 from .shard import Shard
 from .stage import StageRuntime
 from .synth import SyntheticTokenizer
@@ -46,6 +47,12 @@ warnings.filterwarnings("ignore", message="The given NumPy array is not writable
 # from the reference (sharded_inference_engine.py:34-35)
 TEMP = 0.6
 TOP_K = 35
+
+
+def as_shard(shard) -> Shard:
+  """This package's ``Shard`` from anything with the four fields (a reference checkout passes its own
+  dataclass, ``xotorch/inference/shard.py``; the two compare unequal although they mean the same)."""
+  return shard if type(shard) is Shard else Shard(shard.model_id, int(shard.start_layer), int(shard.end_layer), int(shard.n_layers))
 
 
 def state_position(inference_state: Optional[dict]) -> Optional[int]:
@@ -148,9 +155,21 @@ class B200ShardInferenceEngine(InferenceEngine):
     self.direct_host_logits = env.get("XB_API_DIRECT_LOGITS", "1") != "0"   # LM head stores the logits into pinned host memory itself
     self._spec = None          # the decode forward enqueued ahead of the caller's infer_tensor, see sample()
     self.spec_hits = self.spec_misses = 0
+    # intra-box hand-off (networking.py): with device_handoff a non-last shard returns a DeviceTensorRef -- the hidden
+    # rows stay in HBM -- instead of fp32 numpy; connect_next() / bind_ring() say where the next shard lives
+    self.device_handoff = False
+    self.landing_slots = 0          # > 0: this engine keeps landing buffers the previous stage's kernels may store into
+    self.landing_rows = 0
+    self._landing_epoch = 0         # bumped whenever the stage (and with it the landing buffers) is rebuilt
+    self._next_engine = None        # next shard's engine when it lives in this process
+    self._next_epoch = None         # epoch of the next engine's landing buffers this stage is connected to (None: not connected)
+    self._ho_next = 0               # round-robin landing slot + the flag value last written to each slot
+    self._ho_value: List[int] = []
+    self._ring = None               # networking.RingChannel when the next shard is another process (torchrun)
 
   # ------------------------------------------------------------------ shard / weights
   async def ensure_shard(self, shard: Shard):
+    shard = as_shard(shard)
     if self.shard == shard:
       return
     self.model_path = await self.shard_downloader.ensure_shard(shard, self.__class__.__name__)
@@ -164,6 +183,7 @@ class B200ShardInferenceEngine(InferenceEngine):
                         max_seqs=self.max_seqs, max_tokens_per_seq=self.max_tokens_per_seq, page_tokens=self.page_tokens)
       st.load_dir(self.model_path)
       self.stage = st
+      self._stage_changed()
       self.requests.clear()
       self.free_slots = list(range(self.max_seqs - 1, -1, -1))
       self.rng = torch.Generator(device=st.device)
@@ -177,8 +197,9 @@ class B200ShardInferenceEngine(InferenceEngine):
   def attach_stage(self, shard: Shard, stage: StageRuntime, config: dict, tokenizer=None):
     """Adopt an already-loaded StageRuntime (weights resident in HBM) instead of loading the
     shard from a checkpoint directory -- in-memory / synthetic weights, benchmarks."""
-    self.stage, self.shard, self.model_config = stage, shard, config
+    self.stage, self.shard, self.model_config = stage, as_shard(shard), config
     self.max_seqs, self.max_batch_tokens = stage.max_seqs, stage.max_batch_tokens
+    self._stage_changed()
     self.tokenizer = tokenizer or SyntheticTokenizer(config["vocab_size"])
     self.requests.clear()
     self.free_slots = list(range(self.max_seqs - 1, -1, -1))
@@ -186,6 +207,72 @@ class B200ShardInferenceEngine(InferenceEngine):
     self.rng.manual_seed(1234)
     self._stream = torch.cuda.Stream(device=stage.device)
     self._copy_stream = torch.cuda.Stream(device=stage.device)   # sampled ids -> host, beside the next step
+
+  # ------------------------------------------------------------------ intra-box hand-off wiring
+  def enable_landing(self, n_slots: Optional[int] = None, rows: Optional[int] = None):
+    """Keep landing buffers on this engine's GPU so that the PREVIOUS stage can deliver decode steps
+    through its own kernels (xb_forward_handoff).  Call before the shard is loaded (or re-attach)."""
+    self.landing_slots = int(n_slots or self.max_seqs)
+    self.landing_rows = int(rows or min(128, self.max_seqs))
+    if self.stage is not None:
+      self._stage_changed()
+
+  def connect_next(self, next_engine: "B200ShardInferenceEngine"):
+    """The next shard of the ring is served by ``next_engine`` in THIS process (another GPU of the box):
+    hidden rows are handed over as device references, decode steps through its landing buffers."""
+    self._next_engine = next_engine
+    self._next_epoch = None
+    self.device_handoff = True
+
+  def bind_ring(self, channel):
+    """The next shard lives in another process of a torchrun ring: hidden rows leave over the channel's data
+    plane (NCCL), sent by this engine on its own stream right behind the forward that made them."""
+    self._ring = channel
+    self.device_handoff = True
+
+  def _stage_changed(self):
+    self._landing_epoch += 1
+    self._next_epoch = None       # a rebuilt producer stage is not connected to anything yet
+    if self.landing_slots > 0 and self.stage is not None and not self.stage.is_first:
+      self._ensure_handoff_buffers(self.stage, self.landing_slots, self.landing_rows)
+      self._landing_ready = self._landing_epoch
+    else:
+      self._landing_ready = None
+
+  @staticmethod
+  def _ensure_handoff_buffers(st: StageRuntime, n_slots: int, rows: int):
+    """xb_handoff_create once per stage: landing buffers + flags (consumer side) and completion counters (producer side)."""
+    geo = getattr(st, "_ho_geometry", None)
+    if geo is None:
+      st.handoff_create(n_slots, rows, ipc=False)
+      st._ho_geometry = (n_slots, rows)
+    elif geo != (n_slots, rows):
+      raise RuntimeError(f"hand-off geometry {geo} of this stage differs from the {(n_slots, rows)} the next stage uses")
+
+  def _landing_out(self, bsz: int):
+    """(slot, value) in the next engine's landing buffers for a decode step of ``bsz`` rows, or None when that
+    path is not available (then the rows travel as a device tensor).  Connects on first use."""
+    nxt = self._next_engine
+    st = self.stage
+    if nxt is None or st is None or st.is_last or nxt.stage is None or getattr(nxt, "_landing_ready", None) is None:
+      return None
+    if bsz > nxt.landing_rows or nxt.stage.dim != st.dim:
+      return None
+    if self._next_epoch is None:
+      if getattr(self, "_connected_once", None) == self._landing_epoch:
+        return None     # this stage was connected to buffers that no longer exist: stay on the tensor path
+      self._ensure_handoff_buffers(st, nxt.landing_slots, nxt.landing_rows)   # completion counters, consumer's geometry
+      st.handoff_connect_local(nxt.stage)
+      self._next_epoch = nxt._landing_ready
+      self._connected_once = self._landing_epoch
+      self._ho_value = [0] * nxt.landing_slots
+      self._ho_next = 0
+    if self._next_epoch != nxt._landing_ready:
+      return None       # the consumer rebuilt its stage
+    slot = self._ho_next
+    self._ho_next = (slot + 1) % len(self._ho_value)
+    self._ho_value[slot] += 1
+    return slot, self._ho_value[slot]
 
   async def _resolve_tokenizer(self, path):
     try:
@@ -425,6 +512,51 @@ class B200ShardInferenceEngine(InferenceEngine):
         outs.append(full)
     return torch.cat(outs, dim=0)
 
+  # ------------------------------------------------------------------ intra-box hand-off: data path
+  def _rows_from_ref(self, st: StageRuntime, ref: DeviceTensorRef, bsz: int, s: int):
+    """What a DeviceTensorRef stands for, as input of this stage: (bf16 rows [bsz, s, D] on this GPU | None, landing)."""
+    if ref.landing is not None:
+      return None, ref.landing                        # already in this GPU's landing buffer (stored by the producer's kernel)
+    if ref.recv is not None and ref.tensor is None:   # process-per-GPU ring: post the receive on this engine's stream
+      buf = torch.empty((bsz * s, st.dim), dtype=torch.bfloat16, device=st.device)
+      self._ring.recv_rows(buf)
+      return buf.reshape(bsz, s, -1), None
+    t = ref.tensor
+    if ref.event is not None:
+      torch.cuda.current_stream(st.device).wait_event(ref.event)
+    t.record_stream(torch.cuda.current_stream(st.device))   # the producer may drop its reference before this stream is done
+    if t.device != st.device:
+      t = t.to(st.device, non_blocking=True)          # GPU -> GPU over NVLink, no host bounce
+    return t.reshape(bsz, s, -1), None
+
+  def _device_result(self, out: Optional[torch.Tensor], bsz: int, s: int, landing_out) -> DeviceTensorRef:
+    st = self.stage
+    shape = (bsz, s, st.dim)
+    if landing_out is not None:
+      return DeviceTensorRef(shape, landing=landing_out)
+    if self._ring is not None:
+      self._ring.send_rows(out.reshape(bsz * s, -1))    # enqueued on this stream, right behind the forward
+      return DeviceTensorRef(shape, tensor=out, recv=("sent",))
+    ev = torch.cuda.Event()
+    ev.record(torch.cuda.current_stream(st.device))
+    return DeviceTensorRef(shape, tensor=out, event=ev)
+
+  def _forward_decode_hop(self, st: StageRuntime, req: _Request, bsz: int, pos: int, dev_in, is_tokens: bool, landing_in):
+    """One decode step of a ring stage: input = ids / hidden rows / this GPU's landing slot, output = logits (last
+    shard), hidden rows, or -- when the next engine's landing buffers are connected -- nothing but a (slot, value)."""
+    positions = self._positions(req, pos)
+    landing_out = None if self.shard.is_last_layer() else self._landing_out(bsz)
+    inp = {}
+    if landing_in is None:
+      flat = dev_in.reshape(-1) if is_tokens else dev_in.reshape(bsz, -1)
+      inp = {"tokens": flat} if is_tokens else {"hidden": flat.contiguous()}
+    if landing_in is None and landing_out is None:
+      return st.forward(req.slots, [1] * bsz, positions, **inp), None
+    si, vi = landing_in if landing_in is not None else (-1, 0)
+    so, vo = landing_out if landing_out is not None else (-1, 0)
+    out = st.forward(req.slots, [1] * bsz, positions, handoff=(si, vi, so, vo), **inp)
+    return out, landing_out
+
   def _prompt_keep_mask(self, x: np.ndarray, inference_state: Optional[dict], bsz: int, s: int, pos: int) -> Optional[np.ndarray]:
     """bool [bsz, s] of the prompt slots that are NOT padding, or None when the prompt holds no pad
     id (the usual case: the reference's ``tril`` branch).  Only a prompt (multi-token input at
@@ -455,7 +587,8 @@ class B200ShardInferenceEngine(InferenceEngine):
 
     def infer_body():
       st = self.stage
-      x = np.asarray(input_data)
+      ref = input_data if isinstance(input_data, DeviceTensorRef) else None
+      x = ref if ref is not None else np.asarray(input_data)
       if x.ndim == 2:
         bsz, s = x.shape
       elif x.ndim == 3:
@@ -484,16 +617,28 @@ class B200ShardInferenceEngine(InferenceEngine):
         dev_in = torch.as_tensor(np.ascontiguousarray(x, dtype=np.int32)).to(st.device, non_blocking=True)
       if sp is not None:   # this very step was enqueued by sample() on the same ids (checked on the host)
         return finish(req, sp["out"], sp["host"], sp["event"], bsz, s, pos)
-      if x.ndim == 3:
+      landing_in = None
+      if ref is not None:
+        dev_in, landing_in = self._rows_from_ref(st, ref, bsz, s)
+      elif x.ndim == 3:
         dev_in = torch.as_tensor(np.ascontiguousarray(x, dtype=np.float32)).to(st.device, non_blocking=True).to(torch.bfloat16)
       keep = self._prompt_keep_mask(x, inference_state, bsz, s, pos)
       if keep is not None:
         out = self._forward_padded_prompt(st, req, dev_in, keep, x.ndim == 2)
+      elif s == 1 and (landing_in is not None or (self.device_handoff and not shard.is_last_layer())) and bsz <= st.max_batch_tokens:
+        return finish_hop(req, *self._forward_decode_hop(st, req, bsz, pos, dev_in, x.ndim == 2, landing_in), bsz, pos)
       else:
         out = self._forward_chunked(st, req, dev_in, bsz, s, pos, x.ndim == 2)
       if isinstance(out, tuple):
         return finish(req, out[0], out[1], out[2], bsz, s, pos)
       return finish(req, out, None, None, bsz, s, pos)
+
+    def finish_hop(req, out, landing_out, bsz, pos):
+      """A decode step that arrived through / leaves through the box-internal hand-off."""
+      if shard.is_last_layer():
+        return finish(req, out, None, None, bsz, 1, pos)
+      req.pos = pos + 1
+      return self._device_result(out, bsz, 1, landing_out), state_to_dict(req.tokens, pos)
 
     def finish(req, out, host, ev, bsz, s, pos):
       req.pos = pos + s
@@ -504,6 +649,8 @@ class B200ShardInferenceEngine(InferenceEngine):
         ev.synchronize()
         self._last_logits = (host, out, request_id)
         return host, new_state
+      if self.device_handoff:
+        return self._device_result(out, bsz, s, None), new_state      # hidden rows stay in HBM (networking.DeviceTensorRef)
       return self._to_host(out.float().reshape(bsz, s, -1)), new_state  # fp32 [B, s, D]
 
     return await asyncio.get_running_loop().run_in_executor(self.executor, infer_wrapper)

@@ -67,8 +67,12 @@ def local_gpu_capabilities() -> List[DeviceCapabilities]:
 
 
 class Topology:
+  """Nodes + directed peer edges, as ``xotorch/topology/topology.py:22-77`` keeps them (an edge is keyed
+  by its two ends; ``merge`` takes over only what the peer says about ITSELF)."""
+
   def __init__(self):
     self.nodes: Dict[str, DeviceCapabilities] = {}
+    self.peer_graph: Dict[str, Dict[str, Optional[str]]] = {}   # from_id -> {to_id: description}
     self.active_node_id: Optional[str] = None
 
   def update_node(self, node_id: str, device_capabilities: DeviceCapabilities):
@@ -79,6 +83,20 @@ class Topology:
 
   def all_nodes(self):
     return self.nodes.items()
+
+  def add_edge(self, from_id: str, to_id: str, description: Optional[str] = None):
+    self.peer_graph.setdefault(from_id, {}).setdefault(to_id, description)
+
+  def merge(self, peer_node_id: str, other: "Topology"):
+    if peer_node_id in other.nodes:
+      self.update_node(peer_node_id, other.nodes[peer_node_id])
+    for to_id, desc in other.peer_graph.get(peer_node_id, {}).items():
+      self.add_edge(peer_node_id, to_id, desc)
+
+  def to_json(self) -> dict:
+    return {"nodes": {i: c.to_dict() for i, c in self.nodes.items()},
+            "peer_graph": {f: [{"from_id": f, "to_id": t, "description": d} for t, d in tos.items()] for f, tos in self.peer_graph.items()},
+            "active_node_id": self.active_node_id}
 
 
 @dataclass
