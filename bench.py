@@ -288,12 +288,6 @@ def run_b200(args):
 
   # ---- end-to-end leg with host buffers
   e2e = None
-  if world > 1:
-    host_in = [torch.zeros(B, dtype=torch.int32).pin_memory() for _ in range(M)]
-    host_out = [torch.zeros(B, dtype=torch.int32).pin_memory() for _ in range(M)]
-    e2e_ms, _ = timed_median(lambda: runner.decode(K, host_tokens=host_in, host_out=host_out), R)
-    e2e = {"value": B * M * K / (e2e_ms * 1e-3), "unit": "tok/s", "h2d_bytes_per_step": 4 * B * M, "d2h_bytes_per_step": 2 * 4 * B * M,
-           "api": "PipelineRunner.decode with pinned host id buffers (ids D2H+H2D on rank 0, sampled ids D2H on the last rank, every step)"}
   runner.drain()
 
   # ---- roofline of the dominant kernel: the tcgen05 Linear streaming this stage's weights
@@ -379,6 +373,13 @@ def run_b200(args):
       cpu_base = {"value": val, "unit": "tok/s", "cores": os.cpu_count() or 1, "kind": "port",
                   "sample": f"{args.cpu_steps} decode steps of {args.ref_batch} sequences (the named batch) at context {L} (synthetic KV cache), "
                             f"oracle port in reference-exact mode, {time.perf_counter() - t0:.0f}s incl. weight init"}
+
+  # ---- N > 1: end-to-end through the plugin API and the ring: one BoxNode per rank, RingPeerHandle / RingServer
+  # between them, infer_tensor + sample per hop with host buffers at both ends of the ring
+  if world > 1:
+    runner.reset()
+    barrier()
+    e2e = e2e_ring(runner, args.model, cfg, prompts, K, W, dist, rank, world)
 
   if rank == 0:
     line = {
@@ -493,6 +494,72 @@ class PipelineRunnerView:
     steps(W)
     ms = timed(lambda: steps(K))
     return {"decode_bs1_tok_s": K / (ms * 1e-3), "decode_bs1_ms_per_tok": ms / K}
+
+
+def e2e_ring(runner, model_id, cfg, prompts, K, W, dist, rank, world):
+  """N > 1 end to end: every rank runs a BoxNode around a B200ShardInferenceEngine that adopts the rank's resident
+  stage; the entry node (rank 0) gets one request per micro-batch as HOST token ids ``[B, L]`` (process_tokens) and
+  receives every step's sampled ids back as host lists through on_token; between ranks the request travels the way
+  Node.forward_tensor sends it -- RingPeerHandle.send_tensor: header over the gloo control channel, hidden rows over
+  NCCL posted by the engines -- and on the last rank through infer_tensor -> fp32 logits on the host -> sample().
+  Rate = ids delivered to rank 0's callback between step W and step W+K of every request."""
+  import numpy as np
+  import torch
+  from xotorch_support_jetson_b200.b200_engine import B200ShardInferenceEngine
+  from xotorch_support_jetson_b200.orchestration import build_rank_node
+  from xotorch_support_jetson_b200.shard import Shard
+  B, M = runner.B, runner.M
+  L = prompts[0].shape[1]
+  ctrl = dist.new_group(ranks=list(range(world)), backend="gloo")
+  sync = dist.new_group(ranks=list(range(world)), backend="gloo")
+  shards = [None] * world
+  dist.all_gather_object(shards, (tuple(runner.shard), bool(runner.first), bool(runner.last)))
+  for i, (sh, first, last) in enumerate(shards):
+    s_ = Shard(*sh)
+    # the node decides by the Shard where ids enter and where logits leave: that must agree with what the stage holds
+    assert s_.is_first_layer() == first and s_.is_last_layer() == last, f"stage {i}: half-layer cut inside the first / last layer"
+  shard_map = [Shard(*sh) for sh, _, _ in shards]
+  eng = B200ShardInferenceEngine(shard_downloader=None, device=runner.device.index)
+  eng.attach_stage(runner.shard, runner.stage, cfg)
+  n_gen = W + K + 1
+  host_prompts = [p.cpu().numpy().astype(np.int64) for p in prompts] if rank == 0 else None
+  stamps = {}
+
+  async def run():
+    loop = asyncio.get_running_loop()
+    node = build_rank_node(eng, dist, rank, world, ctrl_group=ctrl, data_group=None, max_generate_tokens=n_gen, shard_map=shard_map)
+    await node.start()
+    if rank == 0:
+      left = set(range(M))
+      done = asyncio.Event()
+
+      def on_token(rid, toks, fin):
+        stamps.setdefault(rid, []).append(time.perf_counter())
+        if fin:
+          left.discard(int(rid[2:]))
+          if not left:
+            done.set()
+
+      node.on_token.register("bench").on_next(on_token)
+      base = Shard(model_id, 0, 0, cfg["num_layers"])
+      for m in range(M):
+        asyncio.create_task(node.process_tokens(base, host_prompts[m], f"mb{m}"))
+      await asyncio.wait_for(done.wait(), 600)
+    await loop.run_in_executor(None, lambda: dist.barrier(group=sync))   # the other ranks keep serving until rank 0 is done
+    await node.stop()
+
+  asyncio.run(run())
+  torch.cuda.synchronize()
+  if rank != 0:
+    return None
+  t0 = max(stamps[f"mb{m}"][W] for m in range(M))
+  t1 = max(stamps[f"mb{m}"][W + K] for m in range(M))
+  V = cfg["vocab_size"]
+  return {"value": B * M * K / (t1 - t0), "unit": "tok/s", "h2d_bytes_per_step": 8 * B * M, "d2h_bytes_per_step": B * M * (V * 4 + 4),
+          "api": "one BoxNode per rank (the reference Node's walk): process_tokens(host ids [32, 2048]) per micro-batch on rank 0 -> "
+                 "B200ShardInferenceEngine.infer_tensor per stage -> Node.forward_tensor -> RingPeerHandle.send_tensor (header over gloo, "
+                 "bf16 hidden rows over NCCL posted by the engines) -> last rank: fp32 logits [32, V] to the host, sample(), ids back "
+                 "to rank 0 as host arrays (next step's input) and through send_result / on_token (counted here)"}
 
 
 def e2e_engine_api(runner, cfg, prompt, K, W):

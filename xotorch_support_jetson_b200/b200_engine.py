@@ -65,12 +65,14 @@ def state_position(inference_state: Optional[dict]) -> Optional[int]:
   return None if p is None else int(p)
 
 
-def state_to_dict(tokens: Optional[List[List[int]]], curr_pos: int) -> dict:
+def state_to_dict(tokens: Optional[List[List[int]]], curr_pos: int, copy: bool = True) -> dict:
   """The state this engine hands back: the reference's field names, types and nesting for the two
-  entries it needs (JSON-able, survives the gRPC hop of grpc_peer_handle.py:209-230)."""
+  entries it needs (JSON-able, survives the gRPC hop of grpc_peer_handle.py:209-230).  ``copy=False``
+  (engines bound to an intra-box ring): the token history is the engine's live list instead of a snapshot --
+  O(B x context) per hop is what the box-internal path exists to avoid; whoever serialises it copies."""
   out = {"curr_pos": int(curr_pos)}
   if tokens is not None:
-    out["tokens"] = [row[:] for row in tokens]   # snapshot, like ShardInferenceState.to_dict
+    out["tokens"] = [row[:] for row in tokens] if copy else tokens   # snapshot, like ShardInferenceState.to_dict
   return out
 
 
@@ -638,11 +640,12 @@ class B200ShardInferenceEngine(InferenceEngine):
       if shard.is_last_layer():
         return finish(req, out, None, None, bsz, 1, pos)
       req.pos = pos + 1
-      return self._device_result(out, bsz, 1, landing_out), state_to_dict(req.tokens, pos)
+      return self._device_result(out, bsz, 1, landing_out), state_to_dict(req.tokens, pos, copy=False)
 
     def finish(req, out, host, ev, bsz, s, pos):
       req.pos = pos + s
-      new_state = state_to_dict(req.tokens, pos if not shard.is_last_layer() else pos + s)
+      new_state = state_to_dict(req.tokens, pos if not shard.is_last_layer() else pos + s,
+                                copy=not (self.device_handoff or self._ring is not None))
       if shard.is_last_layer():
         if host is None:
           host, ev = self._to_host_async(out)          # fp32 [B, V]

@@ -70,7 +70,8 @@ class CallbackSystem:
 class BoxNode:
   def __init__(self, _id: str, server, inference_engine, discovery, shard_downloader=None, partitioning_strategy=None,
                max_generate_tokens: int = 1024, default_sample_temperature: float = 0.0,
-               device_capabilities: Optional[DeviceCapabilities] = None, device_token_loop: bool = False):
+               device_capabilities: Optional[DeviceCapabilities] = None, device_token_loop: bool = False,
+               shard_map: Optional[List[Shard]] = None):
     self.id = _id
     self.server, self.inference_engine, self.discovery = server, inference_engine, discovery
     self.shard_downloader = shard_downloader
@@ -87,6 +88,9 @@ class BoxNode:
     self._on_opaque_status = CallbackSystem()
     self._partitions = None
     self._rows_done: Dict[str, List[bool]] = {}
+    # explicit layer range per ring position instead of map_partitions_to_shards (stage boundaries that the
+    # reference's whole-layer mapping cannot express: half-layer cuts balanced by bytes, topology.half_layer_stages)
+    self.shard_map = shard_map
     if hasattr(server, "bind"):
       server.bind(self)
 
@@ -149,6 +153,11 @@ class BoxNode:
   def get_current_shard(self, base_shard: Shard, index: Optional[int] = None) -> Shard:
     if index is None:
       index = self.get_partition_index()
+    if self.shard_map is not None:
+      sh = self.shard_map[index]
+      if sh.model_id != base_shard.model_id or sh.n_layers != base_shard.n_layers:
+        raise ValueError(f"this ring was built for {sh.model_id}/{sh.n_layers} layers, not {base_shard.model_id}/{base_shard.n_layers}")
+      return sh
     return map_partitions_to_shards(self._parts(), base_shard.n_layers, base_shard.model_id)[index]
 
   # ------------------------------------------------------------------ the walk
@@ -341,7 +350,7 @@ def build_box_ring(engines: List, max_generate_tokens: int = 1024, default_sampl
 
 
 def build_rank_node(engine, dist, rank: int, world: int, ctrl_group=None, data_group=None, max_generate_tokens: int = 1024,
-                    default_sample_temperature: float = 0.0, memory_mb: int = 183359) -> BoxNode:
+                    default_sample_temperature: float = 0.0, memory_mb: int = 183359, shard_map: Optional[List[Shard]] = None) -> BoxNode:
   """This RANK's node of a process-per-GPU ring (torchrun): the other ranks appear as ``RingPeerHandle``s, the
   ``RingServer`` listens to the previous rank, layer ranges as in ``build_box_ring`` (rank i = partition i).
   ``ctrl_group``: a CPU (gloo) group for headers; ``data_group``: where hidden rows travel (NCCL on a GPU box).
@@ -353,7 +362,8 @@ def build_rank_node(engine, dist, rank: int, world: int, ctrl_group=None, data_g
   ch = RingChannel(dist, rank, world, ctrl_group=ctrl_group, data_group=data_group)
   node = BoxNode(ids[rank], RingServer(ch), engine, BoxDiscovery([RingPeerHandle(ids[j], j, ch, caps) for j in range(world) if j != rank]),
                  partitioning_strategy=RingMemoryWeightedPartitioningStrategy(), max_generate_tokens=max_generate_tokens,
-                 default_sample_temperature=default_sample_temperature, device_capabilities=caps, device_token_loop=(world == 1))
+                 default_sample_temperature=default_sample_temperature, device_capabilities=caps, device_token_loop=(world == 1),
+                 shard_map=shard_map)
   if world > 1 and rank + 1 < world and hasattr(engine, "bind_ring"):
     engine.bind_ring(ch)
   elif world > 1 and hasattr(engine, "_ring"):
