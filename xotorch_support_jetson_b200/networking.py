@@ -215,7 +215,7 @@ class BoxDiscovery(Discovery):
 
 # ----------------------------------------------------------------------------- one process per GPU (torchrun)
 KIND_PROMPT, KIND_TENSOR, KIND_RESULT, KIND_STATUS, KIND_STOP = 1, 2, 3, 4, 5
-_HDR = 8   # int64 words: kind, meta bytes, payload kind (0 none, 1 int ids, 2 fp32 numpy, 3 device rows over the data channel), ndim, d0, d1, d2, spare
+_HDR = 8   # int64 words: kind, meta bytes, payload kind (0 none, 1 int ids, 2 fp32 numpy, 3 device rows over the data channel), ndim, d0, d1, d2, size of a second message (0: all inline)
 
 
 class RingChannel:
@@ -236,40 +236,55 @@ class RingChannel:
     self._send_lock = threading.Lock()
 
   # -- control plane (any thread; serialised per process)
+  FRAME = 8192   # bytes of the one fixed-size message a decode hop costs: header + JSON + small payload
+
   def send_message(self, kind: int, meta: dict, payload: Optional[np.ndarray] = None, device_rows=None):
     import torch
-    blob = json.dumps(meta).encode()
+    blob = json.dumps(meta, separators=(",", ":")).encode()
     hdr = [kind, len(blob), 0, 0, 0, 0, 0, 0]
-    body = None
+    body = b""
     if device_rows is not None:
       hdr[2], hdr[3] = 3, len(device_rows)
       hdr[4:4 + len(device_rows)] = list(device_rows)
     elif payload is not None:
       arr = np.ascontiguousarray(payload)
       is_int = np.issubdtype(arr.dtype, np.integer)
-      body = arr.astype(np.int64 if is_int else np.float32)
-      hdr[2], hdr[3] = (1 if is_int else 2), body.ndim
-      hdr[4:4 + body.ndim] = list(body.shape)
+      arr = arr.astype(np.int64 if is_int else np.float32)
+      hdr[2], hdr[3] = (1 if is_int else 2), arr.ndim
+      hdr[4:4 + arr.ndim] = list(arr.shape)
+      body = arr.tobytes()
+    rest = blob + body
+    inline = len(rest) <= self.FRAME - 8 * _HDR
+    hdr[7] = 0 if inline else len(rest)        # > 0: the JSON + payload follow as a second message of exactly this size
+    frame = bytearray(self.FRAME)
+    frame[:8 * _HDR] = np.asarray(hdr, dtype=np.int64).tobytes()
+    if inline:
+      frame[8 * _HDR:8 * _HDR + len(rest)] = rest
     with self._send_lock:
-      self.dist.send(torch.tensor(hdr, dtype=torch.int64), dst=self.next_rank, group=self.ctrl_group)
-      self.dist.send(torch.frombuffer(bytearray(blob), dtype=torch.uint8), dst=self.next_rank, group=self.ctrl_group)
-      if body is not None:
-        self.dist.send(torch.from_numpy(body.reshape(-1)), dst=self.next_rank, group=self.ctrl_group)
+      self.dist.send(torch.frombuffer(frame, dtype=torch.uint8), dst=self.next_rank, group=self.ctrl_group)
+      if not inline:
+        self.dist.send(torch.frombuffer(bytearray(rest), dtype=torch.uint8), dst=self.next_rank, group=self.ctrl_group)
 
   def recv_message(self):
     """Blocks until the previous rank sends: (kind, meta, payload ndarray | shape tuple of device rows | None)."""
     import torch
-    hdr = torch.zeros(_HDR, dtype=torch.int64)
-    self.dist.recv(hdr, src=self.prev_rank, group=self.ctrl_group)
-    kind, nblob, pk, ndim = (int(x) for x in hdr[:4])
-    blob = torch.zeros(max(nblob, 1), dtype=torch.uint8)
-    self.dist.recv(blob, src=self.prev_rank, group=self.ctrl_group)
-    meta = json.loads(bytes(blob[:nblob].tolist()).decode()) if nblob else {}
+    frame = torch.zeros(self.FRAME, dtype=torch.uint8)
+    self.dist.recv(frame, src=self.prev_rank, group=self.ctrl_group)
+    raw = frame.numpy().tobytes()
+    hdr = np.frombuffer(raw[:8 * _HDR], dtype=np.int64)
+    kind, nblob, pk, ndim, ext = int(hdr[0]), int(hdr[1]), int(hdr[2]), int(hdr[3]), int(hdr[7])
+    if ext > 0:
+      more = torch.zeros(ext, dtype=torch.uint8)
+      self.dist.recv(more, src=self.prev_rank, group=self.ctrl_group)
+      rest = more.numpy().tobytes()
+    else:
+      rest = raw[8 * _HDR:]
+    meta = json.loads(rest[:nblob].decode()) if nblob else {}
     shape = tuple(int(x) for x in hdr[4:4 + ndim])
     if pk in (1, 2):
-      body = torch.zeros(int(np.prod(shape)) if shape else 1, dtype=torch.int64 if pk == 1 else torch.float32)
-      self.dist.recv(body, src=self.prev_rank, group=self.ctrl_group)
-      return kind, meta, body.numpy().reshape(shape)
+      n = int(np.prod(shape)) if shape else 1
+      dt = np.int64 if pk == 1 else np.float32
+      return kind, meta, np.frombuffer(rest[nblob:nblob + n * np.dtype(dt).itemsize], dtype=dt).reshape(shape).copy()
     if pk == 3:
       return kind, meta, shape
     return kind, meta, None
