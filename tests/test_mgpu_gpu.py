@@ -1,4 +1,8 @@
-"""Multi-GPU parity (needs >= 2 GPUs; skipped on a 1-GPU box): NCCL pipeline == single GPU."""
+"""Multi-GPU parity (needs >= 2 GPUs; skipped on a 1-GPU box, where tests/test_handoff_gpu.py and
+tests/test_box_ring_gpu.py run the same kernels and protocols with both stages on one GPU): the layer pipeline
+under torchrun must give exactly the tokens of a single-GPU full-shard run -- with the peer-store hand-off and
+with NCCL, with half-layer and with whole-layer stage boundaries."""
+import os
 import subprocess
 import sys
 from pathlib import Path
@@ -11,10 +15,14 @@ ROOT = Path(__file__).resolve().parent.parent
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs at least 2 GPUs")
-@pytest.mark.parametrize("mid", ["llama-3.1-tiny", "qwen-2.5-tiny"])
-def test_nccl_pipeline_equals_single_gpu(built_lib, mid):
+@pytest.mark.parametrize("mid,peer,half", [
+  ("llama-3.1-tiny", "1", "1"), ("qwen-2.5-tiny", "1", "1"),
+  ("llama-3.1-tiny", "0", "1"), ("llama-3.1-tiny", "1", "0"), ("qwen-2.5-tiny", "0", "0"),
+])
+def test_pipeline_equals_single_gpu(built_lib, mid, peer, half):
   n = 2
+  env = dict(os.environ, XB_PEER_HANDOFF=peer, XB_HALF_LAYERS=half)
   cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr", "127.0.0.1",
          "--master-port", "29533", str(ROOT / "tests" / "mgpu_pipeline_check.py"), mid]
-  out = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+  out = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env)
   assert out.returncode == 0 and "MGPU_PIPELINE_OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
