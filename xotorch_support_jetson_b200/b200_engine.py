@@ -137,7 +137,7 @@ class B200ShardInferenceEngine(InferenceEngine):
     self.model_config = None
     self.uuid = str(uuid.uuid4())
     self.executor = ThreadPoolExecutor(max_workers=1)  # strictly serialised like the reference (:46)
-    self._waiter = ThreadPoolExecutor(max_workers=4)   # waits for GPU events, so that the worker above never blocks on one
+    self._waiter = ThreadPoolExecutor(max_workers=32)   # waits for GPU events, so that the worker above never blocks on one
     env = os.environ
     self.device_index = device if device is not None else int(env.get("XB_DEVICE", env.get("LOCAL_RANK", "0")))
     self.max_seqs = max_seqs or int(env.get("XB_MAX_SEQS", "32"))

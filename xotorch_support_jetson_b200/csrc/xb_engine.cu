@@ -26,6 +26,8 @@ int xb_fail(int code, const char* fmt, ...) {
   return code;
 }
 
+#define XB_DEC_ROWS 128
+
 struct LayerW {
   bf16 *wqkv = nullptr, *bqkv = nullptr, *wo = nullptr, *wgu = nullptr, *wdown = nullptr;
   bf16 *sa_norm = nullptr, *mlp_norm = nullptr;
@@ -62,6 +64,11 @@ struct xb_engine {
   cudaEvent_t meta_ev[META_RING] = {nullptr};
   int meta_next = 0;
   size_t meta_ints = 0;
+  // decode steps of up to XB_DEC_ROWS sequences describe themselves in a compact block of their own:
+  // [ctl 4 | tok_pos R | seq_slot R | tok_seq R = 0..R-1 | seq_last R = 0..R-1]; the last two never change, so a step
+  // uploads 4 + 2R ints in ONE copy (it used to take three or four small copies per pipeline tick)
+  int* d_dec = nullptr;
+  bool meta_is_dec = false;   // which block the last forward filled (measurement hooks replay that batch)
   // engine-owned input/output staging so captured graphs see fixed addresses
   int* in_tokens = nullptr;
   float* logits = nullptr;
@@ -290,9 +297,15 @@ extern "C" int xb_engine_create(const xb_model_desc* desc, int device, xb_engine
   e->d_seq_last = e->d_meta + 2 * T + d.max_seqs;
   e->d_tile_start = e->d_meta + 2 * T + 2 * d.max_seqs;
   e->d_tile_len = e->d_tile_start + e->max_tiles;
-  e->d_ctl = reinterpret_cast<HandoffCtl*>(e->d_tile_len + e->max_tiles);
+  {
+    XB_TRY(dmalloc((void**)&e->d_dec, (4 + 4 * XB_DEC_ROWS) * 4));
+    int ident[4 + 4 * XB_DEC_ROWS] = {0};
+    for (int i = 0; i < XB_DEC_ROWS; ++i) ident[4 + 2 * XB_DEC_ROWS + i] = ident[4 + 3 * XB_DEC_ROWS + i] = i;
+    XB_CUDA(cudaMemcpy(e->d_dec, ident, sizeof(ident), cudaMemcpyHostToDevice));
+  }
+  e->d_ctl = reinterpret_cast<HandoffCtl*>(e->d_dec);   // the peer hand-off carries decode steps only
   for (int i = 0; i < xb_engine::META_RING; ++i) {
-    XB_CUDA(cudaMallocHost((void**)&e->h_meta_ring[i], e->meta_ints * 4));
+    XB_CUDA(cudaMallocHost((void**)&e->h_meta_ring[i], (e->meta_ints + 4 + 2 * XB_DEC_ROWS) * 4));
     XB_CUDA(cudaEventCreateWithFlags(&e->meta_ev[i], cudaEventDisableTiming));
   }
   XB_TRY(dmalloc((void**)&e->in_tokens, T * 4));
@@ -332,7 +345,7 @@ extern "C" int xb_engine_destroy(xb_engine* e) {
     cudaFree(w.sa_norm); cudaFree(w.mlp_norm); cudaFree(w.k_pool); cudaFree(w.v_pool);
   }
   cudaFree(e->embed); cudaFree(e->final_norm); cudaFree(e->lm_head); cudaFree(e->rope);
-  cudaFree(e->d_page_table); cudaFree(e->d_meta); cudaFree(e->in_tokens); cudaFree(e->logits);
+  cudaFree(e->d_page_table); cudaFree(e->d_meta); cudaFree(e->d_dec); cudaFree(e->in_tokens); cudaFree(e->logits);
   if (e->peer_landing && !e->peer_is_local) cudaIpcCloseMemHandle(e->peer_landing);
   if (e->peer_flags && !e->peer_is_local) cudaIpcCloseMemHandle(e->peer_flags);
   cudaFree(e->landing); cudaFree(e->flags); cudaFree(e->done_cnt);
@@ -869,7 +882,8 @@ static int choose_kv_splits(xb_engine* e, int T, int max_ctx) {
 static int run_head(xb_engine* e, int n_seqs, cudaStream_t st, float* host_logits) {
   const xb_model_desc& d = e->d;
   const int D = d.dim;
-  XB_TRY(launch_k(e, xb_gather_rows_kernel, dim3(n_seqs), dim3(256), 0, st, 1, e->hn, e->d_seq_last, e->last_rows, D));
+  const int* seq_last = e->meta_is_dec ? e->d_dec + 4 + 3 * XB_DEC_ROWS : e->d_seq_last;
+  XB_TRY(launch_k(e, xb_gather_rows_kernel, dim3(n_seqs), dim3(256), 0, st, 1, e->hn, seq_last, e->last_rows, D));
   const GemmPlan* gp;
   XB_TRY(get_plan(e, SITE_HEAD, 0, e->last_rows, D, e->lm_head, n_seqs, d.vocab, D, e->logits, d.vocab, nullptr, 1, &gp));
   if (host_logits != nullptr) {
@@ -883,15 +897,26 @@ static int run_head(xb_engine* e, int n_seqs, cudaStream_t st, float* host_logit
   return 0;
 }
 
+static void fill_batch_meta(const xb_engine* e, BatchMeta& m) {
+  if (e->meta_is_dec) {
+    m.tok_pos = e->d_dec + 4;
+    m.seq_slot = e->d_dec + 4 + XB_DEC_ROWS;
+    m.tok_seq = e->d_dec + 4 + 2 * XB_DEC_ROWS;
+    m.seq_last = e->d_dec + 4 + 3 * XB_DEC_ROWS;
+  } else {
+    m.tok_seq = e->d_tok_seq;
+    m.tok_pos = e->d_tok_pos;
+    m.seq_slot = e->d_seq_slot;
+    m.seq_last = e->d_seq_last;
+  }
+}
+
 static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, void* const* taps, cudaStream_t st,
                     int ho_in = 0, int ho_out = 0, int with_head = 1) {
   const xb_model_desc& d = e->d;
   const bool first = shard_is_first(d), last = shard_is_last(d);
   BatchMeta m;
-  m.tok_seq = e->d_tok_seq;
-  m.tok_pos = e->d_tok_pos;
-  m.seq_slot = e->d_seq_slot;
-  m.seq_last = e->d_seq_last;
+  fill_batch_meta(e, m);
   m.page_table = e->d_page_table;
   m.tile_start = e->d_tile_start;
   m.tile_len = e->d_tile_len;
@@ -903,14 +928,31 @@ static int run_body(xb_engine* e, int T, int n_seqs, int n_splits, int n_tiles, 
   // on the previous GPU) and/or stop after the attention block of its last layer; the residual stream
   // crosses the boundary exactly as it does between whole layers
   const bf16* norm0 = d.first_from_mlp ? e->L[0].mlp_norm : e->L[0].sa_norm;
+  // batches of up to 128 rows run the row kernels after every Linear (launch_resid_norm: T <= 128, D % 4 == 0, D <= 8192)
+  const bool row_norm = T <= 128 && D % 4 == 0 && D <= 8192;
   if (first) {
     XB_TRY(launch_k(e, xb_embed_norm_kernel<256>, dim3(T), dim3(256), 0, st, 1, e->in_tokens, e->embed, e->L[0].sa_norm, e->h, e->hn, D, d.vocab, d.norm_eps,
                                                   d.rmsnorm_two_round));
   } else if (ho_in) {
-    // stage input arrives in the landing buffer, stored there by the previous GPU's last kernel
+    // stage input arrives in the landing buffer, stored there by the previous GPU's last kernel.  Decode rows take the
+    // row kernels' layout: the norm's sum of squares is then accumulated in the order the unsplit model uses (row_ss4)
+    if (row_norm && D <= 4096)
+      XB_TRY(launch_k(e, xb_recv_norm_row_kernel<1024, 1>, dim3(T), dim3(1024), 0, st, 1, (const bf16*)e->landing,
+                      (const uint32_t*)e->flags, (const HandoffCtl*)e->d_ctl, (long long)e->ho_rows * D, e->h, norm0, e->hn, D,
+                      d.norm_eps, d.rmsnorm_two_round, e->ho_timeout_cycles, e->ho_err_dev));
+    else if (row_norm)
+      XB_TRY(launch_k(e, xb_recv_norm_row_kernel<1024, 2>, dim3(T), dim3(1024), 0, st, 1, (const bf16*)e->landing,
+                      (const uint32_t*)e->flags, (const HandoffCtl*)e->d_ctl, (long long)e->ho_rows * D, e->h, norm0, e->hn, D,
+                      d.norm_eps, d.rmsnorm_two_round, e->ho_timeout_cycles, e->ho_err_dev));
+    else
     XB_TRY(launch_k(e, xb_recv_norm_kernel<256>, dim3(T), dim3(256), norm_smem, st, 1, (const bf16*)e->landing,
                     (const uint32_t*)e->flags, (const HandoffCtl*)e->d_ctl, (long long)e->ho_rows * D, e->h, norm0, e->hn, D,
                     d.norm_eps, d.rmsnorm_two_round, e->ho_timeout_cycles, e->ho_err_dev));
+  } else if (row_norm) {
+    if (D <= 4096)
+      XB_TRY(launch_k(e, xb_norm_row_kernel<1024, 1>, dim3(T), dim3(1024), 0, st, 1, (const bf16*)e->h, norm0, e->hn, D, d.norm_eps, d.rmsnorm_two_round));
+    else
+      XB_TRY(launch_k(e, xb_norm_row_kernel<1024, 2>, dim3(T), dim3(1024), 0, st, 1, (const bf16*)e->h, norm0, e->hn, D, d.norm_eps, d.rmsnorm_two_round));
   } else {
     XB_TRY(launch_k(e, xb_resid_norm_kernel<256, 2>, dim3(T), dim3(256), norm_smem, st, 1, nullptr, SplitInfo{1, 0, 1}, 0, nullptr, e->h, norm0, e->hn, D,
                                                              d.norm_eps, d.rmsnorm_two_round));
@@ -1080,21 +1122,22 @@ static int forward_impl(xb_engine* e, const xb_batch* b, void* out, void* const*
     e->slot_len[slot] = pos + ql;
   }
   e->c.kv_pages_free = e->free_pages.size();
-  if (decode_only && T * 4 <= 2048) {
-    // small batch: one contiguous upload of the whole block would move mostly padding;
-    // the pieces are tiny, send them separately
-    XB_CUDA(cudaMemcpyAsync(e->d_tok_seq, tok_seq, T * 4, cudaMemcpyHostToDevice, st));
-    XB_CUDA(cudaMemcpyAsync(e->d_tok_pos, tok_pos, T * 4, cudaMemcpyHostToDevice, st));
-    XB_CUDA(cudaMemcpyAsync(e->d_seq_slot, seq_slot, (size_t)2 * d.max_seqs * 4, cudaMemcpyHostToDevice, st));
+  XB_CHECK(ctl == nullptr || T <= XB_DEC_ROWS, "the peer hand-off carries at most %d rows", XB_DEC_ROWS);
+  e->meta_is_dec = decode_only && T <= XB_DEC_ROWS;
+  if (e->meta_is_dec) {
+    // decode step: positions, slots and the hand-off control words in one small copy (tok_seq / seq_last are the identity)
+    int* hd = hm + e->meta_ints;
+    hd[0] = hd[1] = hd[2] = hd[3] = -1;
+    if (ctl != nullptr) { hd[0] = ctl[0]; hd[1] = ctl[1]; hd[2] = ctl[2]; hd[3] = ctl[3]; }
+    for (int i = 0; i < T; ++i) {
+      hd[4 + i] = tok_pos[i];
+      hd[4 + XB_DEC_ROWS + i] = seq_slot[i];
+    }
+    XB_CUDA(cudaMemcpyAsync(e->d_dec, hd, (4 + XB_DEC_ROWS + T) * 4, cudaMemcpyHostToDevice, st));
   } else {
     XB_CUDA(cudaMemcpyAsync(e->d_meta, hm, e->meta_ints * 4, cudaMemcpyHostToDevice, st));
   }
   e->meta_T = T;
-  if (ctl != nullptr) {
-    int* hc = hm + e->meta_ints - 4;
-    hc[0] = ctl[0]; hc[1] = ctl[1]; hc[2] = ctl[2]; hc[3] = ctl[3];
-    XB_CUDA(cudaMemcpyAsync(e->d_ctl, hc, 16, cudaMemcpyHostToDevice, st));
-  }
   XB_CUDA(cudaEventRecord(e->meta_ev[ring], st));
 
   // ---- inputs to fixed addresses
@@ -1314,7 +1357,7 @@ extern "C" int xb_bench_attention(xb_engine* e, int n_seqs, int max_ctx, int n_s
   cudaStream_t st = (cudaStream_t)stream;
   XB_CUDA(cudaSetDevice(e->device));
   BatchMeta m;
-  m.tok_seq = e->d_tok_seq; m.tok_pos = e->d_tok_pos; m.seq_slot = e->d_seq_slot; m.seq_last = e->d_seq_last;
+  fill_batch_meta(e, m);
   m.page_table = e->d_page_table; m.tile_start = e->d_tile_start; m.tile_len = e->d_tile_len;
   m.max_pages = e->max_pages; m.page_tokens = e->page_tokens;
   if (n_splits <= 0) n_splits = choose_kv_splits(e, n_seqs, max_ctx);

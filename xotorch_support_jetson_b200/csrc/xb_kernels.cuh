@@ -133,6 +133,55 @@ __global__ void __launch_bounds__(NT) xb_resid_norm_kernel(const float* __restri
 // xb_resid_norm_kernel<., 0>; planes are summed in plane order.  (An 8-block cluster per row with a
 // DSMEM exchange measured 5.7-6.0 us per launch at T <= 32: cluster scheduling and the cluster
 // barrier cost more than the extra SMs bring for 100 KB of input.)
+// Sum of squares of 4 row values and the RMSNorm store of a row held as v[VPT][4] per thread (columns
+// (it * NT + tid) * 4 ..): the ONE accumulation order every decode-path norm kernel uses -- after a Linear
+// (xb_resid_norm_row_kernel), at a stage's input (xb_norm_row_kernel), behind the peer hand-off (xb_recv_norm_row_kernel) --
+// so that a pipeline cut anywhere in the model reproduces the unsplit result bit for bit, not just almost always.
+__device__ __forceinline__ float row_ss4(const float* v) { return v[0] * v[0] + v[1] * v[1] + v[2] * v[2] + v[3] * v[3]; }
+
+template <int NT, int VPT>
+__device__ __forceinline__ void row_norm_store(const float (&v)[VPT][4], float ss, const bf16* __restrict__ nw, bf16* __restrict__ hn_row,
+                                               int D, float eps, int two_round, float* red) {
+  ss = block_sum<NT>(ss, red);
+  const float inv = 1.0f / sqrtf(ss / (float)D + eps);
+#pragma unroll
+  for (int it = 0; it < VPT; ++it) {
+    const int c = (it * NT + threadIdx.x) * 4;
+    if (c < D) {
+      const uint2 wu = *reinterpret_cast<const uint2*>(nw + c);
+      const float2 w0 = bf2_to_f2(wu.x), w1 = bf2_to_f2(wu.y);
+      uint2 r;
+      r.x = f2_to_bf2(rms_apply(v[it][0], inv, w0.x, two_round), rms_apply(v[it][1], inv, w0.y, two_round));
+      r.y = f2_to_bf2(rms_apply(v[it][2], inv, w1.x, two_round), rms_apply(v[it][3], inv, w1.y, two_round));
+      *reinterpret_cast<uint2*>(hn_row + c) = r;
+    }
+  }
+}
+
+// stage input of a decode step: hn = RMSNorm(h) (h handed in by the caller; NCCL / plugin-API path)
+template <int NT, int VPT>
+__global__ void __launch_bounds__(NT) xb_norm_row_kernel(const bf16* __restrict__ h, const bf16* __restrict__ nw, bf16* __restrict__ hn,
+                                                         int D, float eps, int two_round) {
+  pdl_launch_dependents();
+  pdl_wait();
+  __shared__ float red[32];
+  const int t = blockIdx.x;
+  float v[VPT][4];
+  float ss = 0.f;
+#pragma unroll
+  for (int it = 0; it < VPT; ++it) {
+    const int c = (it * NT + threadIdx.x) * 4;
+    v[it][0] = v[it][1] = v[it][2] = v[it][3] = 0.f;
+    if (c < D) {
+      const uint2 hu = *reinterpret_cast<const uint2*>(h + (long long)t * D + c);
+      const float2 h0 = bf2_to_f2(hu.x), h1 = bf2_to_f2(hu.y);
+      v[it][0] = h0.x; v[it][1] = h0.y; v[it][2] = h1.x; v[it][3] = h1.y;
+      ss += row_ss4(v[it]);
+    }
+  }
+  row_norm_store<NT, VPT>(v, ss, nw, hn + (long long)t * D, D, eps, two_round, red);
+}
+
 template <int NT, int VPT>
 __global__ void __launch_bounds__(NT) xb_resid_norm_row_kernel(const float* __restrict__ part, SplitInfo si,
                                                                long long split_stride, bf16* __restrict__ h,
@@ -171,24 +220,11 @@ __global__ void __launch_bounds__(NT) xb_resid_norm_row_kernel(const float* __re
       ho.x = f2_to_bf2(v[it][0], v[it][1]);
       ho.y = f2_to_bf2(v[it][2], v[it][3]);
       *reinterpret_cast<uint2*>(h + o) = ho;
-      ss += v[it][0] * v[it][0] + v[it][1] * v[it][1] + v[it][2] * v[it][2] + v[it][3] * v[it][3];
+      ss += row_ss4(v[it]);
     }
   }
   if (nw == nullptr) return;
-  ss = block_sum<NT>(ss, red);
-  const float inv = 1.0f / sqrtf(ss / (float)D + eps);
-#pragma unroll
-  for (int it = 0; it < VPT; ++it) {
-    const int c = (it * NT + threadIdx.x) * 4;
-    if (c < D) {
-      const uint2 wu = *reinterpret_cast<const uint2*>(nw + c);
-      const float2 w0 = bf2_to_f2(wu.x), w1 = bf2_to_f2(wu.y);
-      uint2 r;
-      r.x = f2_to_bf2(rms_apply(v[it][0], inv, w0.x, two_round), rms_apply(v[it][1], inv, w0.y, two_round));
-      r.y = f2_to_bf2(rms_apply(v[it][2], inv, w1.x, two_round), rms_apply(v[it][3], inv, w1.y, two_round));
-      *reinterpret_cast<uint2*>(hn + (long long)t * D + c) = r;
-    }
-  }
+  row_norm_store<NT, VPT>(v, ss, nw, hn + (long long)t * D, D, eps, two_round, red);
 }
 
 // ----------------------------------------------------------------------------- peer hand-off (pipeline, decode)
@@ -259,6 +295,52 @@ __global__ void __launch_bounds__(NT) xb_recv_norm_kernel(const bf16* __restrict
     *reinterpret_cast<uint32_t*>(hn + (long long)t * D + i) =
         f2_to_bf2(rms_apply(row[i], inv, w.x, two_round), rms_apply(row[i + 1], inv, w.y, two_round));
   }
+}
+
+// the same consumer head with the decode path's row-kernel layout and accumulation order (see row_ss4)
+template <int NT, int VPT>
+__global__ void __launch_bounds__(NT) xb_recv_norm_row_kernel(const bf16* __restrict__ landing, const uint32_t* __restrict__ flags,
+                                                              const HandoffCtl* __restrict__ ctl, long long slot_elems,
+                                                              bf16* __restrict__ h, const bf16* __restrict__ nw,
+                                                              bf16* __restrict__ hn, int D, float eps, int two_round,
+                                                              long long timeout_cycles, int* __restrict__ err_word) {
+  pdl_launch_dependents();
+  pdl_wait();
+  __shared__ float red[32];
+  const int t = blockIdx.x;
+  const int slot = ctl->slot_in;
+  const uint32_t want = (uint32_t)ctl->wait_value;
+  if (threadIdx.x == 0) {
+    long long t0 = clock64();
+    while ((int32_t)(ld_acquire_sys(flags + slot) - want) < 0) {
+      if (clock64() - t0 > timeout_cycles) {   // reported through the host-visible word, see xb_recv_norm_kernel
+        if (t == 0) {
+          err_word[1] = (int)want;
+          __threadfence_system();
+          *reinterpret_cast<volatile int*>(err_word) = slot + 1;
+        }
+        break;
+      }
+    }
+  }
+  __syncthreads();
+  const bf16* src = landing + (long long)slot * slot_elems + (long long)t * D;
+  float v[VPT][4];
+  float ss = 0.f;
+#pragma unroll
+  for (int it = 0; it < VPT; ++it) {
+    const int c = (it * NT + threadIdx.x) * 4;
+    v[it][0] = v[it][1] = v[it][2] = v[it][3] = 0.f;
+    if (c < D) {
+      uint2 hu;
+      asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(hu.x), "=r"(hu.y) : "l"(src + c) : "memory");   // written by a peer GPU
+      *reinterpret_cast<uint2*>(h + (long long)t * D + c) = hu;
+      const float2 h0 = bf2_to_f2(hu.x), h1 = bf2_to_f2(hu.y);
+      v[it][0] = h0.x; v[it][1] = h0.y; v[it][2] = h1.x; v[it][3] = h1.y;
+      ss += row_ss4(v[it]);
+    }
+  }
+  row_norm_store<NT, VPT>(v, ss, nw, hn + (long long)t * D, D, eps, two_round, red);
 }
 
 // producer tail: split-K reduce + Linear rounding + residual add (the stage's final hidden rows),
