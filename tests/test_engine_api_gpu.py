@@ -198,6 +198,49 @@ def test_next_step_speculation_is_invisible(built_lib, tmp_path):
   asyncio.run(run())
 
 
+def test_sampler_speculation_is_invisible(built_lib, tmp_path):
+  """With one request in flight the engine also runs the SAMPLER ahead (parameters of the previous sample() call) and
+  the step after it, so the host only collects.  Ids, logits and the noise stream must equal the unspeculated engine's:
+  plain loop (hits), a change of sampling parameters, a step where the caller feeds its own ids without sampling, and
+  sampling the same logits twice."""
+  from xotorch_support_jetson_b200.shard import Shard
+  mid, nl = "llama-3.2-tiny", 4
+  sh = Shard(mid, 0, nl - 1, nl)
+  prompt = np.random.RandomState(9).randint(3, 900, (2, 17)).astype(np.int64)
+
+  async def script(eng):
+    rec = []
+    lg, st = await eng.infer_tensor("a", sh, prompt, None)
+    for step in range(12):
+      rec.append(lg.copy())
+      kw = dict(temp=0.8, top_k=20) if step < 7 else dict(temp=0.3, top_k=5)      # parameters change at step 7
+      tok = await eng.sample(lg, **kw)
+      if step == 4:
+        tok = await eng.sample(lg, **kw)                                          # sampled twice: second draw, new noise
+      rec.append(tok.copy())
+      if step == 9:
+        tok = np.array([[5], [6]], dtype=np.int32)                                # caller overrides the ids
+      lg, st = await eng.infer_tensor("a", sh, tok, st)
+      if step == 10:                                                               # ... and once goes on without sampling at all
+        rec.append(lg.copy())
+        lg, st = await eng.infer_tensor("a", sh, np.array([[7], [8]], dtype=np.int32), st)
+    rec.append(lg.copy())
+    eng.end_request("a")          # gives back the noise of a sampler run that was enqueued ahead and never asked for
+    return rec
+
+  async def run():
+    on, off = _engine(tmp_path, speculate_next=True), _engine(tmp_path, speculate_next=False)
+    r_on, r_off = await script(on), await script(off)
+    assert len(r_on) == len(r_off)
+    for i, (x, y) in enumerate(zip(r_on, r_off)):
+      assert x.shape == y.shape and np.array_equal(x, y), f"record {i} differs with sampler speculation on"
+    assert off.sample_spec_hits == 0
+    assert on.sample_spec_hits >= 6 and on.spec_hits >= 6, (on.sample_spec_hits, on.spec_hits)
+    assert on.sample_calls == off.sample_calls
+
+  asyncio.run(run())
+
+
 def test_generate_device_loop_equals_stepwise_calls(built_lib, tmp_path):
   """generate() (token loop on the device) against the same loop driven from the host
   call by call as Node does (node.py:109-147): same ids, same stop, same state afterwards --

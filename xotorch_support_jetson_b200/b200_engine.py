@@ -112,12 +112,13 @@ class _PinnedPool:
 
 
 class _Request:
-  __slots__ = ("slots", "pos", "tokens", "skip")
+  __slots__ = ("slots", "pos", "tokens", "skip", "last_sample")
 
   def __init__(self, slots: List[int]):
     self.slots = slots
     self.pos = 0          # the reference's curr_pos: counts every prompt slot, padded ones included
     self.skip = [0] * len(slots)   # padded prompt slots of each row (they occupy no KV position here)
+    self.last_sample = None        # (temp, top_k, top_p) of this request's latest sample() call
     # token history per row as Python ints: a decode step appends one id per row, so the
     # ``tokens`` entry of the returned state costs O(B) + a pointer copy, not a fresh
     # ndarray.tolist() of the whole history (1.2 ms per step at 32 x 2100 ids)
@@ -161,6 +162,8 @@ class B200ShardInferenceEngine(InferenceEngine):
     self.direct_host_logits = env.get("XB_API_DIRECT_LOGITS", "1") != "0"   # LM head stores the logits into pinned host memory itself
     self._spec = None          # the decode forward enqueued ahead of the caller's infer_tensor, see sample()
     self.spec_hits = self.spec_misses = 0
+    self._spec_sample = None   # the sampler run enqueued ahead of the caller's sample(), see _speculate_sample()
+    self.sample_spec_hits = 0
     # intra-box hand-off (networking.py): with device_handoff a non-last shard returns a DeviceTensorRef -- the hidden
     # rows stay in HBM -- instead of fp32 numpy; connect_next() / bind_ring() say where the next shard lives
     self.device_handoff = False
@@ -195,7 +198,9 @@ class B200ShardInferenceEngine(InferenceEngine):
       self.rng = torch.Generator(device=st.device)
       self.rng.manual_seed(1234)
       self._stream = torch.cuda.Stream(device=st.device)  # non-default stream: decode steps replay CUDA graphs
-      self._copy_stream = torch.cuda.Stream(device=st.device)   # sampled ids -> host, beside the next step
+      # sampled ids -> host beside the next step; on ring stages also the sampler itself.  High priority: with other
+      # requests' forwards queued back to back, its blocks get the next free SMs instead of waiting for a gap
+      self._copy_stream = torch.cuda.Stream(device=st.device, priority=-1)
 
     await asyncio.get_running_loop().run_in_executor(self.executor, start_model)
     self.shard = shard
@@ -212,7 +217,7 @@ class B200ShardInferenceEngine(InferenceEngine):
     self.rng = torch.Generator(device=stage.device)
     self.rng.manual_seed(1234)
     self._stream = torch.cuda.Stream(device=stage.device)
-    self._copy_stream = torch.cuda.Stream(device=stage.device)   # sampled ids -> host, beside the next step
+    self._copy_stream = torch.cuda.Stream(device=stage.device, priority=-1)   # see ensure_shard
 
   # ------------------------------------------------------------------ intra-box hand-off wiring
   def enable_landing(self, n_slots: Optional[int] = None, rows: Optional[int] = None):
@@ -357,6 +362,13 @@ class B200ShardInferenceEngine(InferenceEngine):
 
     def sample_body():
       st = self.stage
+      params = (float(temp), int(top_k or 0), float(top_p))
+      ss, self._spec_sample = self._spec_sample, None
+      if ss is not None:
+        if ss["ref"]() is x and ss["params"] == params:
+          self.sample_spec_hits += 1       # this very call was enqueued right behind the forward that made x
+          return ss["toks"], ss["ev"]
+        self._rewind_sample(ss)
       owner = None
       ent = self._logits_dev.get(id(x))
       if ent is not None and ent[0]() is x:
@@ -366,31 +378,65 @@ class B200ShardInferenceEngine(InferenceEngine):
       if logits.ndim == 1:
         logits = logits.unsqueeze(0)
       logits.record_stream(torch.cuda.current_stream(st.device))
-      q = None
-      if self.sample_mode == "reference":
-        # the reference draws q ~ Exp(1) of shape [B, vocab] on EVERY call, also at temp 0
-        q = torch.empty((logits.size(0), st.vocab), device=st.device).exponential_(1, generator=self.rng)
-      self.sample_calls += 1
-      # reference semantics at any temperature: logits / max(temp, 1e-5) -> top-k -> softmax -> argmax(p/q)
-      toks = st.sample(logits, temp=max(float(temp), 1e-5), top_k=int(top_k or 0), top_p=top_p, q=q, seed=self.sample_calls)
-      # The next decode step goes onto the stream right behind the sampler (the GPU never waits for
-      # the host); the ids reach the host through a second stream that only waits for the sampler.
-      sampled = torch.cuda.Event()
-      sampled.record(torch.cuda.current_stream(st.device))
-      self._speculate(owner, toks)
-      side = self._copy_stream
-      side.wait_event(sampled)
-      toks.record_stream(side)
-      with torch.cuda.stream(side):
-        host_toks, ev = self._to_host_async(toks)
-      if self._spec is not None and self._spec.get("toks") is None:
-        self._spec["toks"] = host_toks
-      return host_toks, ev
+      req = self.requests.get(owner) if owner is not None else None
+      if req is not None:
+        req.last_sample = params
+      return self._enqueue_sample(logits, owner, *params)
 
     loop = asyncio.get_running_loop()
     host_toks, ev = await loop.run_in_executor(self.executor, sample_wrapper)
     await loop.run_in_executor(self._waiter, ev.synchronize)
     return np.array(host_toks, dtype=np.int32).reshape(-1, 1)
+
+  def _enqueue_sample(self, logits: torch.Tensor, owner: Optional[str], temp: float, top_k: int, top_p: float):
+    """Sampler + (whole-model shard) the next decode step on the current stream; (pinned ids, event)."""
+    st = self.stage
+    q = None
+    if self.sample_mode == "reference":
+      # the reference draws q ~ Exp(1) of shape [B, vocab] on EVERY call, also at temp 0
+      q = torch.empty((logits.size(0), st.vocab), device=st.device).exponential_(1, generator=self.rng)
+    self.sample_calls += 1
+    # reference semantics at any temperature: logits / max(temp, 1e-5) -> top-k -> softmax -> argmax(p/q)
+    toks = st.sample(logits, temp=max(float(temp), 1e-5), top_k=int(top_k or 0), top_p=top_p, q=q, seed=self.sample_calls)
+    # The next decode step goes onto the stream right behind the sampler (the GPU never waits for
+    # the host); the ids reach the host through a second stream that only waits for the sampler.
+    sampled = torch.cuda.Event()
+    sampled.record(torch.cuda.current_stream(st.device))
+    self._speculate(owner, toks)
+    side = self._copy_stream
+    side.wait_event(sampled)
+    toks.record_stream(side)
+    with torch.cuda.stream(side):
+      host_toks, ev = self._to_host_async(toks)
+    if self._spec is not None and self._spec.get("toks") is None:
+      self._spec["toks"] = host_toks
+    return host_toks, ev
+
+  def _speculate_sample(self, request_id: str, req: _Request, host: np.ndarray, logits: torch.Tensor):
+    """Whole-model shard, one request in flight: run the sampler the caller is about to ask for -- with the
+    parameters of its previous sample() call -- right behind the forward that produced these logits, and the next
+    decode step behind that.  The host then only COLLECTS: sample(x) on this array with those parameters returns the
+    ids already on their way, infer_tensor(ids) the forward already running; between a step's logits and the next
+    step's kernels the GPU no longer waits for a host round trip.  Anything else the caller does first un-draws the
+    noise (the reference draws q once per sample() call, in call order) and discards the speculated work, so results
+    are those of the unspeculated path bit for bit.  With more than one request in flight the order of their
+    sample() calls is not known in advance: no sampler speculation then."""
+    import weakref
+    if not self.speculate_next or req.last_sample is None or len(self.requests) != 1 or self.shard is None:
+      return
+    if not (self.shard.is_first_layer() and self.shard.is_last_layer()) or logits.size(0) != len(req.slots):
+      return
+    before = (self.rng.get_state() if self.sample_mode == "reference" else None, self.sample_calls)
+    toks, ev = self._enqueue_sample(logits, request_id, *req.last_sample)
+    self._spec_sample = {"ref": weakref.ref(host), "params": req.last_sample, "toks": toks, "ev": ev, "before": before}
+
+  def _rewind_sample(self, ss: dict):
+    """A speculated sampler run that the caller did not ask for: give its noise back, forget the step enqueued on its ids."""
+    rng_state, calls = ss["before"]
+    if rng_state is not None:
+      self.rng.set_state(rng_state)
+    self.sample_calls = calls
+    self._spec = None
 
   def _speculate(self, request_id: Optional[str], toks: torch.Tensor):
     """Enqueue the decode step the caller is about to ask for (see the module docstring).
@@ -448,6 +494,9 @@ class B200ShardInferenceEngine(InferenceEngine):
 
   def end_request(self, request_id: str):
     req = self.requests.pop(request_id, None)
+    if self._spec_sample is not None:
+      self._rewind_sample(self._spec_sample)
+      self._spec_sample = None
     if self._spec is not None and self._spec["request_id"] == request_id:
       self._spec = None
     if req is not None:
@@ -616,6 +665,11 @@ class B200ShardInferenceEngine(InferenceEngine):
         bsz, s = x.shape[0], x.shape[1]
       else:
         raise ValueError(f"input_data must be 2-D token ids or 3-D hidden states, got ndim={x.ndim}")
+      if self._spec_sample is not None:     # the caller went on without the sample() call that was run ahead
+        ss, self._spec_sample = self._spec_sample, None
+        spec_fwd = self._spec
+        self._rewind_sample(ss)
+        self._spec = spec_fwd                # ... the forward enqueued on those ids is judged by _take_spec as usual
       state_pos = state_position(inference_state)
       req = self.requests.get(request_id)
       # a new request starts with a multi-token input at position 0 (encode() resets the
@@ -667,8 +721,17 @@ class B200ShardInferenceEngine(InferenceEngine):
                                 copy=not (self.device_handoff or self._ring is not None))
       if shard.is_last_layer():
         if host is None:
-          host, ev = self._to_host_async(out)          # fp32 [B, V]
+          # fp32 [B, V] to the host on the side stream: the next request's forward (already queued on this stream
+          # when several are in flight) does not wait behind a 16 MB copy
+          done = torch.cuda.Event()
+          done.record(torch.cuda.current_stream(out.device))
+          side = self._copy_stream
+          side.wait_event(done)
+          out.record_stream(side)
+          with torch.cuda.stream(side):
+            host, ev = self._to_host_async(out)
         self._remember_logits(host, out, request_id)
+        self._speculate_sample(request_id, req, host, out)
         return host, new_state, ev
       if self.device_handoff:
         return self._device_result(out, bsz, s, None), new_state, None   # hidden rows stay in HBM (networking.DeviceTensorRef)
@@ -726,7 +789,9 @@ class B200ShardInferenceEngine(InferenceEngine):
       if req is None or (state_pos == 0) or (state_pos is None and s > 1) or len(req.slots) != bsz:
         req = self._start_request(request_id, bsz)
       pos = req.pos if state_pos is None else int(state_pos)
-      self._spec = self._last_logits = None
+      if self._spec_sample is not None:
+        self._rewind_sample(self._spec_sample)
+      self._spec = self._last_logits = self._spec_sample = None
       self._logits_dev.clear()
       if req.tokens is None or s > 1:
         req.tokens = x.astype(np.int64).tolist()
