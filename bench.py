@@ -624,8 +624,9 @@ def e2e_engine_api(runner, cfg, prompt, K, W):
   return {"value": B * K / dt, "unit": "tok/s", "h2d_bytes_per_step": B * 4, "d2h_bytes_per_step": B * V * 4 + B * 4,
           "api": "B200ShardInferenceEngine.infer_tensor(np ids) -> np fp32 logits [B,V] (written into pinned host memory by the "
                  "LM-head kernel itself); .sample(that array) -> np ids (reference plugin API, host buffers; the logits array "
-                 "handed back to sample() is recognised and not re-uploaded; sample() enqueues the next decode step on the ids "
-                 "it drew, infer_tensor() with those ids collects it)",
+                 "handed back to sample() is recognised and not re-uploaded; with one request in flight the engine runs the sampler "
+                 "(parameters of the previous sample() call) and the next decode step ahead, right behind the forward: "
+                 "sample() and infer_tensor() with the ids it returned collect work already in flight, anything else discards it)",
           "device_loop": {"value": loop_rate, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": B * 4,
                           "api": "B200ShardInferenceEngine.generate(np prompt ids, on_token=cb): sample->forward chained on the "
                                  "device, ids streamed to a pinned table, reference-semantics sampler (top-k 35, q noise) every step"}}

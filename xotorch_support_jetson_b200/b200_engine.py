@@ -21,7 +21,9 @@ memory, before handing those ids to the caller; ``infer_tensor`` called with exa
 exactly that position returns the result already in flight, anything else discards it (a
 forward at the same position overwrites the KV entry, so nothing has to be undone).  The
 results are those of the unspeculated path bit for bit; ``speculate_next=False`` /
-``XB_API_SPECULATE=0`` turns it off.
+``XB_API_SPECULATE=0`` turns it off.  With ONE request in flight the sampler itself is run ahead as
+well (``_speculate_sample``: the parameters of the request's previous ``sample()`` call), so that in
+a steady infer_tensor / sample loop the host only collects results.
 """
 import asyncio
 import functools
@@ -328,6 +330,17 @@ class B200ShardInferenceEngine(InferenceEngine):
     ev.record(torch.cuda.current_stream(dev.device))
     return arr, ev
 
+  def _logits_to_host_beside(self, out: torch.Tensor):
+    """fp32 [B, V] to the host on the side stream: whatever is queued behind the forward on the main stream -- the
+    sampler and the next step run ahead, another request's forward -- does not wait behind a 16 MB copy."""
+    done = torch.cuda.Event()
+    done.record(torch.cuda.current_stream(out.device))
+    side = self._copy_stream
+    side.wait_event(done)
+    out.record_stream(side)
+    with torch.cuda.stream(side):
+      return self._to_host_async(out)
+
   def _remember_logits(self, host: np.ndarray, dev: torch.Tensor, request_id: str):
     import weakref
     key = id(host)
@@ -341,8 +354,7 @@ class B200ShardInferenceEngine(InferenceEngine):
     buffer itself (xb_forward_host_logits); otherwise a device-to-host copy follows the forward."""
     if not self.direct_host_logits:
       out = st.forward(slots, q_lens, positions, **inp)
-      host, ev = self._to_host_async(out)
-      return out, host, ev
+      return (out,) + self._logits_to_host_beside(out)
     buf, arr = self._pinned.take(torch.float32, (len(slots), st.vocab))
     out = st.forward(slots, q_lens, positions, host_logits=buf, **inp)
     ev = torch.cuda.Event()
@@ -721,15 +733,7 @@ class B200ShardInferenceEngine(InferenceEngine):
                                 copy=not (self.device_handoff or self._ring is not None))
       if shard.is_last_layer():
         if host is None:
-          # fp32 [B, V] to the host on the side stream: the next request's forward (already queued on this stream
-          # when several are in flight) does not wait behind a 16 MB copy
-          done = torch.cuda.Event()
-          done.record(torch.cuda.current_stream(out.device))
-          side = self._copy_stream
-          side.wait_event(done)
-          out.record_stream(side)
-          with torch.cuda.stream(side):
-            host, ev = self._to_host_async(out)
+          host, ev = self._logits_to_host_beside(out)
         self._remember_logits(host, out, request_id)
         self._speculate_sample(request_id, req, host, out)
         return host, new_state, ev
