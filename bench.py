@@ -170,7 +170,7 @@ def run_reference(args):
   times = smp.steps(steps)
   val, per_step = sb * steps / sum(times), sum(times) / steps
   sample = (f"{steps} decode steps of {sb} sequences (one micro-batch of {args.batch}"
-            + (f"; the {args.gpus}-GPU arm keeps {args.gpus} such micro-batches in flight" if args.gpus > 1 else "")
+            + (f"; the {args.gpus}-GPU arm keeps {micro_batches(args)} such micro-batches in flight" if args.gpus > 1 else "")
             + f") at context {args.prompt_len} (synthetic KV cache, no CPU prefill), oracle port in reference-exact mode")
   line = {
     "impl": "reference", "metric": "decode_tok_s", "value": val, "unit": "tok/s", "n_gpus": args.gpus, "steps": steps,
@@ -184,13 +184,18 @@ def run_reference(args):
   print(json.dumps(line), flush=True)
 
 
+def micro_batches(args) -> int:
+  """Micro-batches of `batch` sequences kept in flight: one per pipeline stage unless --micro-batches says otherwise."""
+  return args.micro_batches if args.micro_batches > 0 else args.gpus
+
+
 def workload_config(args):
   return {"workload": f"{args.model} bf16 random-init, {args.prompt_len}-token synthetic prompts, greedy decode from context "
-                      f"{args.prompt_len}, batch {args.batch} per micro-batch x {args.gpus} micro-batches in flight "
+                      f"{args.prompt_len}, batch {args.batch} per micro-batch x {micro_batches(args)} micro-batches in flight "
                       f"({args.gpus}-stage layer pipeline, "
                       + ("stage boundaries at half-layer granularity balanced by bytes per step)" if args.gpus > 1 and os.environ.get("XB_HALF_LAYERS", "1") != "0"
                          else "whole-layer ring partition)"),
-          "global_batch": args.batch * args.gpus, "prompt_len": args.prompt_len, "parallelism": f"pp{args.gpus}",
+          "global_batch": args.batch * micro_batches(args), "prompt_len": args.prompt_len, "parallelism": f"pp{args.gpus}",
           "l2_policy": "inputs larger than L2 (weights 15 GB per pass >> 126 MB L2)"}
 
 
@@ -225,7 +230,7 @@ def run_b200(args):
   with tempfile.TemporaryDirectory() as td:
     (Path(td) / "config.json").write_text(json.dumps(hf_cfg))
     cfg = mc.load_model_config(Path(td) / "config.json")
-  B, M, L = args.batch, world, args.prompt_len
+  B, M, L = args.batch, micro_batches(args), args.prompt_len
   K, W = args.steps, args.warmup
   peaks = measured_peaks()
   R = max(1, args.reps)
@@ -562,7 +567,18 @@ def e2e_ring(runner, model_id, cfg, prompts, K, W, dist, rank, world):
     await loop.run_in_executor(None, lambda: dist.barrier(group=sync))   # the other ranks keep serving until rank 0 is done
     await node.stop()
 
-  asyncio.run(run())
+  if os.environ.get("XB_PROFILE_RING") == "1" and rank in (0, world - 1):   # where a hop's host time goes (developer aid)
+    import cProfile, pstats, io
+    pr = cProfile.Profile()
+    pr.enable()
+    asyncio.run(run())
+    pr.disable()
+    buf = io.StringIO()
+    pstats.Stats(pr, stream=buf).sort_stats("tottime").print_stats(35)
+    (ROOT / "gpurun_out").mkdir(exist_ok=True)
+    (ROOT / "gpurun_out" / f"ring_profile_rank{rank}.txt").write_text(buf.getvalue())
+  else:
+    asyncio.run(run())
   torch.cuda.synchronize()
   per_rank = [None] * world
   dist.all_gather_object(per_rank, {k: (round(statistics.median(v) * 1e3, 3) if v else None) for k, v in prof.items()})
@@ -644,6 +660,8 @@ def main():
   ap.add_argument("--max-batch-tokens", type=int, default=8192)
   ap.add_argument("--ref-batch", type=int, default=BATCH, help="sequences per step of the CPU arm (the named batch)")
   ap.add_argument("--cpu-steps", type=int, default=3)
+  ap.add_argument("--micro-batches", type=int, default=int(os.environ.get("XB_BENCH_MICRO_BATCHES", "0")),
+                  help="micro-batches in flight (default: one per GPU)")
   ap.add_argument("--reps", type=int, default=5, help="the K-step timed region is repeated this often; the median is reported")
   ap.add_argument("--no-cpu-baseline", action="store_true")
   args = ap.parse_args()
