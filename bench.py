@@ -546,7 +546,8 @@ def e2e_ring(runner, model_id, cfg, prompts, K, W, dist, rank, world):
 
   async def run():
     loop = asyncio.get_running_loop()
-    node = build_rank_node(eng, dist, rank, world, ctrl_group=ctrl, data_group=None, max_generate_tokens=n_gen, shard_map=shard_map)
+    node = build_rank_node(eng, dist, rank, world, ctrl_group=ctrl, data_group=None, max_generate_tokens=n_gen, shard_map=shard_map,
+                           landing=(M, B) if os.environ.get("XB_RING_LANDING", "1") != "0" else None)
     await node.start()
     if rank == 0:
       left = set(range(M))
@@ -580,6 +581,16 @@ def e2e_ring(runner, model_id, cfg, prompts, K, W, dist, rank, world):
   else:
     asyncio.run(run())
   torch.cuda.synchronize()
+  from xotorch_support_jetson_b200 import networking as _nw
+  if _nw.TRACE is not None:
+    (ROOT / "gpurun_out").mkdir(exist_ok=True)
+    (ROOT / "gpurun_out" / f"ring_trace_rank{rank}.json").write_text(json.dumps(_nw.TRACE))
+    gt = getattr(eng, "_gpu_trace", [])
+    rows = [(round(a.elapsed_time(b) * 1e3, 1), round(b.elapsed_time(gt[i + 1][0]) * 1e3, 1) if i + 1 < len(gt) else None) for i, (a, b) in enumerate(gt)]
+    (ROOT / "gpurun_out" / f"ring_gpu_rank{rank}.json").write_text(json.dumps(rows))
+    gs = getattr(eng, "_gpu_trace_s", [])
+    if gs:
+      (ROOT / "gpurun_out" / f"ring_gpu_sample_rank{rank}.json").write_text(json.dumps([round(a.elapsed_time(b) * 1e3, 1) for a, b in gs]))
   per_rank = [None] * world
   dist.all_gather_object(per_rank, {k: (round(statistics.median(v) * 1e3, 3) if v else None) for k, v in prof.items()})
   if rank != 0:

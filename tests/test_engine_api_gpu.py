@@ -241,6 +241,47 @@ def test_sampler_speculation_is_invisible(built_lib, tmp_path):
   asyncio.run(run())
 
 
+def test_ring_last_stage_sampler_speculation_is_invisible(built_lib, tmp_path):
+  """The last stage of a ring with two requests in flight: the sampler of each is run ahead in forward order
+  (B200ShardInferenceEngine._speculate_ring_sample).  Ids and logits must equal the unspeculated engine's when the
+  sample() calls come in that order (hits), in the opposite order (all run-ahead noise given back), when a request's
+  parameters change, and when one request ends with a sampler still run ahead."""
+  from xotorch_support_jetson_b200.shard import Shard
+  mid, nl = "llama-3.2-tiny", 4
+  sh = Shard(mid, 2, nl - 1, nl)
+  rs = np.random.RandomState(4)
+  hid = lambda b, s: (rs.randn(b, s, 256) * 0.5).astype(np.float32)
+  script_inputs = {"a": [hid(2, 9)] + [hid(2, 1) for _ in range(8)], "b": [hid(1, 5)] + [hid(1, 1) for _ in range(8)]}
+
+  async def script(eng):
+    rec, lg, st = [], {}, {"a": None, "b": None}
+    for step in range(8):
+      for rid in ("a", "b"):
+        lg[rid], st[rid] = await eng.infer_tensor(rid, sh, script_inputs[rid][step], st[rid])
+        rec.append(lg[rid].copy())
+      order = ("b", "a") if step in (3, 6) else ("a", "b")
+      for rid in order:
+        kw = dict(temp=0.8, top_k=20) if (step < 5 or rid == "a") else dict(temp=0.4, top_k=3)
+        rec.append((await eng.sample(lg[rid], **kw)).copy())
+    lg["a"], st["a"] = await eng.infer_tensor("a", sh, script_inputs["a"][8], st["a"])
+    lg["b"], st["b"] = await eng.infer_tensor("b", sh, script_inputs["b"][8], st["b"])
+    eng.end_request("a")                                     # a's sampler was run ahead and is never asked for
+    rec.append((await eng.sample(lg["b"], temp=0.4, top_k=3)).copy())
+    eng.end_request("b")
+    return rec
+
+  async def run():
+    on, off = _engine(tmp_path, speculate_next=True), _engine(tmp_path, speculate_next=False)
+    r_on, r_off = await script(on), await script(off)
+    assert len(r_on) == len(r_off)
+    for i, (x, y) in enumerate(zip(r_on, r_off)):
+      assert x.shape == y.shape and np.array_equal(x, y), f"record {i} differs with sampler speculation on"
+    assert off.sample_spec_hits == 0 and on.sample_spec_hits >= 6, on.sample_spec_hits
+    assert on.sample_calls == off.sample_calls
+
+  asyncio.run(run())
+
+
 def test_generate_device_loop_equals_stepwise_calls(built_lib, tmp_path):
   """generate() (token loop on the device) against the same loop driven from the host
   call by call as Node does (node.py:109-147): same ids, same stop, same state afterwards --

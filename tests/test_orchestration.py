@@ -110,7 +110,7 @@ def _ring_worker(rank, world, port, ret):
     (sent by the engine on the data channel), arrive as a reference that the engine receives."""
     _ring = None
 
-    def bind_ring(self, ch):
+    def bind_ring(self, ch, sends=True):
       self._ring = ch
 
     async def infer_tensor(self, request_id, shard, input_data, inference_state=None):

@@ -26,6 +26,7 @@ well (``_speculate_sample``: the parameters of the request's previous ``sample()
 a steady infer_tensor / sample loop the host only collects results.
 """
 import asyncio
+import collections
 import functools
 import warnings
 import os
@@ -38,7 +39,8 @@ import torch
 
 from .inference_engine import InferenceEngine
 from .model_config import load_model_config
-from .networking import DeviceTensorRef
+from . import networking as _nw
+from .networking import DeviceTensorRef, trace
 from .shard import Shard
 from .stage import StageRuntime
 from .synth import SyntheticTokenizer
@@ -165,6 +167,7 @@ class B200ShardInferenceEngine(InferenceEngine):
     self._spec = None          # the decode forward enqueued ahead of the caller's infer_tensor, see sample()
     self.spec_hits = self.spec_misses = 0
     self._spec_sample = None   # the sampler run enqueued ahead of the caller's sample(), see _speculate_sample()
+    self._ring_specs = collections.deque()   # the same for a ring's last stage: one per request in flight, in forward order
     self.sample_spec_hits = 0
     # intra-box hand-off (networking.py): with device_handoff a non-last shard returns a DeviceTensorRef -- the hidden
     # rows stay in HBM -- instead of fp32 numpy; connect_next() / bind_ring() say where the next shard lives
@@ -177,6 +180,7 @@ class B200ShardInferenceEngine(InferenceEngine):
     self._ho_next = 0               # round-robin landing slot + the flag value last written to each slot
     self._ho_value: List[int] = []
     self._ring = None               # networking.RingChannel when the next shard is another process (torchrun)
+    self._ring_landing = None       # (slots, rows) of the next rank's landing buffers once connect_ring_landing mapped them
 
   # ------------------------------------------------------------------ shard / weights
   async def ensure_shard(self, shard: Shard):
@@ -203,6 +207,7 @@ class B200ShardInferenceEngine(InferenceEngine):
       # sampled ids -> host beside the next step; on ring stages also the sampler itself.  High priority: with other
       # requests' forwards queued back to back, its blocks get the next free SMs instead of waiting for a gap
       self._copy_stream = torch.cuda.Stream(device=st.device, priority=-1)
+      self._logits_stream = torch.cuda.Stream(device=st.device, priority=-1)
 
     await asyncio.get_running_loop().run_in_executor(self.executor, start_model)
     self.shard = shard
@@ -220,6 +225,7 @@ class B200ShardInferenceEngine(InferenceEngine):
     self.rng.manual_seed(1234)
     self._stream = torch.cuda.Stream(device=stage.device)
     self._copy_stream = torch.cuda.Stream(device=stage.device, priority=-1)   # see ensure_shard
+    self._logits_stream = torch.cuda.Stream(device=stage.device, priority=-1)
 
   # ------------------------------------------------------------------ intra-box hand-off wiring
   def enable_landing(self, n_slots: Optional[int] = None, rows: Optional[int] = None):
@@ -237,11 +243,37 @@ class B200ShardInferenceEngine(InferenceEngine):
     self._next_epoch = None
     self.device_handoff = True
 
-  def bind_ring(self, channel):
+  def bind_ring(self, channel, sends: bool = True):
     """The next shard lives in another process of a torchrun ring: hidden rows leave over the channel's data
-    plane (NCCL), sent by this engine on its own stream right behind the forward that made them."""
+    plane (NCCL), sent by this engine on its own stream right behind the forward that made them -- or, once
+    ``connect_ring_landing`` has mapped the next rank's landing buffers, decode steps are stored there by this
+    stage's last kernel.  sends=False: the last stage, which only receives."""
     self._ring = channel
-    self.device_handoff = True
+    self.device_handoff = bool(sends)
+
+  def ring_landing_handles(self, n_slots: int, rows: int) -> Optional[tuple]:
+    """CUDA IPC handles of this stage's landing buffers for the PREVIOUS rank of the ring (created on first use; a
+    stage that already has buffers of another geometry, or none that can be exported, answers None)."""
+    st = self.stage
+    if st is None:
+      return None
+    if st.ho_geometry is None:
+      st.handoff_create(n_slots, rows, ipc=True)
+    if st.ho_geometry != (int(n_slots), int(rows)) or st.ho_handles is None:
+      return None
+    return st.ho_handles
+
+  def connect_ring_landing(self, next_handles: Optional[tuple], n_slots: int, rows: int):
+    """Map the NEXT rank's landing buffers (its ``ring_landing_handles``); decode steps of at most ``rows`` sequences
+    then leave through them, one slot per request in flight (at most ``n_slots``), everything else over the data plane."""
+    st = self.stage
+    if st is None or st.is_last or next_handles is None or st.ho_geometry != (int(n_slots), int(rows)):
+      return
+    if not st.ho_connected:
+      st.handoff_connect(*next_handles)
+    self._ring_landing = (int(n_slots), int(rows))
+    self._ring_slot_of: dict = {}      # request id -> its slot in the next rank's buffers
+    self._ring_slots_free = list(range(int(n_slots)))[::-1]
 
   def _stage_changed(self):
     self._landing_epoch += 1
@@ -262,11 +294,22 @@ class B200ShardInferenceEngine(InferenceEngine):
     elif geo != (n_slots, rows):
       raise RuntimeError(f"hand-off geometry {geo} of this stage differs from the {(n_slots, rows)} the next stage uses")
 
-  def _landing_out(self, bsz: int):
+  def _landing_out(self, bsz: int, request_id: Optional[str] = None):
     """(slot, value) in the next engine's landing buffers for a decode step of ``bsz`` rows, or None when that
     path is not available (then the rows travel as a device tensor).  Connects on first use."""
     nxt = self._next_engine
     st = self.stage
+    if self._ring_landing is not None and st is not None and not st.is_last:
+      # process-per-GPU ring: one slot per request (a request has one step in flight, so its slot is free again
+      # by the time its next step arrives here); the flag value of a slot only grows
+      if bsz > self._ring_landing[1]:
+        return None
+      slot = self._ring_slot_of.get(request_id)
+      if slot is None:
+        if not self._ring_slots_free:
+          return None
+        slot = self._ring_slot_of[request_id] = self._ring_slots_free.pop()
+      return slot, st.ho_sent.get(slot, 0) + 1
     if nxt is None or st is None or st.is_last or nxt.stage is None or getattr(nxt, "_landing_ready", None) is None:
       return None
     if bsz > nxt.landing_rows or nxt.stage.dim != st.dim:
@@ -325,7 +368,14 @@ class B200ShardInferenceEngine(InferenceEngine):
     read-only array OWNS its buffer (see _PinnedPool); its contents are defined once the returned
     event has completed."""
     buf, arr = self._pinned.take(dev.dtype, dev.shape)
-    buf.copy_(dev, non_blocking=True)
+    if dev.dim() >= 2 and dev.is_contiguous() and dev.numel() * dev.element_size() > (4 << 20) and dev.size(0) >= 8:
+      # a large copy in pieces: a few ids on their way to the host from another stream (the sampler's) then wait for
+      # one piece of the copy engine's queue, not for all 16 MB
+      step = -(-dev.size(0) // 8)
+      for r0 in range(0, dev.size(0), step):
+        buf[r0:r0 + step].copy_(dev[r0:r0 + step], non_blocking=True)
+    else:
+      buf.copy_(dev, non_blocking=True)
     ev = torch.cuda.Event()
     ev.record(torch.cuda.current_stream(dev.device))
     return arr, ev
@@ -335,7 +385,9 @@ class B200ShardInferenceEngine(InferenceEngine):
     sampler and the next step run ahead, another request's forward -- does not wait behind a 16 MB copy."""
     done = torch.cuda.Event()
     done.record(torch.cuda.current_stream(out.device))
-    side = self._copy_stream
+    # not the sampler's stream: this copy waits for a forward that may be queued behind other requests' forwards, and a
+    # sampler call for an EARLIER request enqueued after it must not wait with it
+    side = self._logits_stream
     side.wait_event(done)
     out.record_stream(side)
     with torch.cuda.stream(side):
@@ -351,8 +403,12 @@ class B200ShardInferenceEngine(InferenceEngine):
   def _forward_logits(self, st: StageRuntime, slots, q_lens, positions, **inp):
     """One native forward on a last shard whose logits go to the host: (device logits, numpy
     view, event).  With ``direct_host_logits`` the LM-head kernel stores them into the pinned
-    buffer itself (xb_forward_host_logits); otherwise a device-to-host copy follows the forward."""
-    if not self.direct_host_logits:
+    buffer itself (xb_forward_host_logits) -- the shortest path to the host when this request is the only one,
+    since the stores overlap the LM head's own weight stream.  With several requests in flight the next request's
+    forward is already queued behind this one, and 16 MB of stores over PCIe inside the LM-head kernel would hold it
+    back (measured 0.45 ms per hop on the last stage of a 2-GPU ring): then a copy on the side stream follows the
+    forward instead and overlaps the next one."""
+    if not self.direct_host_logits or len(self.requests) > 1:
       out = st.forward(slots, q_lens, positions, **inp)
       return (out,) + self._logits_to_host_beside(out)
     buf, arr = self._pinned.take(torch.float32, (len(slots), st.vocab))
@@ -369,8 +425,11 @@ class B200ShardInferenceEngine(InferenceEngine):
       # may already hold ANOTHER request's forward, and ids that only need this request's finished logits would
       # wait a whole stage time behind it (measured 3 ms per hop at 2 x 32 sequences on a 2-GPU ring).
       own = self.shard is not None and self.shard.is_first_layer() and self.shard.is_last_layer() and self.speculate_next
+      trace("sample.worker.begin")
       with torch.cuda.stream(self._stream if own else self._copy_stream):
-        return sample_body()
+        r = sample_body()
+      trace(f"sample.worker.end.hits{self.sample_spec_hits}")
+      return r
 
     def sample_body():
       st = self.stage
@@ -381,6 +440,13 @@ class B200ShardInferenceEngine(InferenceEngine):
           self.sample_spec_hits += 1       # this very call was enqueued right behind the forward that made x
           return ss["toks"], ss["ev"]
         self._rewind_sample(ss)
+      if self._ring_specs:
+        head = self._ring_specs[0]
+        if head["ref"]() is x and head["params"] == params:
+          self._ring_specs.popleft()
+          self.sample_spec_hits += 1
+          return head["toks"], head["ev"]
+        self._drop_ring_specs()            # the calls come in another order than the forwards did: un-draw all of them
       owner = None
       ent = self._logits_dev.get(id(x))
       if ent is not None and ent[0]() is x:
@@ -397,7 +463,9 @@ class B200ShardInferenceEngine(InferenceEngine):
 
     loop = asyncio.get_running_loop()
     host_toks, ev = await loop.run_in_executor(self.executor, sample_wrapper)
-    await loop.run_in_executor(self._waiter, ev.synchronize)
+    if not ev.query():
+      trace("sample.wait")
+      await loop.run_in_executor(self._waiter, ev.synchronize)
     return np.array(host_toks, dtype=np.int32).reshape(-1, 1)
 
   def _enqueue_sample(self, logits: torch.Tensor, owner: Optional[str], temp: float, top_k: int, top_p: float):
@@ -441,6 +509,34 @@ class B200ShardInferenceEngine(InferenceEngine):
     before = (self.rng.get_state() if self.sample_mode == "reference" else None, self.sample_calls)
     toks, ev = self._enqueue_sample(logits, request_id, *req.last_sample)
     self._spec_sample = {"ref": weakref.ref(host), "params": req.last_sample, "toks": toks, "ev": ev, "before": before}
+
+  def _speculate_ring_sample(self, request_id: str, req: _Request, host: np.ndarray, logits: torch.Tensor):
+    """The last stage of a ring, any number of requests in flight: their logits leave this engine in the order of
+    their forwards, and a node samples each as soon as it has them -- so the sampler of every request is run ahead in
+    that order (right behind its forward, beside the 16 MB logits copy instead of a host round trip after it) and
+    sample() collects.  The first call that does not match the oldest run-ahead sampler gives ALL their noise back
+    (draws happen in call order) and is computed as asked."""
+    import weakref
+    if not self.speculate_next or req.last_sample is None or self.shard is None or logits.size(0) != len(req.slots):
+      return
+    if self.shard.is_first_layer() or not self.shard.is_last_layer():
+      return
+    before = (self.rng.get_state() if self.sample_mode == "reference" else None, self.sample_calls)
+    # on the forward's own stream, whose tail at this moment IS that forward: ~50 us there; beside another request's
+    # forward (the sampler's stream) the same kernels were measured at ~600 us, starved of bandwidth
+    if _nw.TRACE is not None:
+      e0 = torch.cuda.Event(enable_timing=True); e0.record()
+    toks, ev = self._enqueue_sample(logits, request_id, *req.last_sample)
+    if _nw.TRACE is not None:
+      e1 = torch.cuda.Event(enable_timing=True); e1.record()
+      self._gpu_trace_s = getattr(self, "_gpu_trace_s", []) + [(e0, e1)]
+    self._ring_specs.append({"ref": weakref.ref(host), "params": req.last_sample, "toks": toks, "ev": ev, "before": before,
+                             "request_id": request_id})
+
+  def _drop_ring_specs(self):
+    if self._ring_specs:
+      self._rewind_sample(self._ring_specs[0])
+      self._ring_specs.clear()
 
   def _rewind_sample(self, ss: dict):
     """A speculated sampler run that the caller did not ask for: give its noise back, forget the step enqueued on its ids."""
@@ -511,6 +607,10 @@ class B200ShardInferenceEngine(InferenceEngine):
       self._spec_sample = None
     if self._spec is not None and self._spec["request_id"] == request_id:
       self._spec = None
+    if any(sp["request_id"] == request_id for sp in self._ring_specs):
+      self._drop_ring_specs()
+    if self._ring_landing is not None and request_id in self._ring_slot_of:
+      self._ring_slots_free.append(self._ring_slot_of.pop(request_id))
     if req is not None:
       for s in req.slots:
         self.stage.release_slot(s)
@@ -615,7 +715,7 @@ class B200ShardInferenceEngine(InferenceEngine):
     st = self.stage
     shape = (bsz, s, st.dim)
     if landing_out is not None:
-      return DeviceTensorRef(shape, landing=landing_out)
+      return DeviceTensorRef(shape, landing=landing_out, recv=("landed",) if self._ring_landing is not None else None)
     if self._ring is not None:
       self._ring.send_rows(out.reshape(bsz * s, -1))    # enqueued on this stream, right behind the forward
       return DeviceTensorRef(shape, tensor=out, recv=("sent",))
@@ -623,21 +723,29 @@ class B200ShardInferenceEngine(InferenceEngine):
     ev.record(torch.cuda.current_stream(st.device))
     return DeviceTensorRef(shape, tensor=out, event=ev)
 
-  def _forward_decode_hop(self, st: StageRuntime, req: _Request, bsz: int, pos: int, dev_in, is_tokens: bool, landing_in):
+  def _forward_decode_hop(self, st: StageRuntime, req: _Request, bsz: int, pos: int, dev_in, is_tokens: bool, landing_in,
+                          request_id: Optional[str] = None):
     """One decode step of a ring stage: input = ids / hidden rows / this GPU's landing slot, output = logits (last
     shard), hidden rows, or -- when the next engine's landing buffers are connected -- nothing but a (slot, value)."""
     positions = self._positions(req, pos)
-    landing_out = None if self.shard.is_last_layer() else self._landing_out(bsz)
+    landing_out = None if self.shard.is_last_layer() else self._landing_out(bsz, request_id)
     inp = {}
     if landing_in is None:
       flat = dev_in.reshape(-1) if is_tokens else dev_in.reshape(bsz, -1)
       inp = {"tokens": flat} if is_tokens else {"hidden": flat.contiguous()}
-    if landing_in is None and landing_out is None:
-      return st.forward(req.slots, [1] * bsz, positions, **inp), None
-    si, vi = landing_in if landing_in is not None else (-1, 0)
-    so, vo = landing_out if landing_out is not None else (-1, 0)
-    out = st.forward(req.slots, [1] * bsz, positions, handoff=(si, vi, so, vo), **inp)
-    return out, landing_out
+    ho = None
+    if landing_in is not None or landing_out is not None:
+      si, vi = landing_in if landing_in is not None else (-1, 0)
+      so, vo = landing_out if landing_out is not None else (-1, 0)
+      ho = (si, vi, so, vo)
+    if _nw.TRACE is not None:     # developer aid: device time of the hop's forward and the gap to the next one
+      e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+      e0.record()
+      out = st.forward(req.slots, [1] * bsz, positions, handoff=ho, **inp)
+      e1.record()
+      self._gpu_trace = getattr(self, "_gpu_trace", []) + [(e0, e1)]
+      return out, landing_out
+    return st.forward(req.slots, [1] * bsz, positions, handoff=ho, **inp), landing_out
 
   def _prompt_keep_mask(self, x: np.ndarray, inference_state: Optional[dict], bsz: int, s: int, pos: int) -> Optional[np.ndarray]:
     """bool [bsz, s] of the prompt slots that are NOT padding, or None when the prompt holds no pad
@@ -664,8 +772,11 @@ class B200ShardInferenceEngine(InferenceEngine):
     await self.ensure_shard(shard)
 
     def infer_wrapper():
+      trace("eng.worker.begin", request_id)
       with torch.cuda.stream(self._stream):
-        return infer_body()
+        r = infer_body()
+      trace("eng.worker.end", request_id)
+      return r
 
     def infer_body():
       st = self.stage
@@ -713,7 +824,7 @@ class B200ShardInferenceEngine(InferenceEngine):
       if keep is not None:
         out = self._forward_padded_prompt(st, req, dev_in, keep, x.ndim == 2)
       elif s == 1 and (landing_in is not None or (self.device_handoff and not shard.is_last_layer())) and bsz <= st.max_batch_tokens:
-        return finish_hop(req, *self._forward_decode_hop(st, req, bsz, pos, dev_in, x.ndim == 2, landing_in), bsz, pos)
+        return finish_hop(req, *self._forward_decode_hop(st, req, bsz, pos, dev_in, x.ndim == 2, landing_in, request_id), bsz, pos)
       else:
         out = self._forward_chunked(st, req, dev_in, bsz, s, pos, x.ndim == 2)
       if isinstance(out, tuple):
@@ -736,6 +847,7 @@ class B200ShardInferenceEngine(InferenceEngine):
           host, ev = self._logits_to_host_beside(out)
         self._remember_logits(host, out, request_id)
         self._speculate_sample(request_id, req, host, out)
+        self._speculate_ring_sample(request_id, req, host, out)
         return host, new_state, ev
       if self.device_handoff:
         return self._device_result(out, bsz, s, None), new_state, None   # hidden rows stay in HBM (networking.DeviceTensorRef)
@@ -748,7 +860,9 @@ class B200ShardInferenceEngine(InferenceEngine):
     loop = asyncio.get_running_loop()
     result, new_state, ev = await loop.run_in_executor(self.executor, infer_wrapper)
     if ev is not None:
-      await loop.run_in_executor(self._waiter, ev.synchronize)
+      if not ev.query():
+        await loop.run_in_executor(self._waiter, ev.synchronize)
+      trace("eng.gpu.done", request_id)
     return result, new_state
 
   # ------------------------------------------------------------------ device-resident token loop

@@ -23,7 +23,9 @@ on whatever the engine returns.
 """
 import asyncio
 import json
+import os
 import threading
+import time
 from abc import ABC, abstractmethod
 from typing import List, Optional
 
@@ -215,6 +217,15 @@ class BoxDiscovery(Discovery):
 
 # ----------------------------------------------------------------------------- one process per GPU (torchrun)
 KIND_PROMPT, KIND_TENSOR, KIND_RESULT, KIND_STATUS, KIND_STOP = 1, 2, 3, 4, 5
+
+# developer aid: XB_RING_TRACE=1 keeps (monotonic ns, tag, request id) per hop event; bench.py writes them out per rank
+TRACE = [] if os.environ.get("XB_RING_TRACE") == "1" else None
+
+
+def trace(tag: str, rid=None):
+  if TRACE is not None:
+    TRACE.append((time.monotonic_ns(), tag, rid))
+
 _HDR = 8   # int64 words: kind, meta bytes, payload kind (0 none, 1 int ids, 2 fp32 numpy, 3 device rows over the data channel), ndim, d0, d1, d2, size of a second message (0: all inline)
 
 
@@ -260,8 +271,10 @@ class RingChannel:
     frame[:8 * _HDR] = np.asarray(hdr, dtype=np.int64).tobytes()
     if inline:
       frame[8 * _HDR:8 * _HDR + len(rest)] = rest
+    trace("send.begin", meta.get("request_id"))
     with self._send_lock:
       self.dist.send(torch.frombuffer(frame, dtype=torch.uint8), dst=self.next_rank, group=self.ctrl_group)
+      trace("send.end", meta.get("request_id"))
       if not inline:
         self.dist.send(torch.frombuffer(bytearray(rest), dtype=torch.uint8), dst=self.next_rank, group=self.ctrl_group)
 
@@ -362,18 +375,28 @@ class RingPeerHandle(PeerHandle):
     meta = {"request_id": request_id, "shard": shard.to_dict(), "state": self._state_for_the_wire(tensor, inference_state)}
     loop = asyncio.get_running_loop()
     if isinstance(tensor, DeviceTensorRef):
-      if tensor.recv is None or tensor.recv[0] != "sent":
+      if tensor.recv is None or tensor.recv[0] not in ("sent", "landed"):
         raise ValueError("a DeviceTensorRef that crosses processes must come from an engine bound to this ring "
                          "(B200ShardInferenceEngine.bind_ring): its rows are sent by the engine, on its stream")
-      await loop.run_in_executor(None, lambda: self._ch.send_message(KIND_TENSOR, meta, device_rows=tensor.shape))
+      if tensor.recv[0] == "landed":      # stored into the next rank's landing buffer by the producer's own kernel
+        meta["landing"] = [int(tensor.landing[0]), int(tensor.landing[1])]
+      # one fixed-size frame into the socket buffer: cheaper inline than a thread hop
+      self._ch.send_message(KIND_TENSOR, meta, device_rows=tensor.shape)
     else:
-      await loop.run_in_executor(None, lambda: self._ch.send_message(KIND_TENSOR, meta, payload=np.asarray(tensor)))
+      arr = np.asarray(tensor)
+      if arr.size <= 512:     # ids of a decode step: one frame, sent inline like the header of device rows
+        self._ch.send_message(KIND_TENSOR, meta, payload=arr)
+      else:
+        await loop.run_in_executor(None, lambda: self._ch.send_message(KIND_TENSOR, meta, payload=arr))
     return None
 
   async def send_result(self, request_id: str, result: List[int], is_finished: bool) -> None:
     if self._reachable():
       meta = {"request_id": request_id, "result": [int(t) for t in result], "is_finished": bool(is_finished)}
-      await asyncio.get_running_loop().run_in_executor(None, self._ch.send_message, KIND_RESULT, meta)
+      if len(meta["result"]) <= 512:
+        self._ch.send_message(KIND_RESULT, meta)
+      else:
+        await asyncio.get_running_loop().run_in_executor(None, self._ch.send_message, KIND_RESULT, meta)
 
   async def send_opaque_status(self, request_id: str, status: str) -> None:
     pass   # node status broadcasts feed the reference's TUI / download view: nothing consumes them inside a box
@@ -414,6 +437,7 @@ class RingServer(Server):
   def _serve(self):
     while True:
       kind, meta, payload = self.ch.recv_message()
+      trace(f"recv.{kind}", meta.get("request_id"))
       if kind == KIND_STOP:
         self.stopped.set()
         return
@@ -421,6 +445,7 @@ class RingServer(Server):
 
   def _dispatch(self, kind: int, meta: dict, payload):
     node = self.node
+    trace(f"dispatch.{kind}", meta.get("request_id"))
     if kind == KIND_RESULT:
       node.on_token.trigger_all(meta["request_id"], meta["result"], meta["is_finished"])
       return
@@ -428,5 +453,10 @@ class RingServer(Server):
     if kind == KIND_PROMPT:
       asyncio.create_task(node.process_prompt(shard, meta["prompt"], meta["request_id"], meta.get("state")))
     elif kind == KIND_TENSOR:
-      tensor = payload if isinstance(payload, np.ndarray) else DeviceTensorRef(payload, recv=(self.ch.prev_rank,))
+      if isinstance(payload, np.ndarray):
+        tensor = payload
+      elif meta.get("landing") is not None:
+        tensor = DeviceTensorRef(payload, landing=(int(meta["landing"][0]), int(meta["landing"][1])))
+      else:
+        tensor = DeviceTensorRef(payload, recv=(self.ch.prev_rank,))
       asyncio.create_task(node.process_tensor(shard, tensor, meta["request_id"], meta.get("state")))

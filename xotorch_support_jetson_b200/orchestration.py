@@ -25,6 +25,7 @@ from typing import Callable, Dict, List, Optional, Tuple
 
 import numpy as np
 
+from .networking import trace
 from .shard import Shard
 from .topology import DeviceCapabilities, Topology, b200_device_capabilities, map_partitions_to_shards
 
@@ -208,7 +209,9 @@ class BoxNode:
     shard = self.get_current_shard(base_shard)
     try:
       self.outstanding_requests[request_id] = "processing"
+      trace("infer.begin", request_id)
       result, inference_state = await self.inference_engine.infer_tensor(request_id, shard, tensor, inference_state)
+      trace("infer.end", request_id)
       return await self.process_inference_result(shard, result, request_id, inference_state)
     except Exception as e:
       self.outstanding_requests.pop(request_id, None)
@@ -224,6 +227,7 @@ class BoxNode:
     is_finished = len(buf) >= self.max_generate_tokens
     if shard.is_last_layer() and not is_finished:
       token = await self.inference_engine.sample(result, temp=self.default_sample_temperature)
+      trace("sample.end", request_id)
       await self.inference_engine.ensure_shard(shard)
       eos = self.inference_engine.tokenizer.eos_token_id
       if token.size == 1:                      # the reference's case: one sequence per request
@@ -350,11 +354,14 @@ def build_box_ring(engines: List, max_generate_tokens: int = 1024, default_sampl
 
 
 def build_rank_node(engine, dist, rank: int, world: int, ctrl_group=None, data_group=None, max_generate_tokens: int = 1024,
-                    default_sample_temperature: float = 0.0, memory_mb: int = 183359, shard_map: Optional[List[Shard]] = None) -> BoxNode:
+                    default_sample_temperature: float = 0.0, memory_mb: int = 183359, shard_map: Optional[List[Shard]] = None,
+                    landing: Optional[Tuple[int, int]] = None) -> BoxNode:
   """This RANK's node of a process-per-GPU ring (torchrun): the other ranks appear as ``RingPeerHandle``s, the
   ``RingServer`` listens to the previous rank, layer ranges as in ``build_box_ring`` (rank i = partition i).
   ``ctrl_group``: a CPU (gloo) group for headers; ``data_group``: where hidden rows travel (NCCL on a GPU box).
-  The engine is bound to the ring so that it sends / receives the rows itself, on its own stream."""
+  The engine is bound to the ring so that it sends / receives the rows itself, on its own stream.
+  ``landing = (slots, rows)``: decode steps of up to ``rows`` sequences, for up to ``slots`` requests in flight, leave
+  through the next rank's landing buffers instead (a collective call: every rank passes the same value)."""
   from .networking import BoxDiscovery, RingChannel, RingPeerHandle, RingServer
   from .topology import RingMemoryWeightedPartitioningStrategy, b200_device_capabilities
   ids = [f"gpu{world - 1 - i:02d}-rank{i}" for i in range(world)]
@@ -364,8 +371,14 @@ def build_rank_node(engine, dist, rank: int, world: int, ctrl_group=None, data_g
                  partitioning_strategy=RingMemoryWeightedPartitioningStrategy(), max_generate_tokens=max_generate_tokens,
                  default_sample_temperature=default_sample_temperature, device_capabilities=caps, device_token_loop=(world == 1),
                  shard_map=shard_map)
-  if world > 1 and rank + 1 < world and hasattr(engine, "bind_ring"):
-    engine.bind_ring(ch)
-  elif world > 1 and hasattr(engine, "_ring"):
-    engine._ring = ch          # the last stage only RECEIVES rows over the data plane (its output is a token id)
+  if world > 1 and hasattr(engine, "bind_ring"):
+    engine.bind_ring(ch, sends=rank + 1 < world)   # the last stage only RECEIVES rows (its output is a token id)
+    if landing is not None and hasattr(engine, "ring_landing_handles"):
+      # decode steps through the next rank's landing buffers (CUDA IPC): every rank exports its own, maps its successor's
+      n_slots, rows = landing
+      mine = engine.ring_landing_handles(n_slots, rows) if rank > 0 else None
+      everyone = [None] * world
+      dist.all_gather_object(everyone, mine, group=ctrl_group)
+      if rank + 1 < world:
+        engine.connect_ring_landing(everyone[rank + 1], n_slots, rows)
   return node

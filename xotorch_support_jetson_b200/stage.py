@@ -95,6 +95,12 @@ class StageRuntime:
     self.page_tokens = page_tokens
     self.dim = config["embed_dim"]
     self.vocab = config["vocab_size"]
+    # hand-off state: (slots, rows) of this stage's landing buffers, their IPC handles, whether the NEXT stage's buffers
+    # are mapped, and the last flag value this stage stored into each of the next stage's slots
+    self.ho_geometry: Optional[tuple] = None
+    self.ho_handles: Optional[tuple] = None
+    self.ho_connected = False
+    self.ho_sent: Dict[int, int] = {}
 
   # -- lifetime
   def close(self):
@@ -218,6 +224,8 @@ class StageRuntime:
       # (slot_in, wait_value, slot_out, signal_value): input from / output to the NVLink landing buffers
       _cabi.check(self.lib.xb_forward_handoff(self._h, C.byref(b), int(handoff[0]), int(handoff[1]), int(handoff[2]),
                                               int(handoff[3]), optr, C.c_void_p(stream)))
+      if sends:
+        self.ho_sent[int(handoff[2])] = int(handoff[3])   # flag value of the NEXT stage's slot once this step has run
       return None if sends else out
     if host_logits is not None:
       # (page-locked, device-addressable memory is checked by the library: Tensor.is_pinned() costs ~30 us here)
@@ -231,12 +239,14 @@ class StageRuntime:
   def handoff_create(self, n_slots: int, rows: int, ipc: bool = True) -> Optional[tuple]:
     """Allocate this stage's landing buffers; returns the two CUDA IPC handles (bytes) for stages in
     other processes, or None with ipc=False (stages of one process connect with handoff_connect_local)."""
+    self.ho_geometry = (int(n_slots), int(rows))
     if not ipc:
       _cabi.check(self.lib.xb_handoff_create(self._h, int(n_slots), int(rows), None, None))
       return None
     hl, hf = C.create_string_buffer(64), C.create_string_buffer(64)
     _cabi.check(self.lib.xb_handoff_create(self._h, int(n_slots), int(rows), hl, hf))
-    return bytes(hl.raw), bytes(hf.raw)
+    self.ho_handles = (bytes(hl.raw), bytes(hf.raw))
+    return self.ho_handles
 
   def handoff_connect_local(self, next_stage: "StageRuntime"):
     """The NEXT stage lives in this process (another GPU, or the same one): store into its landing
@@ -251,6 +261,7 @@ class StageRuntime:
     """Map the NEXT stage's landing buffers (handles from its handoff_create)."""
     hl, hf = C.create_string_buffer(landing_handle, 64), C.create_string_buffer(flag_handle, 64)
     _cabi.check(self.lib.xb_handoff_connect(self._h, hl, hf))
+    self.ho_connected = True
 
   def sample(self, logits: torch.Tensor, temp: float = 0.0, top_k: int = 0, top_p: float = 0.0,
              q: Optional[torch.Tensor] = None, seed: int = 0, out: Optional[torch.Tensor] = None) -> torch.Tensor:
