@@ -28,6 +28,7 @@ a steady infer_tensor / sample loop the host only collects results.
 import asyncio
 import collections
 import functools
+import threading
 import warnings
 import os
 import uuid
@@ -168,6 +169,7 @@ class B200ShardInferenceEngine(InferenceEngine):
     self.spec_hits = self.spec_misses = 0
     self._spec_sample = None   # the sampler run enqueued ahead of the caller's sample(), see _speculate_sample()
     self._ring_specs = collections.deque()   # the same for a ring's last stage: one per request in flight, in forward order
+    self._ring_spec_lock = threading.Lock()  # sample()'s fast path looks at the queue from the event-loop thread
     self.sample_spec_hits = 0
     # intra-box hand-off (networking.py): with device_handoff a non-last shard returns a DeviceTensorRef -- the hidden
     # rows stay in HBM -- instead of fp32 numpy; connect_next() / bind_ring() say where the next shard lives
@@ -368,14 +370,7 @@ class B200ShardInferenceEngine(InferenceEngine):
     read-only array OWNS its buffer (see _PinnedPool); its contents are defined once the returned
     event has completed."""
     buf, arr = self._pinned.take(dev.dtype, dev.shape)
-    if dev.dim() >= 2 and dev.is_contiguous() and dev.numel() * dev.element_size() > (4 << 20) and dev.size(0) >= 8:
-      # a large copy in pieces: a few ids on their way to the host from another stream (the sampler's) then wait for
-      # one piece of the copy engine's queue, not for all 16 MB
-      step = -(-dev.size(0) // 8)
-      for r0 in range(0, dev.size(0), step):
-        buf[r0:r0 + step].copy_(dev[r0:r0 + step], non_blocking=True)
-    else:
-      buf.copy_(dev, non_blocking=True)
+    buf.copy_(dev, non_blocking=True)
     ev = torch.cuda.Event()
     ev.record(torch.cuda.current_stream(dev.device))
     return arr, ev
@@ -389,7 +384,8 @@ class B200ShardInferenceEngine(InferenceEngine):
     # sampler call for an EARLIER request enqueued after it must not wait with it
     side = self._logits_stream
     side.wait_event(done)
-    out.record_stream(side)
+    # (no record_stream: _remember_logits keeps ``out`` for as long as the caller keeps the host array, and the
+    # caller only gets that array once this copy has completed)
     with torch.cuda.stream(side):
       return self._to_host_async(out)
 
@@ -440,13 +436,9 @@ class B200ShardInferenceEngine(InferenceEngine):
           self.sample_spec_hits += 1       # this very call was enqueued right behind the forward that made x
           return ss["toks"], ss["ev"]
         self._rewind_sample(ss)
-      if self._ring_specs:
-        head = self._ring_specs[0]
-        if head["ref"]() is x and head["params"] == params:
-          self._ring_specs.popleft()
-          self.sample_spec_hits += 1
-          return head["toks"], head["ev"]
-        self._drop_ring_specs()            # the calls come in another order than the forwards did: un-draw all of them
+      hit = self._take_ring_spec(x, params, drop_on_miss=True)
+      if hit is not None:
+        return hit
       owner = None
       ent = self._logits_dev.get(id(x))
       if ent is not None and ent[0]() is x:
@@ -462,7 +454,11 @@ class B200ShardInferenceEngine(InferenceEngine):
       return self._enqueue_sample(logits, owner, *params)
 
     loop = asyncio.get_running_loop()
-    host_toks, ev = await loop.run_in_executor(self.executor, sample_wrapper)
+    # the common case on a ring's last stage: this call's sampler already ran (or runs) behind the forward -- nothing
+    # to enqueue, so no trip through the worker either.  (A call for anything but the oldest run-ahead sampler takes
+    # the worker's queue like every call that draws noise, which keeps the draws in call order.)
+    fast = self._take_ring_spec(x, (float(temp), int(top_k or 0), float(top_p)), drop_on_miss=False) if self._ring_specs else None
+    host_toks, ev = fast if fast is not None else await loop.run_in_executor(self.executor, sample_wrapper)
     if not ev.query():
       trace("sample.wait")
       await loop.run_in_executor(self._waiter, ev.synchronize)
@@ -506,7 +502,7 @@ class B200ShardInferenceEngine(InferenceEngine):
       return
     if not (self.shard.is_first_layer() and self.shard.is_last_layer()) or logits.size(0) != len(req.slots):
       return
-    before = (self.rng.get_state() if self.sample_mode == "reference" else None, self.sample_calls)
+    before = (self._noise_mark(), self.sample_calls)
     toks, ev = self._enqueue_sample(logits, request_id, *req.last_sample)
     self._spec_sample = {"ref": weakref.ref(host), "params": req.last_sample, "toks": toks, "ev": ev, "before": before}
 
@@ -521,7 +517,7 @@ class B200ShardInferenceEngine(InferenceEngine):
       return
     if self.shard.is_first_layer() or not self.shard.is_last_layer():
       return
-    before = (self.rng.get_state() if self.sample_mode == "reference" else None, self.sample_calls)
+    before = (self._noise_mark(), self.sample_calls)
     # on the forward's own stream, whose tail at this moment IS that forward: ~50 us there; beside another request's
     # forward (the sampler's stream) the same kernels were measured at ~600 us, starved of bandwidth
     if _nw.TRACE is not None:
@@ -530,19 +526,42 @@ class B200ShardInferenceEngine(InferenceEngine):
     if _nw.TRACE is not None:
       e1 = torch.cuda.Event(enable_timing=True); e1.record()
       self._gpu_trace_s = getattr(self, "_gpu_trace_s", []) + [(e0, e1)]
-    self._ring_specs.append({"ref": weakref.ref(host), "params": req.last_sample, "toks": toks, "ev": ev, "before": before,
-                             "request_id": request_id})
+    with self._ring_spec_lock:
+      self._ring_specs.append({"ref": weakref.ref(host), "params": req.last_sample, "toks": toks, "ev": ev, "before": before,
+                               "request_id": request_id})
+
+  def _take_ring_spec(self, x, params, drop_on_miss: bool):
+    """The oldest run-ahead sampler if it is the one for ``x`` with these parameters: (pinned ids, event).  Otherwise
+    None -- and, when asked (the engine's worker, about to draw noise for this call), all run-ahead draws are given
+    back first: the calls come in another order than the forwards did."""
+    with self._ring_spec_lock:
+      if not self._ring_specs:
+        return None
+      head = self._ring_specs[0]
+      if head["ref"]() is x and head["params"] == params:
+        self._ring_specs.popleft()
+        self.sample_spec_hits += 1
+        return head["toks"], head["ev"]
+      if drop_on_miss:
+        self._rewind_sample(self._ring_specs[0])
+        self._ring_specs.clear()
+      return None
 
   def _drop_ring_specs(self):
-    if self._ring_specs:
-      self._rewind_sample(self._ring_specs[0])
-      self._ring_specs.clear()
+    with self._ring_spec_lock:
+      if self._ring_specs:
+        self._rewind_sample(self._ring_specs[0])
+        self._ring_specs.clear()
+
+  def _noise_mark(self):
+    """Where the noise stream stands (reference mode): the Philox offset -- an int, no tensor like get_state()."""
+    return self.rng.get_offset() if self.sample_mode == "reference" else None
 
   def _rewind_sample(self, ss: dict):
     """A speculated sampler run that the caller did not ask for: give its noise back, forget the step enqueued on its ids."""
     rng_state, calls = ss["before"]
     if rng_state is not None:
-      self.rng.set_state(rng_state)
+      self.rng.set_offset(rng_state)
     self.sample_calls = calls
     self._spec = None
 
@@ -858,12 +877,32 @@ class B200ShardInferenceEngine(InferenceEngine):
     # GPU happens on another thread, so that with several requests in flight the worker can already enqueue the next
     # request's forward or sampler while this result is on its way to the host.
     loop = asyncio.get_running_loop()
-    result, new_state, ev = await loop.run_in_executor(self.executor, infer_wrapper)
-    if ev is not None:
-      if not ev.query():
-        await loop.run_in_executor(self._waiter, ev.synchronize)
-      trace("eng.gpu.done", request_id)
-    return result, new_state
+    fut = loop.create_future()
+
+    def settle(value, exc=None):
+      if not fut.cancelled():
+        fut.set_exception(exc) if exc is not None else fut.set_result(value)
+
+    def wait_gpu(result, new_state, ev):
+      try:
+        ev.synchronize()
+        trace("eng.gpu.done", request_id)
+        loop.call_soon_threadsafe(settle, (result, new_state))
+      except BaseException as e:
+        loop.call_soon_threadsafe(settle, None, e)
+
+    def job():     # worker -> (waiter) -> event loop: one wake-up of the loop per call
+      try:
+        result, new_state, ev = infer_wrapper()
+        if ev is None or ev.query():
+          loop.call_soon_threadsafe(settle, (result, new_state))
+        else:
+          self._waiter.submit(wait_gpu, result, new_state, ev)
+      except BaseException as e:
+        loop.call_soon_threadsafe(settle, None, e)
+
+    self.executor.submit(job)
+    return await fut
 
   # ------------------------------------------------------------------ device-resident token loop
   async def generate(self, request_id: str, shard: Shard, input_data: np.ndarray, inference_state: Optional[dict] = None, *,

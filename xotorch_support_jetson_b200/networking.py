@@ -352,6 +352,11 @@ class RingPeerHandle(PeerHandle):
   def _reachable(self) -> bool:
     return self._rank == self._ch.next_rank
 
+  @property
+  def delivers_results(self) -> bool:
+    """Node.broadcast_result may skip this handle: its send_result would drop the message anyway."""
+    return self._reachable()
+
   @staticmethod
   def _state_for_the_wire(tensor, inference_state: Optional[dict]) -> Optional[dict]:
     """The token history rides along only with a prompt (a later shard needs it to find padded slots);

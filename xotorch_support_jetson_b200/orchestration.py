@@ -321,7 +321,12 @@ class BoxNode:
         await asyncio.wait_for(peer.send_result(request_id, result, is_finished), timeout=15.0)
       except Exception as e:
         print(f"Error broadcasting result to {peer.id()}: {e}")
-    await asyncio.gather(*[one(p) for p in self.peers], return_exceptions=True)
+    # (a ring handle that cannot reach its peer says so: no coroutine, no timer for it -- 7 of 8 on an 8-GPU ring)
+    targets = [p for p in self.peers if getattr(p, "delivers_results", True)]
+    if len(targets) == 1:
+      await one(targets[0])
+    elif targets:
+      await asyncio.gather(*[one(p) for p in targets], return_exceptions=True)
 
   @property
   def current_topology(self) -> Topology:
