@@ -38,6 +38,18 @@ def _qwen(hidden, heads, kv, inter, layers, vocab=152064, tie=False, max_pos=327
   }
 
 
+def _mistral(hidden, heads, kv, inter, layers, head_dim, vocab=32768):
+  """An id with neither "llama" nor "qwen" in it: the reference then builds plain RotaryPositionalEmbeddings, no
+  q/k/v bias, untied head (general_mha.py:58-63) -- its mistral-nemo / nemotron-70b cards take that branch."""
+  return {
+    "architectures": ["MistralForCausalLM"], "model_type": "mistral", "hidden_act": "silu",
+    "hidden_size": hidden, "intermediate_size": inter, "num_attention_heads": heads,
+    "num_key_value_heads": kv, "num_hidden_layers": layers, "vocab_size": vocab, "head_dim": head_dim,
+    "max_position_embeddings": 131072, "rms_norm_eps": 1e-5, "rope_theta": 1000000.0,
+    "tie_word_embeddings": False, "torch_dtype": "bfloat16",
+  }
+
+
 # model id -> {layers, repo:{EngineClassName: hf repo}, hf_config}
 model_cards = {
   "llama-3.2-1b": {"layers": 16, "repo": {ENGINE_CLASS_NAME: "unsloth/Llama-3.2-1B-Instruct"},
@@ -57,6 +69,8 @@ model_cards = {
                      "hf_config": _llama(512, 4, 2, 1024, 6, head_dim=128, factor=8.0, vocab=2048)},
   "qwen-2.5-tiny": {"layers": 4, "repo": {ENGINE_CLASS_NAME: "synthetic/qwen-2.5-tiny"},
                     "hf_config": _qwen(384, 6, 2, 768, 4, vocab=1536, max_pos=4096)},
+  "mistral-tiny": {"layers": 4, "repo": {ENGINE_CLASS_NAME: "synthetic/mistral-tiny"},
+                   "hf_config": _mistral(320, 5, 1, 640, 4, head_dim=64, vocab=1280)},
 }
 
 
