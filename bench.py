@@ -268,9 +268,10 @@ def run_b200(args):
   c0 = runner.stage.counters()
   # ---- prefill: one untimed pass (builds launch plans), then a timed pass on fresh slots.  At N > 1 the
   # untimed pass is also the correctness check: the pipeline's greedy ids against a one-GPU full-shard run
-  tokens_check = None
+  tokens_check, ids_n1 = None, None
   if world > 1:
     tokens_check = pipeline_token_check(runner, args.model, hf_cfg, cfg, prompts, 8, local, dist)
+    ids_n1 = tokens_check.pop("_ids_n1", None)
   else:
     runner.prefill(prompts)
     runner.drain()
@@ -384,7 +385,7 @@ def run_b200(args):
   if world > 1:
     runner.reset()
     barrier()
-    e2e = e2e_ring(runner, args.model, cfg, prompts, K, W, dist, rank, world)
+    e2e = e2e_ring(runner, args.model, cfg, prompts, K, W, dist, rank, world, ids_n1)
 
   if rank == 0:
     line = {
@@ -431,6 +432,7 @@ def pipeline_token_check(runner, model_id, hf_cfg, cfg, prompts, n_steps, local,
     st.load_hf_tensors(*gpu_random_getter(hf_cfg, 0, 0.02, runner.device))
     per = max(1, runner.max_batch_tokens // L)
     want = torch.zeros_like(got)
+    ties = {}
     with torch.cuda.stream(torch.cuda.Stream(device=runner.device)):
       for m in range(M):
         tok = torch.zeros(B, dtype=torch.int32, device=runner.device)
@@ -438,11 +440,18 @@ def pipeline_token_check(runner, model_id, hf_cfg, cfg, prompts, n_steps, local,
           c1 = min(B, c0 + per)
           lg = st.forward(list(range(c0, c1)), [L] * (c1 - c0), [0] * (c1 - c0), tokens=prompts[m][c0:c1].reshape(-1))
           st.sample(lg, temp=0.0, out=tok[c0:c1])
+          tied0 = (lg == lg.max(dim=-1, keepdim=True).values)
+          for b in torch.nonzero(tied0.sum(-1) > 1).reshape(-1).tolist():
+            ties[f"0,{m},{c0 + b}"] = torch.nonzero(tied0[b]).reshape(-1).tolist()
         want[0, m] = tok.cpu()
         for k in range(n_steps):
           lg = st.forward(list(range(B)), [1] * B, [L + k] * B, tokens=tok)
           tok = st.sample(lg, temp=0.0)
           want[k + 1, m] = tok.cpu()
+          # exact ties of the (bf16-rounded) maximum: argmax takes the first index, the reference sampler lets its noise decide
+          tied = (lg == lg.max(dim=-1, keepdim=True).values)
+          for b in torch.nonzero(tied.sum(-1) > 1).reshape(-1).tolist():
+            ties[f"{k + 1},{m},{b}"] = torch.nonzero(tied[b]).reshape(-1).tolist()
         for b in range(B):
           st.release_slot(b)
     torch.cuda.synchronize()
@@ -452,7 +461,8 @@ def pipeline_token_check(runner, model_id, hf_cfg, cfg, prompts, n_steps, local,
     crc = lambda t: zlib.crc32(t.to(torch.int32).numpy().tobytes())
     res = [{"tokens_equal_n1": bool(torch.equal(got, want)), "tokens_crc": crc(got), "tokens_crc_n1": crc(want),
             "tokens_checked": f"{n_steps + 1} greedy ids x {M} micro-batches x {B} sequences (first id after the prefill + {n_steps} decode steps), "
-                              f"pipeline vs one-GPU full shard; mismatching ids: {int((got != want).sum())}"}]
+                              f"pipeline vs one-GPU full shard; mismatching ids: {int((got != want).sum())}",
+            "_ids_n1": (want.tolist(), ties)}]   # kept for the ring's end-to-end check, not printed
   dist.broadcast_object_list(res, src=world - 1)
   runner.reset()
   return res[0]
@@ -501,7 +511,7 @@ class PipelineRunnerView:
     return {"decode_bs1_tok_s": K / (ms * 1e-3), "decode_bs1_ms_per_tok": ms / K}
 
 
-def e2e_ring(runner, model_id, cfg, prompts, K, W, dist, rank, world):
+def e2e_ring(runner, model_id, cfg, prompts, K, W, dist, rank, world, ids_n1=None):
   """N > 1 end to end: every rank runs a BoxNode around a B200ShardInferenceEngine that adopts the rank's resident
   stage; the entry node (rank 0) gets one request per micro-batch as HOST token ids ``[B, L]`` (process_tokens) and
   receives every step's sampled ids back as host lists through on_token; between ranks the request travels the way
@@ -528,7 +538,7 @@ def e2e_ring(runner, model_id, cfg, prompts, K, W, dist, rank, world):
   eng.attach_stage(runner.shard, runner.stage, cfg)
   n_gen = W + K + 1
   host_prompts = [p.cpu().numpy().astype(np.int64) for p in prompts] if rank == 0 else None
-  stamps = {}
+  stamps, ids_seen = {}, {}
   # where a hop's host time goes: wall time inside the engine calls (they include waiting for the GPU)
   prof = {"infer_tensor": [], "sample": []}
 
@@ -555,6 +565,8 @@ def e2e_ring(runner, model_id, cfg, prompts, K, W, dist, rank, world):
 
       def on_token(rid, toks, fin):
         stamps.setdefault(rid, []).append(time.perf_counter())
+        if len(ids_seen.setdefault(rid, [])) < 16:
+          ids_seen[rid].append([int(t) for t in toks])
         if fin:
           left.discard(int(rid[2:]))
           if not left:
@@ -598,8 +610,31 @@ def e2e_ring(runner, model_id, cfg, prompts, K, W, dist, rank, world):
   t0 = max(stamps[f"mb{m}"][W] for m in range(M))
   t1 = max(stamps[f"mb{m}"][W + K] for m in range(M))
   V = cfg["vocab_size"]
+  # the ids the ring delivered against the one-GPU full-shard run of pipeline_token_check (same prompts, greedy)
+  same = None
+  if ids_n1 is not None:
+    want, ties = ids_n1
+    n_chk = min(len(want), min(len(v) for v in ids_seen.values()))
+    at_tie, bad = 0, 0
+    for m in range(M):
+      for b in range(B):
+        for k in range(n_chk):
+          g_, w_ = ids_seen[f"mb{m}"][k][b], want[k][m][b]
+          if g_ != w_:
+            # the plugin API samples with the reference's rule, argmax(softmax(logits / 1e-5) / q): among EXACTLY tied
+            # bf16 logits its noise decides, where the device loop's argmax takes the first index.  From such a step
+            # on the two runs are different (equally valid) continuations; anything else is a mismatch.
+            if g_ in ties.get(f"{k},{m},{b}", ()):
+              at_tie += 1
+            else:
+              bad += 1
+            break
+    same = {"tokens_equal_n1": bad == 0,
+            "tokens_checked": f"{n_chk} ids x {M} requests x {B} sequences delivered to rank 0's on_token vs one-GPU full shard: "
+                              f"{M * B - at_tie - bad} sequences identical, {at_tie} leave it at an exact tie of the maximum logit "
+                              f"(reference sampler: noise decides; device loop: first index), {bad} unexplained"}
   return {"value": B * M * K / (t1 - t0), "unit": "tok/s", "h2d_bytes_per_step": 8 * B * M, "d2h_bytes_per_step": B * M * (V * 4 + 4),
-          "round_trip_ms": (t1 - t0) / K * 1e3, "engine_call_median_ms_per_rank": per_rank,
+          "round_trip_ms": (t1 - t0) / K * 1e3, "engine_call_median_ms_per_rank": per_rank, **(same or {}),
           "api": "one BoxNode per rank (the reference Node's walk): process_tokens(host ids [32, 2048]) per micro-batch on rank 0 -> "
                  "B200ShardInferenceEngine.infer_tensor per stage -> Node.forward_tensor -> RingPeerHandle.send_tensor (header over gloo, "
                  "bf16 hidden rows over NCCL posted by the engines) -> last rank: fp32 logits [32, V] to the host, sample(), ids back "

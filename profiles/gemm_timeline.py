@@ -94,3 +94,28 @@ for i in ():
   rowsb = sorted([(int(cur[b, 4] - t0), int(cur[b, 5]), b, int(cur[b, 3] - t0)) for b in np.nonzero(act)[0]])
   print(f"launch {i} ({names[i % 4]}): blocks sorted by last-MMA time after the dependency resolved (ns): (t_lastMMA, smid, block, t_firstMMA)")
   print(" ".join(f"({t},{sm},{b},{f})" for t, sm, b, f in rowsb))
+
+
+# how uneven is the finish across blocks, and is it the same SMs every time?  (last MMA committed, relative to the
+# dependency release of the launch; normalised by the launch's median)
+print("finish spread per site: percentiles over blocks of (last MMA - dep release) in us, mean over layers")
+per_sm = {}
+for k_i, k in enumerate(names):
+  pct = []
+  for i in range(5 + (k_i - 5) % 4, n - 1, 4):
+    cur = ts[i]
+    act = cur[:, 0] > 0
+    t0 = cur[act, 2].min()
+    fin = (cur[act, 4] - t0) / 1e3
+    pct.append(np.percentile(fin, [0, 5, 25, 50, 75, 95, 100]))
+    med = np.median(fin)
+    for sm, f in zip(cur[act, 5], fin):
+      per_sm.setdefault((k, int(sm)), []).append(f / med)
+  m = np.mean(np.array(pct), axis=0)
+  print(f"{k:8s} min {m[0]:6.2f}  p5 {m[1]:6.2f}  p25 {m[2]:6.2f}  p50 {m[3]:6.2f}  p75 {m[4]:6.2f}  p95 {m[5]:6.2f}  max {m[6]:6.2f}")
+for k in names:
+  stats = sorted((float(np.mean(v)), float(np.std(v)), sm) for (kk, sm), v in per_sm.items() if kk == k)
+  print(f"{k}: relative finish time by SM (mean over layers, std, smid): fastest " +
+        " ".join(f"({m:.2f},{sd:.2f},{sm})" for m, sd, sm in stats[:8]) + " ... slowest " +
+        " ".join(f"({m:.2f},{sd:.2f},{sm})" for m, sd, sm in stats[-8:]))
+  print(f"   all SMs, sorted by smid: " + " ".join(f"{np.mean(per_sm[(k, sm)]):.2f}" for sm in sorted(sm for (kk, sm) in per_sm if kk == k)))

@@ -26,3 +26,16 @@ def test_pipeline_equals_single_gpu(built_lib, mid, peer, half):
          "--master-port", "29533", str(ROOT / "tests" / "mgpu_pipeline_check.py"), mid]
   out = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env)
   assert out.returncode == 0 and "MGPU_PIPELINE_OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs at least 2 GPUs")
+@pytest.mark.parametrize("mid,mode", [("llama-3.1-tiny", "landing"), ("llama-3.1-tiny", "nccl"), ("qwen-2.5-tiny", "landing")])
+def test_process_ring_equals_direct_engine_loop(built_lib, mid, mode):
+  """One BoxNode + B200ShardInferenceEngine per rank (torchrun), three requests in flight, ids delivered to rank 0:
+  equal to a single full-shard engine -- decode steps through the next rank's landing buffers over CUDA IPC, and over
+  NCCL send / recv."""
+  n = 2
+  cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr", "127.0.0.1",
+         "--master-port", "29537", str(ROOT / "tests" / "mgpu_ring_check.py"), mid, mode]
+  out = subprocess.run(cmd, capture_output=True, text=True, timeout=120)
+  assert out.returncode == 0 and "MGPU_RING_OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]

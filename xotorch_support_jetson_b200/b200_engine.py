@@ -269,7 +269,11 @@ class B200ShardInferenceEngine(InferenceEngine):
     """Map the NEXT rank's landing buffers (its ``ring_landing_handles``); decode steps of at most ``rows`` sequences
     then leave through them, one slot per request in flight (at most ``n_slots``), everything else over the data plane."""
     st = self.stage
-    if st is None or st.is_last or next_handles is None or st.ho_geometry != (int(n_slots), int(rows)):
+    if st is None or st.is_last or next_handles is None:
+      return
+    if st.ho_geometry is None:      # the first stage receives nothing, but a producer needs its side of the hand-off state too
+      st.handoff_create(n_slots, rows, ipc=False)
+    if st.ho_geometry != (int(n_slots), int(rows)):
       return
     if not st.ho_connected:
       st.handoff_connect(*next_handles)
@@ -279,6 +283,7 @@ class B200ShardInferenceEngine(InferenceEngine):
 
   def _stage_changed(self):
     self._landing_epoch += 1
+    self._ring_landing = None     # mapped buffers belonged to the old stage: back to the data plane until reconnected
     self._next_epoch = None       # a rebuilt producer stage is not connected to anything yet
     if self.landing_slots > 0 and self.stage is not None and not self.stage.is_first:
       self._ensure_handoff_buffers(self.stage, self.landing_slots, self.landing_rows)

@@ -302,6 +302,22 @@ class RingChannel:
       return kind, meta, shape
     return kind, meta, None
 
+  def warm_up(self, device=None):
+    """First contact on the data plane, made by every rank at the same time (a collective step of ring set-up).
+    NCCL connects a pair of ranks when they first exchange data and BOTH have to be in the call for that; in
+    steady state the receiver posts its side only after the header has reached it, which the sender sends after
+    its own -- so without this the first hidden rows would wait for a receive that waits for them."""
+    if self.world < 2 or device is None or self.dist.get_backend(self.data_group) != "nccl":
+      return
+    import torch
+    out = torch.zeros(8, dtype=torch.bfloat16, device=device)
+    inp = torch.empty_like(out)
+    ops = [self.dist.P2POp(self.dist.isend, out, self.next_rank, group=self.data_group),
+           self.dist.P2POp(self.dist.irecv, inp, self.prev_rank, group=self.data_group)]
+    for w in self.dist.batch_isend_irecv(ops):
+      w.wait()
+    torch.cuda.synchronize(device)
+
   # -- data plane (engine threads only)
   def send_rows(self, rows):
     """Non-blocking for the host: on NCCL the send is enqueued on the current stream, on gloo it completes in the

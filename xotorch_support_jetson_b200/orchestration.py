@@ -378,12 +378,27 @@ def build_rank_node(engine, dist, rank: int, world: int, ctrl_group=None, data_g
                  shard_map=shard_map)
   if world > 1 and hasattr(engine, "bind_ring"):
     engine.bind_ring(ch, sends=rank + 1 < world)   # the last stage only RECEIVES rows (its output is a token id)
-    if landing is not None and hasattr(engine, "ring_landing_handles"):
-      # decode steps through the next rank's landing buffers (CUDA IPC): every rank exports its own, maps its successor's
-      n_slots, rows = landing
-      mine = engine.ring_landing_handles(n_slots, rows) if rank > 0 else None
-      everyone = [None] * world
-      dist.all_gather_object(everyone, mine, group=ctrl_group)
-      if rank + 1 < world:
-        engine.connect_ring_landing(everyone[rank + 1], n_slots, rows)
+    dev = getattr(engine, "device_index", None)
+    if dev is not None:
+      import torch
+      ch.warm_up(torch.device("cuda", int(dev)))
+    if landing is not None:
+      connect_rank_landing(engine, dist, rank, world, ctrl_group, landing)
   return node
+
+
+def connect_rank_landing(engine, dist, rank: int, world: int, ctrl_group, landing: Tuple[int, int]) -> None:
+  """Decode steps of a process-per-GPU ring through the next rank's landing buffers (CUDA IPC) instead of NCCL
+  send / recv: every rank exports the buffers of its stage and maps its successor's.  A COLLECTIVE call (one
+  all_gather over ``ctrl_group`` -- a group no running RingServer is listening on) to be made once every rank's engine holds its stage -- ``build_rank_node`` makes
+  it when given ``landing``, which suits engines that adopt a resident stage; engines that load their shard on first
+  use call it after ``ensure_shard``.  A rank whose engine cannot take part (no stage yet, other buffer geometry)
+  simply stays on the NCCL path, and so does its predecessor."""
+  if not hasattr(engine, "ring_landing_handles"):
+    mine = None
+  else:
+    mine = engine.ring_landing_handles(*landing) if rank > 0 else None
+  everyone = [None] * world
+  dist.all_gather_object(everyone, mine, group=ctrl_group)
+  if rank + 1 < world and hasattr(engine, "connect_ring_landing"):
+    engine.connect_ring_landing(everyone[rank + 1], *landing)
