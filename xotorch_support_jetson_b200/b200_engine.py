@@ -23,7 +23,12 @@ forward at the same position overwrites the KV entry, so nothing has to be undon
 results are those of the unspeculated path bit for bit; ``speculate_next=False`` /
 ``XB_API_SPECULATE=0`` turns it off.  With ONE request in flight the sampler itself is run ahead as
 well (``_speculate_sample``: the parameters of the request's previous ``sample()`` call), so that in
-a steady infer_tensor / sample loop the host only collects results.
+a steady infer_tensor / sample loop the host only collects results.  The LAST stage of a ring does the
+same for every request in flight, in the order of their forwards (``_speculate_ring_sample``).
+
+Inside a box the engine is also the data plane of the ring (``connect_next`` / ``bind_ring`` /
+``connect_ring_landing``): hidden rows leave as device references, decode steps through the next
+stage's landing buffers (same process: device pointers; other process: CUDA IPC).
 """
 import asyncio
 import collections
