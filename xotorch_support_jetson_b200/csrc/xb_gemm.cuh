@@ -654,7 +654,30 @@ struct GemmPlan {
   SplitInfo split;   // how a consumer sums the fp32 partial planes (SKINNY)
   int bn;
   int grid;
+  int stages;        // SKINNY: depth of the smem pipeline (xb_skinny_stages)
 };
+
+// Depth of the shared-memory pipeline of the skinny (decode) Linear by token-column width.  Every stage is a 16 KB box
+// of weights plus the token tile; the stages a block can fill before the upstream grid is done are what keeps HBM
+// busy across the kernel boundary, while a block too large to share the SM with its neighbours in the stream loses
+// that overlap again.  Measured on the graph-replayed 8B step (ms per step; profiles/r02_decode_ab_stages.txt):
+//   16 columns (bs=1):  5: 3.294  6: 3.249  7: 3.227  8: 3.280  9: 3.299  10: 3.335
+//   32 columns (bs=32): 5: 4.85   6: 4.67   7: 4.68   8: 4.70   9: 4.72   10: 4.76
+//   64 columns (bs=64): 4: 6.85   5: 6.60   6: 6.59   7: 6.59   8: 6.57
+// XB_GEMM_STAGES=r1 selects the round-1 depths (5 / 5 / 4 / 6) for an A/B; a number selects that depth for the widths
+// that have it instantiated (xb_gemm_run) and leaves the others at their default.
+static int xb_skinny_stages(int bn) {
+  const int w = bn <= 16 ? 0 : bn <= 32 ? 1 : bn <= 64 ? 2 : 3;
+  static const int dflt[4] = {7, 6, 8, 6}, r1[4] = {5, 5, 4, 6};
+  static const int have[4][4] = {{5, 7, 0, 0}, {5, 6, 7, 8}, {4, 8, 0, 0}, {6, 7, 0, 0}};
+  const char* ev = getenv("XB_GEMM_STAGES");
+  if (ev == nullptr) return dflt[w];
+  if (ev[0] == 'r') return r1[w];
+  const int n = atoi(ev);
+  for (int i = 0; i < 4; ++i)
+    if (n > 0 && have[w][i] == n) return n;
+  return dflt[w];
+}
 
 static int xb_pick_bn_skinny(int T) { return T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : 128; }
 
@@ -733,6 +756,7 @@ static int xb_gemm_plan(GemmPlan* p, const bf16* x, long long ldx, const bf16* w
   } else {
     p->tmC = p->tmA;
   }
+  p->stages = g.mode == XB_GEMM_SKINNY ? xb_skinny_stages(p->bn) : 0;
   p->split.k_blocks = g.k_blocks;
   p->split.q = g.mode == XB_GEMM_SKINNY ? g.sk_q : 0;
   p->split.splits = g.mode == XB_GEMM_SKINNY ? g.splits : 1;
@@ -740,13 +764,15 @@ static int xb_gemm_plan(GemmPlan* p, const bf16* x, long long ldx, const bf16* w
 }
 
 static int xb_gemm_run(const GemmPlan& p, cudaStream_t st, int pdl) {
+  if (p.stages > 0) {
+#define XB_STAGE_CASE(BN_, N_) if (p.bn == BN_ && p.stages == N_) return xb_gemm_launch_t<BN_, N_>(p.tmA, p.tmB, p.tmC, p.args, p.grid, st, pdl);
+    XB_STAGE_CASE(16, 7) XB_STAGE_CASE(32, 6) XB_STAGE_CASE(64, 8) XB_STAGE_CASE(128, 6)          // defaults
+    XB_STAGE_CASE(16, 5) XB_STAGE_CASE(32, 5) XB_STAGE_CASE(64, 4) XB_STAGE_CASE(128, 7)          // A/B (XB_GEMM_STAGES)
+    XB_STAGE_CASE(32, 7) XB_STAGE_CASE(32, 8)
+#undef XB_STAGE_CASE
+    return xb_fail(1, "no skinny Linear instantiated for %d token columns with %d stages", p.bn, p.stages);
+  }
   switch (p.bn) {
-    case 16:  return xb_gemm_launch_t<16, 5>(p.tmA, p.tmB, p.tmC, p.args, p.grid, st, pdl);
-#ifndef XB_G32_STAGES
-#define XB_G32_STAGES 5
-#endif
-    case 32:  return xb_gemm_launch_t<32, XB_G32_STAGES>(p.tmA, p.tmB, p.tmC, p.args, p.grid, st, pdl);
-    case 64:  return xb_gemm_launch_t<64, 4>(p.tmA, p.tmB, p.tmC, p.args, p.grid, st, pdl);
     case 128: return xb_gemm_launch_t<128, 6>(p.tmA, p.tmB, p.tmC, p.args, p.grid, st, pdl);
     case 256: return xb_gemm_launch_t<256, 4>(p.tmA, p.tmB, p.tmC, p.args, p.grid, st, pdl);
   }
