@@ -186,6 +186,14 @@ int xb_handoff_connect_local(xb_engine* e, xb_engine* next);
  * and lets the step finish on whatever the landing buffer holds; every later xb_forward* call on that
  * engine fails with the recorded message until xb_handoff_clear_error is called. */
 int xb_handoff_clear_error(xb_engine* e);
+/* Keep `n` SMs out of the decode Linears' grids (one persistent block per SM otherwise; default 1, XB_RESERVE_SMS at
+ * engine creation).  A stage of a ring has a communication kernel resident for whole steps -- an NCCL receive posted
+ * ahead for the ids the last stage will send: a Linear block that finds no SM free of it runs as a second wave after
+ * all the others and doubles that launch (measured at 2 GPUs: 4.9 -> 5.45 ms per step once the blocks had grown to
+ * 124 KB of shared memory; 4.70 ms with one SM set aside).  The stream-K split follows the block count, so all stages
+ * of a ring -- and a single-GPU engine whose ids they are compared with -- must use the same value to agree bit for
+ * bit.  Drops the captured decode steps and launch plans; call it before serving. */
+int xb_reserve_sms(xb_engine* e, int n);
 
 /* Replaces TorchDynamicShardInferenceEngine.sample + torchtune.generation.sample
  * (sharded_inference_engine.py:208-228).  logits: device fp32 [n, vocab].

@@ -12,7 +12,7 @@ SYMBOLS = (
   "xb_last_error", "xb_abi_version", "xb_engine_create", "xb_engine_destroy", "xb_load_weight",
   "xb_load_safetensors", "xb_weights_missing", "xb_safetensors_list",
   "xb_kv_reserve", "xb_kv_release_slot", "xb_kv_slot_len", "xb_forward", "xb_forward_host_logits", "xb_sample",
-  "xb_handoff_create", "xb_handoff_connect", "xb_forward_handoff", "xb_handoff_connect_local", "xb_handoff_clear_error",
+  "xb_handoff_create", "xb_handoff_connect", "xb_forward_handoff", "xb_handoff_connect_local", "xb_handoff_clear_error", "xb_reserve_sms",
   "xb_get_counters", "xb_debug_linear", "xb_bench_linears", "xb_bench_attention", "xb_linear_noalloc", "xb_debug_timeline",
 )
 
@@ -94,6 +94,7 @@ def load():
   lib.xb_handoff_connect.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
   lib.xb_handoff_connect_local.argtypes = [C.c_void_p, C.c_void_p]
   lib.xb_handoff_clear_error.argtypes = [C.c_void_p]
+  lib.xb_reserve_sms.argtypes = [C.c_void_p, C.c_int]
   lib.xb_forward_handoff.argtypes = [C.c_void_p, C.POINTER(Batch), C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
   lib.xb_sample.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_float, C.c_void_p, C.c_uint64,
                             C.c_void_p, C.c_void_p]

@@ -41,6 +41,7 @@ struct xb_engine {
   xb_model_desc d;
   int device = 0;
   int num_sms = 148;
+  int reserved_sms = 1;   // SMs kept free of the decode Linears (xb_engine_create, xb_reserve_sms)
   int nl = 0;  // local layers
   int NQ = 0, NKV = 0, NQKV = 0;
   std::vector<LayerW> L;
@@ -229,6 +230,14 @@ extern "C" int xb_engine_create(const xb_model_desc* desc, int device, xb_engine
   e->d = d;
   e->device = device;
   e->num_sms = prop.multiProcessorCount;
+  {
+    // One SM is left out of the decode Linears' grids on EVERY engine, not only where a communication kernel is
+    // resident: the stream-K decomposition (and with it the fp32 summation order) follows the block count, and the
+    // stages of a ring must produce the bits a single-GPU engine produces.
+    const char* rv = getenv("XB_RESERVE_SMS");
+    e->reserved_sms = rv != nullptr ? atoi(rv) : 1;
+    if (e->reserved_sms < 0 || e->reserved_sms >= e->num_sms) e->reserved_sms = 1;
+  }
   e->nl = d.end_layer - d.start_layer + 1;
   e->NQ = d.n_heads * d.head_dim;
   e->NKV = d.n_kv_heads * d.head_dim;
@@ -723,7 +732,9 @@ static int get_plan(xb_engine* e, int site, int layer, const bf16* x, long long 
   auto it = e->plans.find(key);
   if (it == e->plans.end()) {
     GemmPlan p;
-    XB_TRY(xb_gemm_plan(&p, x, ldx, w, 1, T, N, K, out, ld_out, bias, round_bf16, e->num_sms, 0));
+    // (a decode Linear is one block per SM; SMs set aside with xb_reserve_sms stay free for a resident communication kernel)
+    const int sms = (T <= 128 && e->reserved_sms > 0 && e->reserved_sms < e->num_sms) ? e->num_sms - e->reserved_sms : e->num_sms;
+    XB_TRY(xb_gemm_plan(&p, x, ldx, w, 1, T, N, K, out, ld_out, bias, round_bf16, sms, 0));
     if (p.args.mode == XB_GEMM_WIDE && site == SITE_QKV) {
       // prefill: bias + RoPE + q store + paged-KV append happen in the GEMM epilogue
       const xb_model_desc& d = e->d;
@@ -1243,6 +1254,18 @@ extern "C" int xb_handoff_create(xb_engine* e, int n_slots, int rows, void* land
     XB_CUDA(cudaHostGetDevicePointer((void**)&e->ho_err_dev, e->ho_err, 0));
   }
   XB_CUDA(cudaDeviceSynchronize());
+  return 0;
+}
+
+extern "C" int xb_reserve_sms(xb_engine* e, int n) {
+  XB_CHECK(e != nullptr && n >= 0 && n < e->num_sms, "bad argument");
+  XB_CUDA(cudaSetDevice(e->device));
+  XB_CUDA(cudaDeviceSynchronize());
+  for (auto& kv : e->graphs)
+    if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+  e->graphs.clear();     // captured steps and launch plans were sized for the old SM count
+  e->plans.clear();
+  e->reserved_sms = n;
   return 0;
 }
 

@@ -254,6 +254,10 @@ class StageRuntime:
     _cabi.check(self.lib.xb_handoff_connect_local(self._h, next_stage._h))
     self._next_stage = next_stage   # keeps the consumer's buffers alive as long as this producer
 
+  def reserve_sms(self, n: int):
+    """Keep n SMs free of the decode Linears (xb_reserve_sms): for stages with a resident communication kernel."""
+    _cabi.check(self.lib.xb_reserve_sms(self._h, int(n)))
+
   def handoff_clear_error(self):
     _cabi.check(self.lib.xb_handoff_clear_error(self._h))
 
