@@ -580,18 +580,7 @@ def e2e_ring(runner, model_id, cfg, prompts, K, W, dist, rank, world, ids_n1=Non
     await loop.run_in_executor(None, lambda: dist.barrier(group=sync))   # the other ranks keep serving until rank 0 is done
     await node.stop()
 
-  if os.environ.get("XB_PROFILE_RING") == "1" and rank in (0, world - 1):   # where a hop's host time goes (developer aid)
-    import cProfile, pstats, io
-    pr = cProfile.Profile()
-    pr.enable()
-    asyncio.run(run())
-    pr.disable()
-    buf = io.StringIO()
-    pstats.Stats(pr, stream=buf).sort_stats("tottime").print_stats(35)
-    (ROOT / "gpurun_out").mkdir(exist_ok=True)
-    (ROOT / "gpurun_out" / f"ring_profile_rank{rank}.txt").write_text(buf.getvalue())
-  else:
-    asyncio.run(run())
+  asyncio.run(run())
   torch.cuda.synchronize()
   from xotorch_support_jetson_b200 import networking as _nw
   if _nw.TRACE is not None:

@@ -127,7 +127,8 @@ def _ring_worker(rank, world, port, ret):
 
   async def run():
     node = build_rank_node(RingScripted(tr["node_ids"][rank], log, tr["eos_token_id"]), dist, rank, world, ctrl_group=ctrl,
-                           data_group=data, max_generate_tokens=tr["max_generate_tokens"])
+                           data_group=data, max_generate_tokens=tr["max_generate_tokens"],
+                           landing=(4, 8) if world == 3 else None)   # an engine without landing buffers: the ring stays on the data plane
     await node.start()
     await node.collect_topology(set())
     done = asyncio.Event()
