@@ -358,16 +358,6 @@ def run_b200(args):
   if tokens_check is not None:
     extra.update(tokens_check)
 
-  # ---- decode bs=1 (latency-bound single stream), same pipeline
-  runner.reset()
-  barrier()
-  r1 = PipelineRunnerView(runner)
-  bs1 = r1.run_bs1(prompts[0][:1], W, K, timed, dist if world > 1 else None)
-  extra.update(bs1)
-  if world == 1:
-    b1_bytes = wbytes + (L + W + (K - 1) / 2.0) * cnt["kv_bytes_per_pos"]
-    extra["decode_bs1_hbm_frac"] = (b1_bytes / (1.0 / bs1["decode_bs1_tok_s"])) / 1e9 / peaks["hbm_gbs"]
-
   # ---- N=1: end-to-end through the InferenceEngine API with host numpy buffers
   cpu_base = None
   if world == 1:
@@ -379,6 +369,18 @@ def run_b200(args):
       cpu_base = {"value": val, "unit": "tok/s", "cores": os.cpu_count() or 1, "kind": "port",
                   "sample": f"{args.cpu_steps} decode steps of {args.ref_batch} sequences (the named batch) at context {L} (synthetic KV cache), "
                             f"oracle port in reference-exact mode, {time.perf_counter() - t0:.0f}s incl. weight init"}
+
+  # ---- decode bs=1 (latency-bound single stream), same pipeline; median of R x K steps like the main leg.  (At N=1 it
+  # comes after the CPU-baseline leg, i.e. on a GPU that has been idle for a while, not one still at its power cap
+  # from the batch-32 and prefill legs: a single stream draws far less power than they do.)
+  runner.reset()
+  barrier()
+  r1 = PipelineRunnerView(runner)
+  bs1 = r1.run_bs1(prompts[0][:1], W, K, lambda f: timed_median(f, R)[0], dist if world > 1 else None)
+  extra.update(bs1)
+  if world == 1:
+    b1_bytes = wbytes + (L + W + (R * K - 1) / 2.0) * cnt["kv_bytes_per_pos"]
+    extra["decode_bs1_hbm_frac"] = (b1_bytes / (1.0 / bs1["decode_bs1_tok_s"])) / 1e9 / peaks["hbm_gbs"]
 
   # ---- N > 1: end-to-end through the plugin API and the ring: one BoxNode per rank, RingPeerHandle / RingServer
   # between them, infer_tensor + sample per hop with host buffers at both ends of the ring
