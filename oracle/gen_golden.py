@@ -26,7 +26,7 @@ ROOT = Path(__file__).resolve().parent.parent
 sys.path.insert(0, str(ROOT))
 GOLD = ROOT / "tests" / "golden"
 
-MODELS = ("llama-3.2-tiny", "llama-3.1-tiny", "qwen-2.5-tiny")
+MODELS = ("llama-3.2-tiny", "llama-3.1-tiny", "qwen-2.5-tiny", "mistral-tiny")
 SEED, STD, JITTER = 0, 0.05, 0.1
 PROMPT_LEN, N_DEC = 37, 8
 

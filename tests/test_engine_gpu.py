@@ -174,7 +174,7 @@ def test_sampler_matches_reference_semantics(built_lib):
   st.close()
 
 
-@pytest.mark.parametrize("mid", ["llama-3.2-tiny", "llama-3.1-tiny", "qwen-2.5-tiny"])
+@pytest.mark.parametrize("mid", ["llama-3.2-tiny", "llama-3.1-tiny", "qwen-2.5-tiny", "mistral-tiny"])
 def test_cuda_path_against_committed_golden(built_lib, mid):
   """The CUDA forward against tests/golden/oracle_<model>.npz (generated by oracle/gen_golden.py
   from the oracle in reference-exact mode; nothing under oracle/ is executed here)."""

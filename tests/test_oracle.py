@@ -12,7 +12,7 @@ from xotorch_support_jetson_b200.models import model_cards
 from xotorch_support_jetson_b200.synth import random_hf_state
 
 GOLD = Path(__file__).resolve().parent / "golden"
-MODELS = ("llama-3.2-tiny", "llama-3.1-tiny", "qwen-2.5-tiny")
+MODELS = ("llama-3.2-tiny", "llama-3.1-tiny", "qwen-2.5-tiny", "mistral-tiny")
 
 
 def _setup(mid, dtype=None):
@@ -78,7 +78,7 @@ def test_sampler_restatement():
   assert t.dtype == torch.int32 and t.shape == (4, 1)
 
 
-@pytest.mark.parametrize("mid", MODELS + ("mistral-tiny",))     # the last one: the reference's "plain" RoPE branch
+@pytest.mark.parametrize("mid", MODELS)     # mistral-tiny: the reference's "plain" RoPE branch
 def test_product_rope_table_equals_oracle(mid):
   """The host builds the XB_W_ROPE_TABLE upload independently of the oracle; both must be the
   same numbers (bf16-rounded, reference-exact mode and fp32 mode)."""
